@@ -1,0 +1,110 @@
+"""world_size>1 plumbing on CPU/gloo: BASELINE config 1 (ResNet-32, 2-stage model parallel, one
+gradient-poisoning node), 1F1B pipeline == single-process numerics, trust-weighted DP."""
+import pytest
+import torch
+
+from mp_utils import run_distributed
+from trustworthy_dl.parallel.pipeline import make_schedule
+
+
+def _mp_worker(rank, world, parallelism, micro, attack_step, steps):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = None
+    if attack_step is not None:
+        att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5,
+                                               start_step=attack_step))
+        att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world,
+                         learning_rate=1e-3, checkpoint_interval=0, device="cpu", parallelism=parallelism,
+                         micro_batches=micro, optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=steps)]
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+            "reassign": [(r["from_node"], r["to_node"], r["step"], r["stages"]) for r in t.reassignment_history],
+            "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist(),
+            "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
+
+
+def test_schedules_are_topological():
+    for kind in ("gpipe", "1f1b"):
+        for S, M in ((2, 1), (4, 8), (3, 2), (8, 8)):
+            order = make_schedule(S, M, kind)
+            assert len(order) == 2 * S * M and len(set(order)) == 2 * S * M
+            pos = {op: i for i, op in enumerate(order)}
+            for s in range(S):
+                for m in range(M):
+                    if s > 0:
+                        assert pos[("F", s - 1, m)] < pos[("F", s, m)]
+                    if s < S - 1:
+                        assert pos[("B", s + 1, m)] < pos[("B", s, m)]
+                    assert pos[("F", s, m)] < pos[("B", s, m)]
+    # 1F1B bounds in-flight activations of stage 0 by the number of stages
+    order = make_schedule(4, 8, "1f1b")
+    live = peak = 0
+    for k, s, m in order:
+        if s == 0:
+            live += 1 if k == "F" else -1
+            peak = max(peak, live)
+    assert peak <= 4
+
+
+def test_config1_resnet32_two_stage_gloo_with_poisoned_node():
+    res = run_distributed(_mp_worker, 2, "model", 1, 12, 18)
+    a, b = res
+    assert a["losses"] == pytest.approx(b["losses"])                     # replicated view of the loss
+    assert a["attacks"] == b["attacks"] == [(1, 12, "gradient_poisoning")]
+    assert a["reassign"] == b["reassign"] == [(1, 0, 12, [1])]
+    assert a["owner"] == b["owner"] == [0, 0]
+    assert a["trust"] == pytest.approx(b["trust"]) and a["trust"][1] < 0.5 < a["trust"][0]
+    assert all(torch.isfinite(torch.tensor(a["losses"])))
+    assert len(a["losses"]) == 18                                        # kept training after migration
+
+
+def test_model_parallel_matches_single_process():
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=2, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd")
+    t = DistributedTrainer(cfg)
+    single = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=5)]
+    multi = run_distributed(_mp_worker, 2, "model", 1, None, 5)[0]["losses"]
+    assert multi == pytest.approx(single, rel=1e-4)
+
+
+def test_pipeline_1f1b_runs_and_learns():
+    res = run_distributed(_mp_worker, 2, "pipeline", 4, None, 12)
+    assert res[0]["losses"] == pytest.approx(res[1]["losses"])
+    assert res[0]["attacks"] == [] and res[0]["owner"] == [0, 1]
+
+
+def _dp_worker(rank, world, mode, steps, attack_step):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5,
+                                           start_step=attack_step, gradient_mode=mode))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=12, num_nodes=world,
+                         learning_rate=1e-3, checkpoint_interval=0, device="cpu", parallelism="data", optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 12, num_batches=steps)]
+    w = torch.cat([p.detach().reshape(-1) for p in t.model_partitions[0].parameters()])
+    return {"losses": losses, "wsum": float(w.double().sum()), "attacks": [(a["node_id"], a["step"]) for a in t.attack_history],
+            "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist(),
+            "coeff": t._backend_impl.reducer.last_coeff.tolist()}
+
+
+@pytest.mark.parametrize("mode", ["scale", "sign_flip"])
+def test_data_parallel_trust_weighted_allreduce(mode):
+    res = run_distributed(_dp_worker, 3, mode, 10, 6)
+    assert len({round(r["wsum"], 6) for r in res}) == 1                  # replicas stay in sync
+    assert all(r["attacks"] == res[0]["attacks"] for r in res)
+    assert res[0]["attacks"][0] == (1, 6)                                # flagged the step it was injected
+    assert res[0]["owner"][1] != 1                                       # its data shard was reassigned
+    assert res[0]["coeff"][1] == 0.0                                     # and it no longer contributes
+    assert res[0]["trust"][1] < 0.5

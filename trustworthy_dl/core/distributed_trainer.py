@@ -1,0 +1,626 @@
+"""Training engine / orchestrator.
+
+Public surface of the reference trainer (``/root/reference/distributed_trainer.py``):
+``TrainingState`` (:30-35), ``NodeConfig`` (:37-46), ``TrainingConfig`` (:48-61) and
+``DistributedTrainer`` (:63-527) with ``setup_distributed_environment``, ``create_model_partitions``,
+``forward_pass``, ``backward_pass``, ``update_trust_scores``, ``calculate_output_deviation``,
+``calculate_gradient_consistency``, ``handle_detected_attack``, ``handle_gradient_attack``,
+``reassign_node_tasks``, ``estimate_migration_time``, ``perform_task_reassignment``,
+``train_epoch``, ``calculate_loss``, ``optimizer_step``, ``save_checkpoint``, ``train``,
+``validate``, ``get_training_stats``, ``cleanup``.  Both constructor forms are accepted
+(SURVEY 2.3): ``DistributedTrainer(TrainingConfig(...))`` and the README's
+``DistributedTrainer(model_name='gpt2', num_nodes=8, trust_threshold=0.7)``.
+
+What is different from the reference (which cannot be imported and never populates its stage /
+optimizer tables):
+
+* ``parallelism`` selects the execution strategy: ``"model"`` (the reference's stage loop —
+  in one process when no process group exists, one stage per rank over send/recv otherwise),
+  ``"pipeline"`` (micro-batched 1F1B, parallel/pipeline.py), ``"data"`` (replicas + the fused
+  trust-weighted all-reduce, parallel/data_parallel.py) and ``"tensor"``
+  (parallel/tensor_parallel.py).
+* Stage ownership lives in a :class:`StageMap`; reassignment really moves stages (and, across
+  processes, their parameters) instead of aliasing a python object, is load-aware, honours
+  ``max_reassignment_attempts`` and never leaves a layer unexecuted (the reference skips a
+  compromised stage and silently trains a shallower model, :154-157).
+* Security inputs are computed on the device: one statistics kernel per stage output, one
+  multi-tensor norm launch per node; with ``deferred_detection`` all per-stage statistics of a
+  step cross PCIe in a single copy instead of one full-activation D2H per stage (:78).
+* Gradients that fail verification are not applied.
+* ``load_checkpoint`` exists.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import time
+from dataclasses import dataclass, field, fields
+from enum import Enum
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..models.model_factory import ModelFactory
+from ..security.attack_detection import AttackDetector
+from ..security.gradient_verification import GradientVerifier
+from ..security.parameter_monitor import ParameterMonitor
+from ..utils.metrics import MetricsCollector
+from . import checkpoint as _ckpt
+from .node_monitor import NodeMonitor
+from .partition import StageMap, build_stages, unit_cost
+from .reassignment import ReassignmentPlanner, estimate_migration_time
+from .trust_manager import NodeStatus, TrustManager
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["TrainingState", "NodeConfig", "TrainingConfig", "DistributedTrainer"]
+
+
+class TrainingState(Enum):
+    INITIALIZING = "initializing"
+    TRAINING = "training"
+    UNDER_ATTACK = "under_attack"
+    RECOVERING = "recovering"
+    COMPLETED = "completed"
+
+
+@dataclass
+class NodeConfig:
+    node_id: int
+    rank: int
+    world_size: int
+    gpu_id: int
+    model_partition: str
+    trust_score: float = 1.0
+    status: NodeStatus = NodeStatus.TRUSTED
+
+
+@dataclass
+class TrainingConfig:
+    # ---- reference fields (distributed_trainer.py:48-61), same order and defaults ----
+    model_name: str = "gpt2"
+    dataset_name: str = "openwebtext"
+    batch_size: int = 32
+    learning_rate: float = 5e-5
+    num_epochs: int = 10
+    num_nodes: int = 4
+    trust_threshold: float = 0.7
+    attack_detection_enabled: bool = True
+    gradient_verification_enabled: bool = True
+    checkpoint_interval: int = 100
+    max_reassignment_attempts: int = 3
+    # ---- extensions ----
+    model_size: Optional[str] = None
+    model_kwargs: Dict[str, Any] = field(default_factory=dict)
+    parallelism: str = "model"                 # model | pipeline | data | tensor
+    tp_size: int = 1
+    pp_size: int = 1
+    dp_size: int = 1
+    micro_batches: int = 1
+    device: str = "auto"
+    dtype: str = "fp32"                        # fp32 | bf16 (autocast on CUDA)
+    optimizer: str = "adamw"
+    weight_decay: float = 0.01
+    lr_schedule: str = "constant"              # constant | cosine | step
+    clip_norm: float = 0.0
+    parameter_monitoring_enabled: bool = False
+    deferred_detection: bool = True
+    checkpoint_dir: str = "checkpoints"
+    migration_model: str = "reference"         # reference (1 GiB/s + 2 s) | nvlink
+    initial_trust: float = 1.0
+    steps_per_epoch: Optional[int] = None
+    seq_len: Optional[int] = None
+    log_interval: int = 10
+    seed: int = 0
+    engine: str = "auto"                       # auto | eager | fused (GPT2Engine on sm_100a)
+
+    @classmethod
+    def from_kwargs(cls, **kw) -> "TrainingConfig":
+        names = {f.name for f in fields(cls)}
+        unknown = set(kw) - names
+        if unknown:
+            raise TypeError(f"unknown TrainingConfig fields: {sorted(unknown)}")
+        return cls(**kw)
+
+
+def _resolve_device(spec: str) -> torch.device:
+    if spec == "auto":
+        return torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+    return torch.device(spec)
+
+
+class DistributedTrainer:
+    """Main orchestrator with adversarial attack mitigation."""
+
+    def __init__(self, config: Optional[TrainingConfig] = None, *, attacker=None,
+                 trust_manager: Optional[TrustManager] = None, model: Optional[nn.Module] = None, **kwargs):
+        if config is None:
+            config = TrainingConfig.from_kwargs(**kwargs)
+        elif kwargs:
+            raise TypeError("pass either a TrainingConfig or keyword fields, not both")
+        self.config = config
+        self.training_state = TrainingState.INITIALIZING
+        self.current_epoch = 0
+        self.global_step = 0
+        self.device = _resolve_device(config.device)
+
+        self.trust_manager = trust_manager if trust_manager is not None else TrustManager(
+            num_nodes=config.num_nodes, trust_threshold=config.trust_threshold, initial_trust=config.initial_trust)
+        self.trust_manager.resize(config.num_nodes)
+        self.node_monitor = NodeMonitor()
+        self.gradient_verifier = GradientVerifier(clip_norm=config.clip_norm)
+        self.attack_detector = AttackDetector()
+        self.parameter_monitor = ParameterMonitor()
+        self.metrics_collector = MetricsCollector()
+        self.attacker = attacker
+        self.planner = ReassignmentPlanner(self.trust_manager, max_attempts=config.max_reassignment_attempts)
+
+        self.node_configs: Dict[int, NodeConfig] = {}
+        self.model_partitions: Dict[int, nn.Module] = {}      # stage id -> module
+        self.optimizers: Dict[int, torch.optim.Optimizer] = {}
+        self.schedulers: Dict[int, Any] = {}
+        self.stage_map: Optional[StageMap] = None
+        self.stage_costs: List[float] = []
+        self.model: Optional[nn.Module] = model
+        self.attack_history: List[Dict] = []
+        self.reassignment_history: List[Dict] = []
+        self._rank, self._world = 0, 1
+        self._backend_impl = None                               # multi-process strategy object
+        self._last_step_info: Dict[str, Any] = {}
+        logger.info("Initialized DistributedTrainer with %d nodes (%s parallel)", config.num_nodes, config.parallelism)
+
+    # ------------------------------------------------------------------ setup
+    def setup_distributed_environment(self, rank: int, world_size: int, backend: Optional[str] = None,
+                                      master_addr: str = "127.0.0.1", master_port: int = 12355) -> None:
+        """Reference :99-114 (NCCL, port 12355).  gloo is selected automatically without a GPU;
+        the rendezvous address is 127.0.0.1 because container hostnames may not resolve."""
+        os.environ.setdefault("MASTER_ADDR", master_addr)
+        os.environ.setdefault("MASTER_PORT", str(master_port))
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if not dist.is_initialized():
+            dist.init_process_group(backend=backend, rank=rank, world_size=world_size)
+        if backend == "nccl":
+            torch.cuda.set_device(rank % torch.cuda.device_count())
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self._rank, self._world = rank, world_size
+        logger.info("Initialized distributed environment: rank %d/%d (%s)", rank, world_size, backend)
+
+    def _build_model(self) -> nn.Module:
+        if self.model is None:
+            torch.manual_seed(self.config.seed)
+            self.model = ModelFactory().create_model(self.config.model_name, self.config.model_size,
+                                                     **self.config.model_kwargs)
+        return self.model
+
+    def create_model_partitions(self, model_name: Optional[str] = None) -> Dict[int, nn.Module]:
+        """Balanced contiguous stages, one per node (reference :116-146; Q3/Q4 fixed)."""
+        if model_name is not None and model_name != self.config.model_name:
+            self.config.model_name, self.model = model_name, None
+        model = self._build_model()
+        stages = build_stages(model, self.config.num_nodes)
+        self.stage_costs = [sum(unit_cost(u) for u in st) for st in stages]
+        return {i: st for i, st in enumerate(stages)}
+
+    def _make_optimizer(self, params: Iterable[nn.Parameter]) -> torch.optim.Optimizer:
+        params = [p for p in params if p.requires_grad]
+        c = self.config
+        if c.optimizer == "sgd":
+            return torch.optim.SGD(params, lr=c.learning_rate, momentum=0.9, weight_decay=c.weight_decay)
+        if c.optimizer == "adam":
+            return torch.optim.Adam(params, lr=c.learning_rate)
+        return torch.optim.AdamW(params, lr=c.learning_rate, weight_decay=c.weight_decay)
+
+    def _make_scheduler(self, opt):
+        c = self.config
+        if c.lr_schedule == "cosine":
+            return torch.optim.lr_scheduler.CosineAnnealingLR(opt, T_max=max(1, c.num_epochs))
+        if c.lr_schedule == "step":
+            return torch.optim.lr_scheduler.StepLR(opt, step_size=max(1, c.num_epochs // 3), gamma=0.1)
+        return torch.optim.lr_scheduler.LambdaLR(opt, lambda e: 1.0)
+
+    def setup(self) -> "DistributedTrainer":
+        """Build model, stages, optimizers, schedulers, node table (the reference never does, Q5)."""
+        if self.model_partitions or self._backend_impl is not None:
+            return self
+        c = self.config
+        if self._world > 1 or c.parallelism in ("data", "tensor"):
+            from ..parallel import make_strategy
+            self._backend_impl = make_strategy(self)
+            self._backend_impl.setup()
+        else:
+            parts = self.create_model_partitions()
+            seen = set()
+            for sid, st in parts.items():
+                st.to(self.device)
+                self.model_partitions[sid] = st
+                own = [p for p in st.parameters() if id(p) not in seen]   # tied weights belong to the first stage
+                seen.update(id(p) for p in own)
+                if own:
+                    self.optimizers[sid] = self._make_optimizer(own)
+                    self.schedulers[sid] = self._make_scheduler(self.optimizers[sid])
+            self.stage_map = StageMap(len(parts), c.num_nodes)
+        gpu = self.device.index if self.device.type == "cuda" else -1
+        for n in range(c.num_nodes):
+            self.node_configs[n] = NodeConfig(node_id=n, rank=n if self._world > 1 else 0,
+                                              world_size=max(self._world, 1), gpu_id=gpu or 0,
+                                              model_partition=f"partition_{n}")
+        return self
+
+    # ----------------------------------------------------------- forward/backward
+    def _autocast(self):
+        if self.device.type == "cuda" and self.config.dtype == "bf16":
+            return torch.autocast("cuda", dtype=torch.bfloat16)
+        import contextlib
+        return contextlib.nullcontext()
+
+    def forward_pass(self, inputs: torch.Tensor, node_sequence: Optional[Sequence[int]] = None
+                     ) -> Tuple[torch.Tensor, Dict[int, torch.Tensor]]:
+        """Stage loop (reference :148-175).  Returns ``(output, node_outputs)`` (Q2).  Stages run
+        in order on whichever node currently owns them; detection runs on every stage output."""
+        self.setup()
+        x = inputs.to(self.device, non_blocking=True)
+        node_outputs: Dict[int, torch.Tensor] = {}
+        pending: List[Tuple[int, Any]] = []
+        allowed = None if node_sequence is None else set(node_sequence)
+        with self._autocast():
+            for sid in range(len(self.model_partitions)):
+                node = self.stage_map.owner[sid]
+                if allowed is not None and node not in allowed:
+                    continue
+                x = self.model_partitions[sid](x)
+                if self.attacker is not None:
+                    x = self.attacker.poison_output(node, x, self.global_step)
+                node_outputs[node] = x.detach()
+                if self.config.attack_detection_enabled:
+                    if self.config.deferred_detection and x.is_cuda:
+                        from ..ops.stats import tensor_statistics_device
+                        pending.append((node, tensor_statistics_device(x)))
+                    else:
+                        res = self.attack_detector.analyze_output(x, node, self.global_step)
+                        self._note_output_stats(node, self.attack_detector.output_history[node].view()[-1])
+                        if res.is_attack:
+                            self.handle_detected_attack(node, x, result=res)
+        if pending:                                            # one D2H copy for the whole step
+            block = torch.stack([s for _, s in pending]).cpu().numpy()
+            for (node, _), vec in zip(pending, block):
+                res = self.attack_detector.observe_stats(vec, node, self.global_step)
+                self._note_output_stats(node, vec)
+                if res.is_attack:
+                    self.handle_detected_attack(node, node_outputs[node], result=res)
+        return x, node_outputs
+
+    def _note_output_stats(self, node: int, vec: np.ndarray) -> None:
+        self._last_step_info.setdefault("out_stats", {})[node] = (float(vec[0]), float(vec[1]))
+
+    def backward_pass(self, loss: torch.Tensor, node_sequence: Optional[Sequence[int]] = None
+                      ) -> Dict[int, List[torch.Tensor]]:
+        """One autograd backward, then per-node gradient verification (reference :177-207).
+        No gradient clones are made; the lists reference ``param.grad`` directly."""
+        gradients: Dict[int, List[torch.Tensor]] = {}
+        loss.backward()
+        order = list(range(len(self.model_partitions)))
+        for sid in reversed(order):
+            node = self.stage_map.owner[sid]
+            if node_sequence is not None and node not in node_sequence:
+                continue
+            grads = [p.grad for p in self.model_partitions[sid].parameters() if p.grad is not None]
+            gradients.setdefault(node, [])
+            gradients[node] = grads + gradients[node]
+        self._last_step_info["invalid_nodes"] = set()
+        self._last_step_info["invalid_stages"] = set()
+        for node, grads in gradients.items():
+            if self.attacker is not None:
+                self.attacker.poison_gradients(node, grads, self.global_step)
+            if self.config.gradient_verification_enabled:
+                if not self.gradient_verifier.verify_gradients(grads, node, self.global_step):
+                    logger.warning("Invalid gradients detected from node %d", node)
+                    self._last_step_info["invalid_nodes"].add(node)
+                    self._last_step_info["invalid_stages"].update(self.stage_map.stages_of(node))
+                    self.handle_gradient_attack(node, grads)
+        return gradients
+
+    # ------------------------------------------------------------------ trust
+    def update_trust_scores(self, node_outputs: Dict[int, torch.Tensor],
+                            gradients: Dict[int, List[torch.Tensor]]) -> None:
+        """Reference :209-226 — every node, every step."""
+        flagged = {a["node_id"] for a in self.attack_history if a["step"] == self.global_step}
+        for node in range(self.config.num_nodes):
+            dev = self.calculate_output_deviation(node_outputs.get(node), node)
+            gc = self.calculate_gradient_consistency(gradients.get(node), node)
+            self.trust_manager.update_trust_score(node, dev, gc)
+            if node not in flagged:                              # only clean behaviour feeds expectations
+                st = self._last_step_info.get("out_stats", {}).get(node)
+                if st is not None:
+                    self.node_monitor.record_output(node, *st)
+                norms = self._last_step_info.get("grad_norms", {}).get(node)
+                if norms is not None:
+                    self.node_monitor.record_gradient_norms(node, norms)
+
+    def calculate_output_deviation(self, output: Optional[torch.Tensor], node_id: int) -> float:
+        """Reference :228-248; mean/std come from the statistics already computed this step."""
+        if output is None:
+            return 1.0
+        exp_mean = self.node_monitor.get_expected_mean(node_id)
+        exp_std = self.node_monitor.get_expected_std(node_id)
+        st = self._last_step_info.get("out_stats", {}).get(node_id)
+        if st is None:
+            from ..ops.stats import mean_std
+            st = mean_std(output, unbiased=False)
+            self._note_output_stats(node_id, np.array([st[0], st[1]]))
+        if exp_mean is None or exp_std is None:
+            return 0.0
+        mean_dev = abs(st[0] - exp_mean) / exp_std
+        std_dev = abs(st[1] - exp_std) / exp_std
+        return float(min(1.0, (mean_dev + std_dev) / 2.0))
+
+    def calculate_gradient_consistency(self, gradients: Optional[List[torch.Tensor]], node_id: int) -> float:
+        """Reference :250-271 (Q15: only shrunken norms lower the score) with a single
+        multi-tensor norm launch instead of one sync per parameter."""
+        if not gradients:
+            return 0.0
+        from ..ops.multi_tensor import per_tensor_l2norms
+        groups: Dict[torch.dtype, List[int]] = {}
+        for i, g in enumerate(gradients):
+            groups.setdefault(g.dtype, []).append(i)
+        norms = np.zeros(len(gradients))
+        for idxs in groups.values():
+            vals = per_tensor_l2norms([gradients[i] for i in idxs]).detach().cpu().numpy()
+            norms[idxs] = vals
+        self._last_step_info.setdefault("grad_norms", {})[node_id] = norms
+        expected = self.node_monitor.get_expected_gradient_norms(node_id)
+        if not expected or len(expected) != len(norms):
+            return 1.0
+        exp = np.asarray(expected)
+        ok = exp > 0
+        if not ok.any():
+            return 1.0
+        return float(np.mean(np.minimum(1.0, norms[ok] / exp[ok])))
+
+    # ---------------------------------------------------------- attack handling
+    def handle_detected_attack(self, node_id: int, output: Optional[torch.Tensor], result=None) -> None:
+        """Reference :273-299."""
+        logger.error("Attack detected on node %d", node_id)
+        st = self._last_step_info.get("out_stats", {}).get(node_id, (None, None))
+        hist = self.attack_detector.output_history.get(node_id)
+        vec = hist.view()[-1] if hist is not None and len(hist) else None
+        info = {"node_id": node_id, "timestamp": time.time(), "step": self.global_step,
+                "attack_type": "output_anomaly",
+                "output_stats": {"mean": st[0], "std": st[1],
+                                 "max": float(vec[3]) if vec is not None else None,
+                                 "min": float(vec[2]) if vec is not None else None}}
+        if result is not None:
+            info["classified_as"] = result.attack_type.value if result.attack_type else None
+            info["confidence"] = result.confidence
+        self.attack_history.append(info)
+        self.metrics_collector.record_event("attack", node_id=node_id, type="output_anomaly", step=self.global_step)
+        self.trust_manager.mark_compromised(node_id, "output_anomaly")
+        self.reassign_node_tasks(node_id)
+        self.training_state = TrainingState.UNDER_ATTACK
+
+    def handle_gradient_attack(self, node_id: int, gradients: List[torch.Tensor]) -> None:
+        """Reference :301-322 (also flips the training state, which the reference forgets)."""
+        logger.error("Gradient attack detected on node %d", node_id)
+        self.attack_history.append({
+            "node_id": node_id, "timestamp": time.time(), "step": self.global_step,
+            "attack_type": "gradient_poisoning",
+            "gradient_stats": {"total_norm": self.gradient_verifier.last_norm.get(node_id),
+                               "num_gradients": len(gradients)}})
+        self.metrics_collector.record_event("attack", node_id=node_id, type="gradient_poisoning", step=self.global_step)
+        self.trust_manager.mark_compromised(node_id, "gradient_poisoning")
+        self.reassign_node_tasks(node_id)
+        self.training_state = TrainingState.UNDER_ATTACK
+
+    def reassign_node_tasks(self, compromised_node_id: int) -> Optional[int]:
+        """Reference :324-352, load-aware (Q6) and bounded by ``max_reassignment_attempts``."""
+        if self._backend_impl is not None:
+            return self._backend_impl.reassign(compromised_node_id)
+        if self.stage_map is None or not self.stage_map.stages_of(compromised_node_id):
+            return None
+        if not self.planner.allowed(compromised_node_id):
+            logger.error("node %d exhausted its %d reassignment attempts", compromised_node_id,
+                         self.config.max_reassignment_attempts)
+            return None
+        loads = [self.stage_map.load(n, self.stage_costs) for n in range(self.config.num_nodes)]
+        best = self.planner.choose_target(compromised_node_id, loads)
+        if best is None:
+            logger.error("No trusted nodes available for reassignment")
+            return None
+        self.planner.note_attempt(compromised_node_id)
+        t0 = time.perf_counter()
+        migration_time = self.estimate_migration_time(compromised_node_id, best)
+        moved = self.perform_task_reassignment(compromised_node_id, best)
+        self.reassignment_history.append({
+            "from_node": compromised_node_id, "to_node": best, "timestamp": time.time(),
+            "migration_time": migration_time, "measured_time": time.perf_counter() - t0,
+            "stages": moved, "step": self.global_step})
+        self.metrics_collector.record_event("reassignment", from_node=compromised_node_id, to_node=best,
+                                            step=self.global_step)
+        return best
+
+    def estimate_migration_time(self, source_node: int, target_node: int) -> float:
+        numel = sum(p.numel() for s in self.stage_map.stages_of(source_node)
+                    for p in self.model_partitions[s].parameters())
+        return estimate_migration_time(numel, 4, self.config.migration_model)
+
+    def perform_task_reassignment(self, source_node: int, target_node: int) -> List[int]:
+        """Move every stage of ``source_node`` to ``target_node`` (reference :367-380)."""
+        moved = self.stage_map.move_all(source_node, target_node)
+        names = "+".join(f"partition_{s}" for s in self.stage_map.stages_of(target_node))
+        if target_node in self.node_configs:
+            self.node_configs[target_node].model_partition = names
+        if source_node in self.node_configs:
+            self.node_configs[source_node].model_partition = ""
+        # detector/monitor baselines of the target no longer describe what it computes
+        self.attack_detector.reset_node_history(target_node)
+        self.node_monitor.reset_node(target_node)
+        self.gradient_verifier.reset_node(target_node)
+        logger.info("Task reassignment completed: %d -> %d (stages %s)", source_node, target_node, moved)
+        return moved
+
+    # ------------------------------------------------------------------- steps
+    def calculate_loss(self, outputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        """Cross entropy (reference :435-439); LM logits ``[B,T,V]`` are flattened."""
+        targets = targets.to(outputs.device, non_blocking=True)
+        if outputs.dim() == 3:
+            return nn.functional.cross_entropy(outputs.reshape(-1, outputs.shape[-1]).float(), targets.reshape(-1))
+        return nn.functional.cross_entropy(outputs.float(), targets)
+
+    def optimizer_step(self, gradients: Dict[int, List[torch.Tensor]]) -> None:
+        """Per-stage optimizer step (reference :441-446); poisoned gradients are dropped."""
+        invalid = self._last_step_info.get("invalid_stages", set())
+        for sid, opt in self.optimizers.items():
+            if sid in invalid:
+                opt.zero_grad(set_to_none=True)
+                continue
+            if self.config.clip_norm > 0:
+                nn.utils.clip_grad_norm_(self.model_partitions[sid].parameters(), self.config.clip_norm)
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+
+    def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
+        """One full step (the body of the reference's hot loop, :391-418)."""
+        self.setup()
+        self.global_step += 1
+        self._last_step_info = {}
+        if self._backend_impl is not None:
+            return self._backend_impl.train_step(batch)
+        t0 = time.perf_counter()
+        if self.attacker is not None and self.config.parameter_monitoring_enabled:
+            for sid, part in self.model_partitions.items():
+                self.attacker.poison_parameters(self.stage_map.owner[sid], list(part.parameters()), self.global_step)
+        if self.config.parameter_monitoring_enabled:
+            for sid, part in self.model_partitions.items():
+                node = self.stage_map.owner[sid]
+                if self.parameter_monitor.detect_parameter_poisoning(sid, part.parameters(), self.global_step):
+                    self.attack_history.append({"node_id": node, "timestamp": time.time(), "step": self.global_step,
+                                                "attack_type": "model_poisoning"})
+                    self.trust_manager.mark_compromised(node, "model_poisoning")
+                    self.reassign_node_tasks(node)
+                    self.training_state = TrainingState.UNDER_ATTACK
+        outputs, node_outputs = self.forward_pass(batch["input"])
+        loss = self.calculate_loss(outputs, batch["target"])
+        gradients = self.backward_pass(loss)
+        self.update_trust_scores(node_outputs, gradients)
+        self.optimizer_step(gradients)
+        loss_val = float(loss.item())
+        n = batch["input"].shape[0] * (batch["input"].shape[1] if batch["input"].dim() == 2 else 1)
+        self.metrics_collector.collect_batch_metrics({
+            "loss": loss_val, "step": self.global_step, "epoch": self.current_epoch,
+            "trust_scores": {i: self.trust_manager.get_trust_score(i) for i in range(self.config.num_nodes)},
+            "step_time": time.perf_counter() - t0, "samples": n})
+        return loss_val
+
+    def train_epoch(self, dataloader, epoch: int) -> float:
+        self.current_epoch = epoch
+        total, count = 0.0, 0
+        for batch_idx, batch in enumerate(dataloader):
+            if self.config.steps_per_epoch is not None and batch_idx >= self.config.steps_per_epoch:
+                break
+            if self.attacker is not None and self.attacker.is_active():
+                batch = self.attacker.apply_attacks(batch, self.global_step + 1)
+            loss = self.train_step(batch)
+            total += loss
+            count += 1
+            if self.config.checkpoint_interval and self.global_step % self.config.checkpoint_interval == 0:
+                self.save_checkpoint()
+            if batch_idx % max(1, self.config.log_interval) == 0:
+                logger.info("Epoch %d, Batch %d, Loss: %.4f", epoch, batch_idx, loss)
+        avg = total / max(1, count)
+        logger.info("Epoch %d completed. Average loss: %.4f", epoch, avg)
+        return avg
+
+    def train(self, train_dataloader=None, val_dataloader=None, num_epochs: Optional[int] = None, *,
+              dataset: Optional[str] = None, epochs: Optional[int] = None,
+              trust_manager: Optional[TrustManager] = None) -> Dict[str, Any]:
+        """Main loop (reference :465-492).  Also accepts the README form
+        ``train(dataset='openwebtext', epochs=10, trust_manager=tm)`` (README.md:78-82)."""
+        if trust_manager is not None:
+            trust_manager.resize(self.config.num_nodes)
+            trust_manager.trust_threshold = self.config.trust_threshold if trust_manager.trust_threshold is None \
+                else trust_manager.trust_threshold
+            self.trust_manager = trust_manager
+            self.planner.trust_manager = trust_manager
+        if isinstance(train_dataloader, str):
+            dataset, train_dataloader = train_dataloader, None
+        if train_dataloader is None:
+            from ..utils.data_loader import get_dataloader
+            name = dataset or self.config.dataset_name
+            kw = {"seq_len": self.config.seq_len} if self.config.seq_len else {}
+            train_dataloader = get_dataloader(name, "train", self.config.batch_size, **kw)
+            if val_dataloader is None:
+                val_dataloader = get_dataloader(name, "validation", self.config.batch_size, **kw)
+        num_epochs = epochs if epochs is not None else (num_epochs if num_epochs is not None else self.config.num_epochs)
+        self.setup()
+        logger.info("Starting training for %d epochs", num_epochs)
+        self.training_state = TrainingState.TRAINING
+        history = []
+        for epoch in range(num_epochs):
+            avg = self.train_epoch(train_dataloader, epoch)
+            rec = {"epoch": epoch, "train_loss": avg}
+            if val_dataloader is not None:
+                rec["val_loss"] = self.validate(val_dataloader)
+                logger.info("Validation loss: %.4f", rec["val_loss"])
+            if self.training_state == TrainingState.UNDER_ATTACK:
+                logger.info("Training under attack - implementing recovery measures")
+                self.training_state = TrainingState.RECOVERING
+                for n in self.trust_manager.get_compromised_nodes():
+                    self.trust_manager.initiate_recovery(n)
+            for sch in self.schedulers.values():
+                sch.step()
+            history.append(rec)
+        self.training_state = TrainingState.COMPLETED
+        logger.info("Training completed successfully")
+        return {"history": history, **self.get_training_stats()}
+
+    @torch.no_grad()
+    def validate(self, val_dataloader) -> float:
+        self.setup()
+        if self._backend_impl is not None:
+            return self._backend_impl.validate(val_dataloader)
+        total, count = 0.0, 0
+        was = self.config.attack_detection_enabled
+        self.config.attack_detection_enabled = False          # validation batches must not move baselines
+        try:
+            for part in self.model_partitions.values():
+                part.eval()
+            for batch in val_dataloader:
+                outputs, _ = self.forward_pass(batch["input"])
+                total += float(self.calculate_loss(outputs, batch["target"]).item())
+                count += 1
+        finally:
+            self.config.attack_detection_enabled = was
+            for part in self.model_partitions.values():
+                part.train()
+        return total / max(1, count)
+
+    # ------------------------------------------------------------- persistence
+    def save_checkpoint(self, directory: Optional[str] = None) -> str:
+        path = _ckpt.save_checkpoint(self, directory, rank=self._rank if self._world > 1 else None)
+        logger.info("Checkpoint saved: %s", path)
+        return path
+
+    def load_checkpoint(self, path: Optional[str] = None) -> Dict[str, Any]:
+        self.setup()
+        if path is None:
+            path = _ckpt.latest_checkpoint(self.config.checkpoint_dir, self._rank if self._world > 1 else None)
+            if path is None:
+                raise FileNotFoundError(f"no checkpoint in {self.config.checkpoint_dir}")
+        return _ckpt.load_checkpoint(self, path)
+
+    def get_training_stats(self) -> Dict[str, Any]:
+        return {"current_epoch": self.current_epoch, "global_step": self.global_step,
+                "training_state": self.training_state.value,
+                "trust_scores": {i: self.trust_manager.get_trust_score(i) for i in range(self.config.num_nodes)},
+                "attack_count": len(self.attack_history), "reassignment_count": len(self.reassignment_history),
+                "metrics": self.metrics_collector.get_summary()}
+
+    def cleanup(self) -> None:
+        if self._backend_impl is not None:
+            self._backend_impl.cleanup()
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+        logger.info("Distributed training cleanup completed")

@@ -1,0 +1,106 @@
+"""Process-group plumbing: NCCL on GPUs, gloo on CPU, rendezvous
+on 127.0.0.1; typed p2p send/recv with a small shape header so stages can exchange activations
+whose shapes they have never seen; replicated-decision helper (all-gather of small float vectors).
+The reference only ever calls ``init_process_group('nccl')`` and ``destroy_process_group``
+(distributed_trainer.py:99-114,523-527) and moves no data."""
+from __future__ import annotations
+
+import os
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["init_process_group", "rank", "world_size", "send_tensor", "recv_tensor", "isend_tensor",
+           "all_gather_vector", "broadcast_float", "is_gloo"]
+
+_DTYPES = [torch.float32, torch.bfloat16, torch.float16, torch.int64, torch.int32, torch.float64, torch.uint8, torch.bool]
+
+
+def init_process_group(backend: Optional[str] = None, rank_: Optional[int] = None, world: Optional[int] = None,
+                       master_addr: str = "127.0.0.1", master_port: int = 12355) -> Tuple[int, int]:
+    if dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    os.environ.setdefault("MASTER_ADDR", master_addr)
+    os.environ.setdefault("MASTER_PORT", str(master_port))
+    rank_ = int(os.environ.get("RANK", 0)) if rank_ is None else rank_
+    world = int(os.environ.get("WORLD_SIZE", 1)) if world is None else world
+    backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
+    if backend == "nccl":
+        local = int(os.environ.get("LOCAL_RANK", rank_ % max(1, torch.cuda.device_count())))
+        torch.cuda.set_device(local)
+        dist.init_process_group(backend, rank=rank_, world_size=world,
+                                device_id=torch.device("cuda", local))
+    else:
+        dist.init_process_group(backend, rank=rank_, world_size=world)
+    return rank_, world
+
+
+def rank() -> int:
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def world_size() -> int:
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def is_gloo() -> bool:
+    return dist.is_initialized() and dist.get_backend() == "gloo"
+
+
+def _comm_device(t: torch.Tensor) -> torch.device:
+    return torch.device("cpu") if is_gloo() else t.device
+
+
+def _header(t: torch.Tensor) -> torch.Tensor:
+    h = torch.full((8,), -1, dtype=torch.int64)
+    h[0] = _DTYPES.index(t.dtype)
+    h[1] = t.dim()
+    for i, s in enumerate(t.shape):
+        h[2 + i] = s
+    return h
+
+
+def isend_tensor(t: torch.Tensor, dst: int, tag: int = 0) -> List:
+    """Non-blocking typed send; returns work handles (keep the tensor alive until waited)."""
+    dev = _comm_device(t)
+    payload = t.detach().contiguous().to(dev)
+    hdr = _header(t).to(dev)
+    return [dist.isend(hdr, dst, tag=tag), dist.isend(payload, dst, tag=tag), payload, hdr]
+
+
+def send_tensor(t: torch.Tensor, dst: int, tag: int = 0) -> None:
+    for w in isend_tensor(t, dst, tag)[:2]:
+        w.wait()
+
+
+def recv_tensor(src: int, device: torch.device, tag: int = 0) -> torch.Tensor:
+    dev = torch.device("cpu") if is_gloo() else device
+    hdr = torch.empty(8, dtype=torch.int64, device=dev)
+    dist.recv(hdr, src, tag=tag)
+    h = hdr.cpu().tolist()
+    shape = [int(s) for s in h[2:2 + int(h[1])]]
+    buf = torch.empty(shape, dtype=_DTYPES[int(h[0])], device=dev)
+    dist.recv(buf, src, tag=tag)
+    return buf.to(device)
+
+
+def all_gather_vector(v: torch.Tensor) -> torch.Tensor:
+    """[W, len(v)] float64 gather of a small per-rank vector (decision inputs)."""
+    W = world_size()
+    if W == 1:
+        return v.reshape(1, -1).double().cpu()
+    dev = torch.device("cpu") if is_gloo() else torch.device("cuda", torch.cuda.current_device())
+    x = v.detach().double().reshape(-1).to(dev)
+    out = torch.empty(W * x.numel(), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(out, x)
+    return out.reshape(W, -1).cpu()
+
+
+def broadcast_float(value: float, src: int) -> float:
+    if world_size() == 1:
+        return value
+    dev = torch.device("cpu") if is_gloo() else torch.device("cuda", torch.cuda.current_device())
+    t = torch.tensor([value], dtype=torch.float64, device=dev)
+    dist.broadcast(t, src)
+    return float(t.item())

@@ -1,0 +1,213 @@
+"""Data parallelism with the fused trust-weighted all-reduce (BASELINE config 3 and the headline
+GPT-2-medium metric).  The reference imports DDP and never uses it (distributed_trainer.py:9,
+SURVEY 2.4).
+
+Every rank is a trust "node" holding a full replica.  Gradients are written straight into one
+flat bucket (``param.grad`` are views, no pack copy on the eager path); the bucket is aggregated
+by :class:`TrustAllReduce`; the statistics it emits feed the verifier and the trust state machine
+identically on every rank, so decisions are replicated without extra traffic.  A rank that is
+COMPROMISED gets coefficient 0 and its data shard is handed to the most trusted, least loaded
+rank (the DP form of "task reassignment").
+
+On a B200 with a GPT-2 model the replica is executed by the fused engine
+(:mod:`trustworthy_dl.engine.gpt2_engine`) instead of eager autograd.
+"""
+from __future__ import annotations
+
+import logging
+import time
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ..core.partition import StageMap
+from . import comm
+from .trust_allreduce import TrustAllReduce
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["DataParallelStrategy", "flatten_grads_into"]
+
+
+def flatten_grads_into(params: List[nn.Parameter], dtype: torch.dtype, device: torch.device,
+                       buffer: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Make every ``p.grad`` a view into one flat buffer (allocated here unless given)."""
+    total = sum(p.numel() for p in params)
+    if buffer is None:
+        buffer = torch.zeros(total, dtype=dtype, device=device)
+    off = 0
+    for p in params:
+        n = p.numel()
+        p.grad = buffer[off:off + n].view_as(p)
+        off += n
+    return buffer
+
+
+class DataParallelStrategy:
+    def __init__(self, trainer):
+        self.t = trainer
+        self.rank, self.world = comm.rank(), comm.world_size()
+        self.device = trainer.device
+        self.engine = None
+        self._sec_s = 0.0
+        self._step_s = 0.0
+
+    def setup(self) -> None:
+        t, c = self.t, self.t.config
+        if c.num_nodes != self.world:
+            c.num_nodes = self.world
+            t.trust_manager.resize(self.world)
+        model = t._build_model().to(self.device)
+        t.model_partitions[0] = model
+        use_fused = c.engine == "fused" or (c.engine == "auto" and self.device.type == "cuda"
+                                            and c.model_name.startswith("gpt2") and c.dtype == "bf16")
+        if use_fused:
+            from ..engine.gpt2_engine import GPT2Engine
+            self.engine = GPT2Engine.from_module(model, batch_size=max(1, c.batch_size // self.world),
+                                                 seq_len=c.seq_len or model.config.n_positions,
+                                                 lr=c.learning_rate, weight_decay=c.weight_decay,
+                                                 world=self.world, rank=self.rank)
+            self.reducer = self.engine.reducer
+        else:
+            self.params = [p for p in model.parameters() if p.requires_grad]
+            gdtype = torch.float32
+            self.reducer = TrustAllReduce(sum(p.numel() for p in self.params), gdtype, self.device)
+            flatten_grads_into(self.params, gdtype, self.device, self.reducer.buffer)
+            t.optimizers[0] = t._make_optimizer(self.params)
+            t.schedulers[0] = t._make_scheduler(t.optimizers[0])
+        # data shards play the role of stages: shard i starts on rank i
+        t.stage_map = StageMap(self.world, self.world)
+        t.stage_costs = [1.0] * self.world
+
+    # ------------------------------------------------------------------ step
+    def _local_batch(self, batch: Dict[str, torch.Tensor]) -> Optional[Dict[str, torch.Tensor]]:
+        shards = self.t.stage_map.stages_of(self.rank)
+        if not shards:
+            return None
+        xs, ys = batch["input"].chunk(self.world), batch["target"].chunk(self.world)
+        return {"input": torch.cat([xs[s] for s in shards]), "target": torch.cat([ys[s] for s in shards])}
+
+    def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
+        t, c = self.t, self.t.config
+        t0 = time.perf_counter()
+        step = t.global_step
+        if self.engine is not None:
+            return self._engine_step(batch, t0)
+        model = t.model_partitions[0]
+        local = self._local_batch(batch)
+        self.reducer.buffer.zero_()
+        loss_val, n_local = 0.0, 0
+        out_stats = None
+        if local is not None:
+            with t._autocast():
+                out = model(local["input"].to(self.device))
+            if t.attacker is not None:
+                out = t.attacker.poison_output(self.rank, out, step)
+            loss = t.calculate_loss(out, local["target"])
+            flatten_grads_into(self.params, self.reducer.buffer.dtype, self.device, self.reducer.buffer)
+            loss.backward()
+            loss_val, n_local = float(loss.item()), local["input"].shape[0]
+            if c.attack_detection_enabled:
+                from ..ops.stats import tensor_statistics
+                out_stats = tensor_statistics(out.detach()).cpu()
+        if t.attacker is not None:
+            t.attacker.poison_gradients(self.rank, [self.reducer.buffer], step)
+        ts = time.perf_counter()
+        weights = torch.from_numpy(t.trust_manager.aggregation_weights()).float()
+        stats, coeff = self.reducer.reduce_(weights)
+        stats = stats.detach().cpu().double().numpy()
+        # ---- replicated security decisions -----------------------------------------
+        vec = torch.cat([out_stats if out_stats is not None else torch.zeros(12, dtype=torch.float64),
+                         torch.tensor([1.0 if out_stats is not None else 0.0, loss_val, float(n_local)],
+                                      dtype=torch.float64)])
+        table = comm.all_gather_vector(vec).numpy()
+        t._last_step_info = {"out_stats": {}, "invalid_nodes": set(), "grad_norms": {}}
+        for node in range(self.world):
+            if table[node, 12] > 0:
+                t._last_step_info["out_stats"][node] = (float(table[node, 0]), float(table[node, 1]))
+                if c.attack_detection_enabled:
+                    res = t.attack_detector.observe_stats(table[node, :12], node, step)
+                    if res.is_attack:
+                        t.handle_detected_attack(node, None, result=res)
+        if c.gradient_verification_enabled:
+            ok = t.gradient_verifier.verify_rank_stats(stats[:, 0], stats[:, 1], float(stats[0, 2]), step)
+            for node in np.nonzero(~ok)[0]:
+                node = int(node)
+                if t.trust_manager.get_node_status(node).value != "compromised":
+                    t._last_step_info["invalid_nodes"].add(node)
+                    t.handle_gradient_attack(node, [])
+        flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
+        cos = stats[:, 3]
+        for node in range(self.world):
+            st = t._last_step_info["out_stats"].get(node)
+            dev = 1.0 if st is None else self._deviation(node, st)
+            gc = float(np.clip(cos[node], 0.0, 1.0)) if self.world >= 3 else \
+                (0.0 if node in t._last_step_info["invalid_nodes"] else 1.0)
+            t.trust_manager.update_trust_score(node, dev, gc)
+            if st is not None and node not in flagged:
+                t.node_monitor.record_output(node, *st)
+        self._sec_s += time.perf_counter() - ts
+        # ---- optimizer on the aggregated gradient ------------------------------------
+        opt = t.optimizers[0]
+        if c.clip_norm > 0:
+            nn.utils.clip_grad_norm_(self.params, c.clip_norm)
+        opt.step()
+        tot_n = table[:, 14].sum()
+        loss = float((table[:, 13] * table[:, 14]).sum() / max(1.0, tot_n))
+        self._step_s += time.perf_counter() - t0
+        t.metrics_collector.collect_batch_metrics({
+            "loss": loss, "step": step, "epoch": t.current_epoch,
+            "trust_scores": {i: t.trust_manager.get_trust_score(i) for i in range(self.world)},
+            "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        return loss
+
+    def _engine_step(self, batch, t0) -> float:
+        t = self.t
+        local = self._local_batch(batch)
+        loss = self.engine.train_step(local["input"], local["target"], trust_manager=t.trust_manager,
+                                      attacker=t.attacker, step=t.global_step, trainer=t)
+        self._step_s += time.perf_counter() - t0
+        return loss
+
+    def _deviation(self, node: int, st) -> float:
+        em, es = self.t.node_monitor.get_expected_mean(node), self.t.node_monitor.get_expected_std(node)
+        if em is None or es is None:
+            return 0.0
+        return float(min(1.0, (abs(st[0] - em) / es + abs(st[1] - es) / es) / 2.0))
+
+    def reassign(self, src: int) -> Optional[int]:
+        """Hand the compromised rank's data shard(s) to the best trusted rank."""
+        t = self.t
+        moved = t.stage_map.stages_of(src)
+        if not moved or not t.planner.allowed(src):
+            return None
+        loads = [float(len(t.stage_map.stages_of(n))) for n in range(self.world)]
+        dst = t.planner.choose_target(src, loads)
+        if dst is None:
+            return None
+        t.planner.note_attempt(src)
+        t.stage_map.move_all(src, dst)
+        t.reassignment_history.append({"from_node": src, "to_node": dst, "timestamp": time.time(),
+                                       "step": t.global_step, "stages": moved, "migration_time": 0.0,
+                                       "kind": "data_shard"})
+        return dst
+
+    @torch.no_grad()
+    def validate(self, loader) -> float:
+        model = self.t.model_partitions[0]
+        model.eval()
+        total, n = 0.0, 0
+        for batch in loader:
+            out = model(batch["input"].to(self.device))
+            total += float(self.t.calculate_loss(out, batch["target"]).item())
+            n += 1
+        model.train()
+        return total / max(1, n)
+
+    def comm_fraction(self) -> float:
+        return self._sec_s / self._step_s if self._step_s > 0 else 0.0
+
+    def cleanup(self) -> None:
+        pass

@@ -1,0 +1,346 @@
+"""Inter-layer model parallelism across processes: ``parallelism: model`` (one micro-batch, the
+reference's stage-after-stage flow) and ``parallelism: pipeline`` (micro-batched 1F1B).
+
+The reference walks its stages in a python loop inside one process and sends nothing
+(distributed_trainer.py:153-173).  Here each rank is a node owning one or more
+stages; activations and activation-gradients move with NCCL / gloo p2p (row C1 of the SURVEY
+work-list keeps PP traffic on NCCL by design); sends are non-blocking so they overlap the next
+compute op.
+
+Scheduling is data driven: a global topological order of ``(F|B, stage, micro-batch)`` ops is
+generated once (GPipe order or a simulated 1F1B order) and each rank executes the ops of the
+stages it owns.  Because the order is topological and sends never block, any stage->rank map is
+deadlock free — which is what lets stages move between ranks (trust-driven reassignment) without
+a restart.
+
+Security is receiver-side: the rank that *consumes* an activation computes its statistics, so a
+compromised sender cannot vouch for itself.  All ranks then all-gather the tiny per-stage
+statistic vectors and per-node gradient norms and run the same detector / verifier / trust state
+machine, i.e. decisions are replicated and deterministic.
+"""
+from __future__ import annotations
+
+import logging
+import time
+from typing import Any, Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..core.partition import StageMap
+from ..ops.reference_impl import NUM_STATS
+from ..ops.stats import tensor_statistics
+from . import comm
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["PipelineStrategy", "make_schedule"]
+
+
+def make_schedule(num_stages: int, micro_batches: int, kind: str = "1f1b") -> List[Tuple[str, int, int]]:
+    """Global topological order of ops.  ``gpipe``: all forwards then all backwards.
+    ``1f1b``: per-stage warm-up / steady 1F1B / cool-down sequences merged by simulation."""
+    S, M = num_stages, micro_batches
+    if kind == "gpipe" or M == 1:
+        fwd = [("F", s, m) for m in range(M) for s in range(S)]
+        bwd = [("B", s, m) for m in range(M) for s in reversed(range(S))]
+        return fwd + bwd
+    per_stage: List[List[Tuple[str, int]]] = []
+    for s in range(S):
+        warm = min(S - s - 1, M)
+        ops: List[Tuple[str, int]] = [("F", m) for m in range(warm)]
+        f, b = warm, 0
+        while f < M:
+            ops.append(("F", f)); f += 1
+            ops.append(("B", b)); b += 1
+        while b < M:
+            ops.append(("B", b)); b += 1
+        per_stage.append(ops)
+    done_f, done_b = set(), set()
+    ptr = [0] * S
+    order: List[Tuple[str, int, int]] = []
+    total = sum(len(o) for o in per_stage)
+    while len(order) < total:
+        progressed = False
+        for s in range(S):
+            if ptr[s] >= len(per_stage[s]):
+                continue
+            kind_, m = per_stage[s][ptr[s]]
+            ready = (s == 0 or (s - 1, m) in done_f) if kind_ == "F" else \
+                ((s, m) in done_f and (s == S - 1 or (s + 1, m) in done_b))
+            if ready:
+                order.append((kind_, s, m))
+                (done_f if kind_ == "F" else done_b).add((s, m))
+                ptr[s] += 1
+                progressed = True
+        if not progressed:
+            raise RuntimeError("1F1B schedule simulation stalled")
+    return order
+
+
+class PipelineStrategy:
+    def __init__(self, trainer):
+        self.t = trainer
+        self.rank, self.world = comm.rank(), comm.world_size()
+        self.device = trainer.device
+        self.stages: List[nn.Module] = []
+        self._comm_s = 0.0
+        self._step_s = 0.0
+        self._grad_handoff: Dict[Tuple[int, int], torch.Tensor] = {}
+
+    # ------------------------------------------------------------------ setup
+    def setup(self) -> None:
+        t, c = self.t, self.t.config
+        if c.num_nodes != self.world:
+            logger.warning("num_nodes (%d) != world size (%d): using world size", c.num_nodes, self.world)
+            c.num_nodes = self.world
+            t.trust_manager.resize(self.world)
+        model = t._build_model()
+        if hasattr(model, "untie_head") and self.world > 1:
+            model.untie_head()
+        parts = t.create_model_partitions()
+        self.stages = [parts[i] for i in range(len(parts))]
+        t.stage_map = StageMap(len(self.stages), self.world)
+        for sid, st in enumerate(self.stages):
+            t.model_partitions[sid] = st
+            if t.stage_map.owner[sid] == self.rank:
+                self._adopt(sid)
+        kind = "1f1b" if c.parallelism == "pipeline" else "gpipe"
+        self.micro = max(1, c.micro_batches if c.parallelism == "pipeline" else 1)
+        self.schedule = make_schedule(len(self.stages), self.micro, kind)
+
+    def _adopt(self, sid: int) -> None:
+        st = self.stages[sid].to(self.device)
+        params = [p for p in st.parameters() if p.requires_grad]
+        if params and sid not in self.t.optimizers:
+            self.t.optimizers[sid] = self.t._make_optimizer(params)
+            self.t.schedulers[sid] = self.t._make_scheduler(self.t.optimizers[sid])
+
+    def _owner(self, sid: int) -> int:
+        return self.t.stage_map.owner[sid]
+
+    # ------------------------------------------------------------- one step
+    def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
+        t, c = self.t, self.t.config
+        t0 = time.perf_counter()
+        S, M = len(self.stages), self.micro
+        step = t.global_step
+        xs = batch["input"].chunk(M)
+        ys = batch["target"].chunk(M)
+        acts: Dict[Tuple[int, int], Tuple[Optional[torch.Tensor], torch.Tensor]] = {}
+        pending_sends: List = []
+        stage_stats = torch.zeros(S, NUM_STATS, dtype=torch.float64)
+        have_stats = torch.zeros(S, dtype=torch.float64)
+        losses: List[torch.Tensor] = []
+        comm_s = 0.0
+        for kind, s, m in self.schedule:
+            if self._owner(s) != self.rank:
+                continue
+            if kind == "F":
+                if s == 0:
+                    x_in = xs[m].to(self.device)
+                elif self._owner(s - 1) == self.rank:
+                    x_in = acts[(s - 1, m)][1].detach()
+                else:
+                    tc = time.perf_counter()
+                    x_in = comm.recv_tensor(self._owner(s - 1), self.device, tag=0)
+                    comm_s += time.perf_counter() - tc
+                if s > 0:
+                    # receiver-side verification of the previous stage's output
+                    if c.attack_detection_enabled and m == 0:
+                        stage_stats[s - 1] = tensor_statistics(x_in).cpu()
+                        have_stats[s - 1] = 1.0
+                    if x_in.is_floating_point():
+                        x_in.requires_grad_(True)
+                with t._autocast():
+                    out = self.stages[s](x_in)
+                if t.attacker is not None:
+                    out = t.attacker.poison_output(self.rank, out, step)
+                acts[(s, m)] = (x_in if s > 0 else None, out)
+                if s == S - 1:
+                    if c.attack_detection_enabled and m == 0:
+                        stage_stats[s] = tensor_statistics(out.detach()).cpu()
+                        have_stats[s] = 1.0
+                    losses.append(t.calculate_loss(out, ys[m]) / M)
+                elif self._owner(s + 1) != self.rank:
+                    pending_sends += comm.isend_tensor(out.detach(), self._owner(s + 1), tag=0)
+            else:
+                x_in, out = acts.pop((s, m))
+                if s == S - 1:
+                    losses[m].backward()
+                else:
+                    if self._owner(s + 1) == self.rank:
+                        g = self._grad_handoff.pop((s + 1, m))
+                    else:
+                        tc = time.perf_counter()
+                        g = comm.recv_tensor(self._owner(s + 1), self.device, tag=1)
+                        comm_s += time.perf_counter() - tc
+                    out.backward(g)
+                if s > 0 and x_in is not None and x_in.grad is not None:
+                    if self._owner(s - 1) == self.rank:
+                        self._grad_handoff[(s, m)] = x_in.grad
+                    else:
+                        pending_sends += comm.isend_tensor(x_in.grad, self._owner(s - 1), tag=1)
+        for w in pending_sends:
+            if hasattr(w, "wait"):
+                w.wait()
+        self._grad_handoff.clear()
+
+        # ---- local gradients: fault injection + norm --------------------------------
+        my_grads = [p.grad for sid in t.stage_map.stages_of(self.rank) for p in self.stages[sid].parameters()
+                    if p.grad is not None]
+        if t.attacker is not None:
+            t.attacker.poison_gradients(self.rank, my_grads, step)
+        my_norm = t.gradient_verifier.total_norm(my_grads) if my_grads else 0.0
+        loss_local = float(sum(l.detach() for l in losses).item()) if losses else 0.0
+
+        # ---- replicated decisions ---------------------------------------------------
+        vec = torch.cat([stage_stats.reshape(-1), have_stats, torch.tensor([my_norm, loss_local,
+                         1.0 if losses else 0.0], dtype=torch.float64)])
+        tc = time.perf_counter()
+        table = comm.all_gather_vector(vec).numpy()
+        comm_s += time.perf_counter() - tc
+        ss = table[:, :S * NUM_STATS].reshape(self.world, S, NUM_STATS)
+        hv = table[:, S * NUM_STATS:S * NUM_STATS + S]
+        norms = table[:, -3]
+        loss = float(table[table[:, -1] > 0, -2].sum())
+        out_stats: Dict[int, np.ndarray] = {}
+        for s in range(S):
+            src = np.nonzero(hv[:, s] > 0)[0]
+            if src.size:
+                out_stats[self._owner(s)] = ss[src[0], s]          # a node's last stage wins
+        t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
+                             "invalid_nodes": set(), "grad_norms": {}}
+        if c.attack_detection_enabled:
+            for node, v in out_stats.items():
+                res = t.attack_detector.observe_stats(v, node, step)
+                if res.is_attack:
+                    t.handle_detected_attack(node, None, result=res)
+        if c.gradient_verification_enabled:
+            for node in range(self.world):
+                if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
+                    t._last_step_info["invalid_nodes"].add(node)
+                    t.handle_gradient_attack(node, [])
+        flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
+        for node in range(self.world):
+            st = t._last_step_info["out_stats"].get(node)
+            dev = 1.0 if st is None else self._deviation(node, st)
+            gc = 0.0 if not t.stage_map.stages_of(node) and node not in flagged else \
+                (1.0 if node not in t._last_step_info["invalid_nodes"] else 0.0)
+            t.trust_manager.update_trust_score(node, dev, gc)
+            if st is not None and node not in flagged:
+                t.node_monitor.record_output(node, *st)
+
+        # ---- optimizer --------------------------------------------------------------
+        for sid in list(t.optimizers):
+            if self._owner(sid) != self.rank:
+                continue
+            opt = t.optimizers[sid]
+            if self.rank in t._last_step_info["invalid_nodes"]:
+                opt.zero_grad(set_to_none=True)
+                continue
+            if c.clip_norm > 0:
+                nn.utils.clip_grad_norm_(self.stages[sid].parameters(), c.clip_norm)
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+        self._comm_s += comm_s
+        self._step_s += time.perf_counter() - t0
+        t.metrics_collector.collect_batch_metrics({
+            "loss": loss, "step": step, "epoch": t.current_epoch,
+            "trust_scores": {i: t.trust_manager.get_trust_score(i) for i in range(self.world)},
+            "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        return loss
+
+    def _deviation(self, node: int, st) -> float:
+        em, es = self.t.node_monitor.get_expected_mean(node), self.t.node_monitor.get_expected_std(node)
+        if em is None or es is None:
+            return 0.0
+        return float(min(1.0, (abs(st[0] - em) / es + abs(st[1] - es) / es) / 2.0))
+
+    # ---------------------------------------------------------- reassignment
+    def reassign(self, src: int) -> Optional[int]:
+        """Move every stage of ``src`` to the best trusted rank: parameters and optimizer state are
+        sent p2p; all ranks update the (replicated) stage map.  No process restarts."""
+        t = self.t
+        moved = t.stage_map.stages_of(src)
+        if not moved or not t.planner.allowed(src):
+            return None
+        loads = [t.stage_map.load(n, t.stage_costs) for n in range(self.world)]
+        dst = t.planner.choose_target(src, loads)
+        if dst is None:
+            logger.error("No trusted nodes available for reassignment")
+            return None
+        t.planner.note_attempt(src)
+        t0 = time.perf_counter()
+        numel = sum(p.numel() for s in moved for p in self.stages[s].parameters())
+        for sid in moved:
+            self._migrate(sid, src, dst)
+        t.stage_map.move_all(src, dst)
+        from ..core.reassignment import estimate_migration_time
+        t.reassignment_history.append({
+            "from_node": src, "to_node": dst, "timestamp": time.time(), "step": t.global_step, "stages": moved,
+            "migration_time": estimate_migration_time(numel, 4, t.config.migration_model),
+            "measured_time": time.perf_counter() - t0})
+        for obj in (t.attack_detector, t.node_monitor, t.gradient_verifier):
+            (obj.reset_node_history if hasattr(obj, "reset_node_history") else obj.reset_node)(dst)
+        if dst in t.node_configs:
+            t.node_configs[dst].model_partition = "+".join(f"partition_{s}" for s in t.stage_map.stages_of(dst))
+        return dst
+
+    def _migrate(self, sid: int, src: int, dst: int) -> None:
+        st = self.stages[sid]
+        if self.rank == src:
+            flat = torch.cat([p.detach().reshape(-1).float() for p in st.state_dict().values()
+                              if p.is_floating_point()] or [torch.zeros(1)])
+            cs = float(flat.double().sum().item())
+            comm.send_tensor(torch.cat([flat.cpu(), torch.tensor([cs], dtype=torch.float32)]), dst, tag=2)
+            opt = self.t.optimizers.pop(sid, None)
+            self.t.schedulers.pop(sid, None)
+            st.to("cpu")
+            for p in st.parameters():
+                p.grad = None
+        elif self.rank == dst:
+            buf = comm.recv_tensor(src, torch.device("cpu"), tag=2)
+            flat = buf[:-1]
+            off = 0
+            sd = st.state_dict()
+            for k, v in sd.items():
+                if v.is_floating_point():
+                    n = v.numel()
+                    v.copy_(flat[off:off + n].reshape(v.shape).to(v.dtype))
+                    off += n
+            for p in st.parameters():
+                p.grad = None
+            self._adopt(sid)
+
+    # ------------------------------------------------------------------ misc
+    @torch.no_grad()
+    def validate(self, loader) -> float:
+        S = len(self.stages)
+        total, n = 0.0, 0
+        for batch in loader:
+            x = None
+            for s in range(S):
+                if self._owner(s) != self.rank:
+                    continue
+                if s == 0:
+                    x = batch["input"].to(self.device)
+                elif self._owner(s - 1) != self.rank:
+                    x = comm.recv_tensor(self._owner(s - 1), self.device, tag=3)
+                x = self.stages[s](x)
+                if s < S - 1 and self._owner(s + 1) != self.rank:
+                    comm.send_tensor(x, self._owner(s + 1), tag=3)
+            loss = 0.0
+            if self._owner(S - 1) == self.rank:
+                loss = float(self.t.calculate_loss(x, batch["target"]).item())
+            total += comm.broadcast_float(loss, self._owner(S - 1))
+            n += 1
+        return total / max(1, n)
+
+    def comm_fraction(self) -> float:
+        return self._comm_s / self._step_s if self._step_s > 0 else 0.0
+
+    def cleanup(self) -> None:
+        pass

@@ -1,0 +1,87 @@
+"""Parameter monitor — named in the reference's architecture sketch ("Param Monitor",
+README.md:22) and implied by ``AttackType.MODEL_POISONING`` (attack_detector.py:22) but never
+implemented.  North-star semantics: per-shard checksums and drift norms, fused into
+the parameter all-gather.
+
+* checksum: order-sensitive Fletcher-style 64-bit sum over the raw 32-bit words of a shard.  A
+  receiver recomputes it while it copies the shard in (csrc/param_gather.cu) and compares with
+  the value the owner published -> in-flight / at-rest tampering shows up as a mismatch.
+* drift: ``||theta_t - theta_{t-1}||_2`` per shard.  An optimizer step moves parameters by about
+  ``lr * sqrt(numel)``; a poisoned shard moves orders of magnitude more.  Flagged when the drift
+  exceeds ``drift_ratio_max`` x the running median drift (after warm-up), or is non-finite.
+"""
+from __future__ import annotations
+
+import logging
+from collections import defaultdict, deque
+from typing import Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["ParameterMonitor"]
+
+
+class ParameterMonitor:
+    def __init__(self, drift_ratio_max: float = 10.0, warmup: int = 3, history: int = 64):
+        self.drift_ratio_max = float(drift_ratio_max)
+        self.warmup = int(warmup)
+        self._prev: Dict[int, torch.Tensor] = {}
+        self._drifts: Dict[int, deque] = defaultdict(lambda: deque(maxlen=history))
+        self.checksums: Dict[int, int] = {}
+        self.events: List[Dict] = []
+
+    @staticmethod
+    def _flat(params: Iterable[torch.Tensor]) -> torch.Tensor:
+        ps = [p.detach().reshape(-1) for p in params]
+        return ps[0] if len(ps) == 1 else torch.cat(ps)
+
+    @staticmethod
+    def checksum(t: torch.Tensor) -> int:
+        from ..ops.integrity import checksum64
+        return checksum64(t)
+
+    def publish(self, shard_id: int, params: Iterable[torch.Tensor]) -> int:
+        """Owner side: record (and return) the checksum peers should observe."""
+        cs = self.checksum(self._flat(params))
+        self.checksums[shard_id] = cs
+        return cs
+
+    def verify_received(self, shard_id: int, params: Iterable[torch.Tensor], expected: Optional[int] = None) -> bool:
+        exp = self.checksums.get(shard_id) if expected is None else expected
+        got = self.checksum(self._flat(params))
+        ok = exp is None or got == exp
+        if not ok:
+            self.events.append({"shard": shard_id, "reason": "checksum_mismatch", "expected": exp, "got": got})
+            logger.error("parameter shard %d failed its integrity check", shard_id)
+        return ok
+
+    def observe(self, shard_id: int, params: Iterable[torch.Tensor], step: int) -> Dict:
+        """Track drift of one shard; returns ``{drift, expected, poisoned}``."""
+        from ..ops.integrity import drift_sq_and_update
+        flat = self._flat(params)
+        prev = self._prev.get(shard_id)
+        if prev is None or prev.numel() != flat.numel():
+            self._prev[shard_id] = flat.clone()
+            return {"drift": 0.0, "expected": None, "poisoned": False}
+        drift = float(drift_sq_and_update(flat, prev)) ** 0.5          # prev <- flat in the same pass
+        hist = self._drifts[shard_id]
+        expected = float(np.median(hist)) if len(hist) >= self.warmup else None
+        poisoned = (not np.isfinite(drift)) or (expected is not None and expected > 0
+                                                and drift > self.drift_ratio_max * expected)
+        if poisoned:
+            self.events.append({"shard": shard_id, "step": step, "reason": "drift", "drift": drift,
+                                "expected": expected})
+        else:
+            hist.append(drift)
+        return {"drift": drift, "expected": expected, "poisoned": poisoned}
+
+    def detect_parameter_poisoning(self, shard_id: int, params: Iterable[torch.Tensor], step: int) -> bool:
+        return bool(self.observe(shard_id, params, step)["poisoned"])
+
+    def reset(self, shard_id: int) -> None:
+        self._prev.pop(shard_id, None)
+        self._drifts.pop(shard_id, None)
+        self.checksums.pop(shard_id, None)
