@@ -1,0 +1,505 @@
+// K12: causal softmax-attention forward / backward for head_dim 64 on tcgen05 tensor cores.
+//
+// Layout: qkv is the fused projection output [B*T, 3C] (bf16), head h uses columns
+// [h*64, h*64+64) of each third; the output / its gradient are [B*T, C].  TMA pulls 128x64 tiles
+// straight out of those buffers (no head split / transpose copies).
+//
+// Forward (one CTA = one 128-query block of one head, 2 CTAs per SM):
+//   S = Q K^T      tcgen05.mma, K-major operands, fp32 S in TMEM (128 lanes x 128 columns)
+//   softmax        each of the 128 threads owns one query row (tcgen05.ld 32x32b), online max/sum in
+//                  registers, exp2 with the scale folded in, P written to smem as bf16 in the
+//                  128B-swizzled K-major layout the tensor core reads
+//   O += P V       tcgen05.mma with V consumed MN-major exactly as it sits in memory; partial
+//                  products land in TMEM and are folded into the register accumulator with the
+//                  running rescale
+// Backward = preprocess (delta = rowsum(dO*O)) + two tensor-core kernels:
+//   dK/dV kernel   one CTA per key block, loops over query blocks; dV += P^T dO, dK += dS^T Q with
+//                  P / dS read from smem as MN-major A operands, accumulators stay in TMEM
+//   dQ kernel      one CTA per query block, loops over key blocks; dQ += dS K
+// The reference reaches attention only through torch/HF eager ops.
+#include "common.cuh"
+
+namespace {
+
+constexpr int D = 64;            // head dim
+constexpr int BQ = 128;          // query rows per tile
+constexpr int BK = 128;          // key rows per tile
+constexpr int TILE_BYTES = 128 * 64 * 2;   // 16 KB: one [128 x 64] bf16 tile
+
+struct AttnParams {
+    int B, T, H, C;              // C = H * 64
+    float scale_log2;            // softmax scale * log2(e)
+    float scale;                 // softmax scale
+    __nv_bfloat16* out;          // fwd: O [B*T, C]
+    float* lse;                  // [B, H, T]  natural-log logsumexp of the scaled scores
+    const float* delta;          // bwd: [B, H, T]
+    __nv_bfloat16* dqkv;         // bwd: [B*T, 3C]
+};
+
+// byte offset of the 16-byte piece `q8` (0..7) of row r inside a [rows x 64] bf16 tile with 128B swizzle
+__device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t q8) { return r * 128u + ((q8 ^ (r & 7u)) << 4); }
+
+// write 32 fp32 values (columns c0..c0+31 of row r, already final) as bf16 into a [128 x 128] operand
+// stored as two swizzled [128 x 64] sub-tiles
+__device__ __forceinline__ void store_p_chunk(uint8_t* tile, int r, int c0, const float (&v)[32]) {
+    uint8_t* sub = tile + (c0 >> 6) * TILE_BYTES;
+    const int q0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+        u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+        *reinterpret_cast<uint4*>(sub + swz(r, q0 + q)) = u;
+    }
+}
+
+// ---- descriptor helpers for [128 x 64] swizzled tiles ------------------------------------------
+// tile rows are the M/N index, 64 contiguous elements are K (K-major); k16 = which 16-wide K slice
+__device__ __forceinline__ uint64_t desc_kmajor(const uint8_t* tile, int k16) {
+    return umma_smem_desc(smem_u32(tile) + k16 * 32, 16, 1024);
+}
+// tile rows are the K index, 64 contiguous elements are M/N (MN-major); `lbo` = distance between
+// consecutive 64-wide M/N chunks (only used when the operand is wider than 64)
+__device__ __forceinline__ uint64_t desc_mnmajor(const uint8_t* tile, int k16, uint32_t lbo) {
+    return umma_smem_desc(smem_u32(tile) + k16 * 2048, lbo, 1024);
+}
+
+// =================================================================================================
+// forward
+// =================================================================================================
+__global__ void __launch_bounds__(128, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + TILE_BYTES;              // 2 buffers
+    uint8_t* sV = smem + 3 * TILE_BYTES;          // 2 buffers
+    uint8_t* sP = smem + 5 * TILE_BYTES;          // [128 x 128] = 2 sub-tiles
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * TILE_BYTES);
+    uint64_t* bar_q = bars;
+    uint64_t* bar_kv = bars + 1;                  // [2]
+    uint64_t* bar_s = bars + 3;
+    uint64_t* bar_o = bars + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    // heaviest (longest causal row) tiles first
+    const int qb = (gridDim.x - 1) - blockIdx.x;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int row0 = b * p.T;
+    const int n_kv = qb + 1;
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        tma_prefetch_desc(&tmap_qkv);
+        mbar_init(bar_q, 1); mbar_init(&bar_kv[0], 1); mbar_init(&bar_kv[1], 1);
+        mbar_init(bar_s, 1); mbar_init(bar_o, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+    if (tid == 0) {
+        mbar_arrive_expect_tx(bar_q, TILE_BYTES);
+        tma_load_2d(sQ, &tmap_qkv, bar_q, h * D, row0 + qb * BQ);
+        mbar_arrive_expect_tx(&bar_kv[0], 2 * TILE_BYTES);
+        tma_load_2d(sK, &tmap_qkv, &bar_kv[0], p.C + h * D, row0);
+        tma_load_2d(sV, &tmap_qkv, &bar_kv[0], 2 * p.C + h * D, row0);
+    }
+
+    const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    float o_acc[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) o_acc[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const int r = tid;                               // query row inside the tile
+
+    for (int j = 0; j < n_kv; ++j) {
+        const int buf = j & 1;
+        if (tid == 0) {
+            if (j + 1 < n_kv) {                      // prefetch next K/V into the other buffer
+                mbar_arrive_expect_tx(&bar_kv[buf ^ 1], 2 * TILE_BYTES);
+                tma_load_2d(sK + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], p.C + h * D, row0 + (j + 1) * BK);
+                tma_load_2d(sV + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], 2 * p.C + h * D, row0 + (j + 1) * BK);
+            }
+            if (j == 0) mbar_wait(bar_q, 0);
+            mbar_wait(&bar_kv[buf], (j >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k)
+                umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + buf * TILE_BYTES, k), idesc_s, k > 0);
+            umma_commit(bar_s);
+        }
+        mbar_wait(bar_s, j & 1);
+        __syncwarp();
+        tc_fence_after();
+
+        // ---- online softmax over this thread's row --------------------------------------------
+        const bool diag = (j == qb);
+        float mx = m_run;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_s + lane_base + c * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float s = __uint_as_float(raw[i]) * p.scale_log2;
+                if (!diag || (c * 32 + i) <= r) mx = fmaxf(mx, s);
+            }
+        }
+        const float alpha = exp2f(m_run - mx);
+        float rs = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_s + lane_base + c * 32, raw);
+            tmem_ld_wait();
+            float pv[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float s = __uint_as_float(raw[i]) * p.scale_log2;
+                float e = exp2f(s - mx);
+                if (diag && (c * 32 + i) > r) e = 0.f;
+                // the tensor core consumes the bf16-rounded probability: keep the row sum consistent
+                e = __bfloat162float(__float2bfloat16_rn(e));
+                pv[i] = e;
+                rs += e;
+            }
+            store_p_chunk(sP, r, c * 32, pv);
+        }
+        l_run = l_run * alpha + rs;
+        m_run = mx;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) o_acc[i] *= alpha;
+
+        fence_proxy_async_smem();                    // P (generic proxy) -> visible to the tensor core
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+                umma_bf16_ss(tmem_o, desc_kmajor(sP + (k >> 2) * TILE_BYTES, k & 3),
+                             desc_mnmajor(sV + buf * TILE_BYTES, k, TILE_BYTES), idesc_o, k > 0);
+            umma_commit(bar_o);
+        }
+        mbar_wait(bar_o, j & 1);
+        __syncwarp();
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_o + lane_base + c * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(raw[i]);
+        }
+        tc_fence_before();
+    }
+
+    // ---- epilogue -----------------------------------------------------------------------------
+    const float inv = 1.0f / l_run;
+    const long long grow = (long long)(row0 + qb * BQ + r);
+    __nv_bfloat16* orow = p.out + grow * p.C + h * D;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(o_acc[q * 8 + 0] * inv, o_acc[q * 8 + 1] * inv); u.y = pack_bf16x2(o_acc[q * 8 + 2] * inv, o_acc[q * 8 + 3] * inv);
+        u.z = pack_bf16x2(o_acc[q * 8 + 4] * inv, o_acc[q * 8 + 5] * inv); u.w = pack_bf16x2(o_acc[q * 8 + 6] * inv, o_acc[q * 8 + 7] * inv);
+        *reinterpret_cast<uint4*>(orow + q * 8) = u;
+    }
+    p.lse[((long long)b * p.H + h) * p.T + qb * BQ + r] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+}
+
+// =================================================================================================
+// backward preprocess: delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]
+// =================================================================================================
+__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                                         float* __restrict__ delta, int B, int T, int H) {
+    // 8 threads per (row, head): each handles 8 of the 64 elements
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long item = gid >> 3;
+    const int part = gid & 7;
+    const long long total = (long long)B * T * H;
+    float acc = 0.f;
+    if (item < total) {
+        const long long row = item / H;
+        const int h = item % H;
+        const long long off = row * (long long)(H * D) + h * D + part * 8;
+        const uint4 a = *reinterpret_cast<const uint4*>(o + off), g = *reinterpret_cast<const uint4*>(d_o + off);
+        const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+        const float2 g0 = unpack_bf16x2(g.x), g1 = unpack_bf16x2(g.y), g2 = unpack_bf16x2(g.z), g3 = unpack_bf16x2(g.w);
+        acc = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y + a2.x * g2.x + a2.y * g2.y + a3.x * g3.x + a3.y * g3.y;
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (item < total && part == 0) {
+        const long long row = item / H;
+        const int h = item % H;
+        const int b = row / T, t = row % T;
+        delta[((long long)b * H + h) * T + t] = acc;
+    }
+}
+
+// =================================================================================================
+// backward main kernels.  MODE 0: dK/dV (outer tile = key block, inner loop over query blocks)
+//                         MODE 1: dQ    (outer tile = query block, inner loop over key blocks)
+// smem: fixed pair (2 tiles) | streamed pair x2 (4 tiles) | P (2 tiles) | dS (2 tiles)  = 160 KB
+// TMEM: S [0,128) dP [128,256) acc0 [256,320) acc1 [320,384)
+// =================================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(128, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sFix0 = smem;                         // MODE0: K   MODE1: Q
+    uint8_t* sFix1 = smem + TILE_BYTES;            // MODE0: V   MODE1: dO
+    uint8_t* sStr = smem + 2 * TILE_BYTES;         // [buf][2] : MODE0: Q,dO   MODE1: K,V
+    uint8_t* sP = smem + 6 * TILE_BYTES;
+    uint8_t* sdS = smem + 8 * TILE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 10 * TILE_BYTES);
+    uint64_t* bar_fix = bars;
+    uint64_t* bar_str = bars + 1;                  // [2]
+    uint64_t* bar_s = bars + 3;
+    uint64_t* bar_acc = bars + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int nblk = p.T / 128;
+    const int ob = MODE == 0 ? blockIdx.x : (gridDim.x - 1) - blockIdx.x;      // outer block index
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int row0 = b * p.T;
+    const int i_begin = MODE == 0 ? ob : 0;
+    const int i_end = MODE == 0 ? nblk : ob + 1;
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do);
+        mbar_init(bar_fix, 1); mbar_init(&bar_str[0], 1); mbar_init(&bar_str[1], 1);
+        mbar_init(bar_s, 1); mbar_init(bar_acc, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem_s = tmem, tmem_dp = tmem + 128, tmem_a0 = tmem + 256, tmem_a1 = tmem + 320;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+    auto load_stream = [&](int i, int buf) {      // called by thread 0
+        uint8_t* s0 = sStr + buf * 2 * TILE_BYTES;
+        mbar_arrive_expect_tx(&bar_str[buf], 2 * TILE_BYTES);
+        if (MODE == 0) {
+            tma_load_2d(s0, &tmap_qkv, &bar_str[buf], h * D, row0 + i * 128);                  // Q_i
+            tma_load_2d(s0 + TILE_BYTES, &tmap_do, &bar_str[buf], h * D, row0 + i * 128);      // dO_i
+        } else {
+            tma_load_2d(s0, &tmap_qkv, &bar_str[buf], p.C + h * D, row0 + i * 128);            // K_i
+            tma_load_2d(s0 + TILE_BYTES, &tmap_qkv, &bar_str[buf], 2 * p.C + h * D, row0 + i * 128);   // V_i
+        }
+    };
+    if (tid == 0) {
+        mbar_arrive_expect_tx(bar_fix, 2 * TILE_BYTES);
+        if (MODE == 0) {
+            tma_load_2d(sFix0, &tmap_qkv, bar_fix, p.C + h * D, row0 + ob * 128);              // K
+            tma_load_2d(sFix1, &tmap_qkv, bar_fix, 2 * p.C + h * D, row0 + ob * 128);          // V
+        } else {
+            tma_load_2d(sFix0, &tmap_qkv, bar_fix, h * D, row0 + ob * 128);                    // Q
+            tma_load_2d(sFix1, &tmap_do, bar_fix, h * D, row0 + ob * 128);                     // dO
+        }
+        load_stream(i_begin, 0);
+    }
+
+    const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
+    const uint32_t idesc_kv = umma_idesc_bf16(128, 64, 1, 1);       // dV, dK: MN-major A x MN-major B
+    const uint32_t idesc_dq = umma_idesc_bf16(128, 64, 0, 1);       // dQ    : K-major A x MN-major B
+    const int r = tid;
+    // MODE 1: this thread's query row is fixed for the whole kernel
+    float lse2_fix = 0.f, delta_fix = 0.f;
+    if (MODE == 1) {
+        const long long idx = ((long long)b * p.H + h) * p.T + ob * 128 + r;
+        lse2_fix = p.lse[idx] * 1.4426950408889634f;
+        delta_fix = p.delta[idx];
+    }
+
+    int it = 0;
+    for (int i = i_begin; i < i_end; ++i, ++it) {
+        const int buf = it & 1;
+        uint8_t* s0 = sStr + buf * 2 * TILE_BYTES;
+        uint8_t* s1 = s0 + TILE_BYTES;
+        // operand roles for this iteration
+        const uint8_t* tQ = MODE == 0 ? s0 : sFix0;
+        const uint8_t* tdO = MODE == 0 ? s1 : sFix1;
+        const uint8_t* tK = MODE == 0 ? sFix0 : s0;
+        const uint8_t* tV = MODE == 0 ? sFix1 : s1;
+        if (tid == 0) {
+            if (it == 0) mbar_wait(bar_fix, 0);
+            mbar_wait(&bar_str[buf], (it >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_s, desc_kmajor(tQ, k), desc_kmajor(tK, k), idesc_s, k > 0);
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(tdO, k), desc_kmajor(tV, k), idesc_s, k > 0);
+            umma_commit(bar_s);
+        }
+        // the previous iteration's accumulate-MMAs must be done before P/dS (and the other stream
+        // buffer) are overwritten
+        if (it > 0) { mbar_wait(bar_acc, (it - 1) & 1); tc_fence_after(); }
+        if (tid == 0 && i + 1 < i_end) load_stream(i + 1, buf ^ 1);
+
+        const int qblk = MODE == 0 ? i : ob, kblk = MODE == 0 ? ob : i;
+        const bool diag = (qblk == kblk);
+        float lse2 = lse2_fix, dlt = delta_fix;
+        if (MODE == 0) {
+            const long long idx = ((long long)b * p.H + h) * p.T + i * 128 + r;
+            lse2 = p.lse[idx] * 1.4426950408889634f;
+            dlt = p.delta[idx];
+        }
+        mbar_wait(bar_s, it & 1);
+        __syncwarp();
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t rs_[32], rd_[32];
+            tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
+            tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
+            tmem_ld_wait();
+            float pv[32], dsv[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                float e = exp2f(__uint_as_float(rs_[k]) * p.scale_log2 - lse2);
+                if (diag && (c * 32 + k) > r) e = 0.f;
+                pv[k] = e;
+                dsv[k] = e * (__uint_as_float(rd_[k]) - dlt);
+            }
+            if (MODE == 0) store_p_chunk(sP, r, c * 32, pv);
+            store_p_chunk(sdS, r, c * 32, dsv);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            if (MODE == 0) {
+                // dV[k, d] += sum_q P[q, k] dO[q, d] ;  dK[k, d] += sum_q dS[q, k] Q[q, d]   (K dim = 128 queries)
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16_ss(tmem_a0, desc_mnmajor(sP, k, TILE_BYTES), desc_mnmajor(tdO, k, TILE_BYTES), idesc_kv, (it > 0 || k > 0));
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16_ss(tmem_a1, desc_mnmajor(sdS, k, TILE_BYTES), desc_mnmajor(tQ, k, TILE_BYTES), idesc_kv, (it > 0 || k > 0));
+            } else {
+                // dQ[q, d] += sum_k dS[q, k] K[k, d]     (K dim = 128 keys)
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16_ss(tmem_a0, desc_kmajor(sdS + (k >> 2) * TILE_BYTES, k & 3), desc_mnmajor(tK, k, TILE_BYTES), idesc_dq, (it > 0 || k > 0));
+            }
+            umma_commit(bar_acc);
+        }
+    }
+    // ---- write the accumulators ------------------------------------------------------------------
+    mbar_wait(bar_acc, (it - 1) & 1);
+    __syncwarp();
+    tc_fence_after();
+    const long long grow = (long long)(row0 + ob * 128 + r);
+    auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t raw[32];
+            tmem_ld_32x32(taddr + lane_base + c * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 u;
+                u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
+                u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
+                u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
+                u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
+                *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
+            }
+        }
+    };
+    __nv_bfloat16* base = p.dqkv + grow * (3LL * p.C) + h * D;
+    if (MODE == 0) {
+        write_acc(tmem_a1, base + p.C, p.scale);          // dK
+        write_acc(tmem_a0, base + 2 * p.C, 1.0f);         // dV
+    } else {
+        write_acc(tmem_a0, base, p.scale);                // dQ
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+}  // namespace
+
+int tdl_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                          uint32_t box_inner, uint32_t box_outer);
+
+static int check_attn_shapes(int64_t B, int64_t T, int64_t H, int64_t Dh) {
+    TDL_REQUIRE(Dh == 64, "attention kernels are specialised for head_dim 64 (got %lld)", (long long)Dh);
+    TDL_REQUIRE(T % 128 == 0 && T > 0, "sequence length must be a multiple of 128 (got %lld)", (long long)T);
+    TDL_REQUIRE(B > 0 && H > 0 && B <= 65535 && H <= 65535, "bad batch/head count");
+    return 0;
+}
+
+extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t B, int64_t T, int64_t H, int64_t Dh,
+                                 void* stream) {
+    if (int rc = check_attn_shapes(B, T, H, Dh)) return rc;
+    const int C = (int)(H * 64);
+    CUtensorMap tm;
+    if (int rc = tdl_make_tmap_2d_bf16(&tm, qkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
+    AttnParams p{};
+    p.B = (int)B; p.T = (int)T; p.H = (int)H; p.C = C;
+    p.scale = 1.0f / sqrtf(64.0f);
+    p.scale_log2 = p.scale * 1.4426950408889634f;
+    p.out = (__nv_bfloat16*)out; p.lse = lse;
+    const int smem = 7 * TILE_BYTES + 64;
+    static bool configured = false;
+    if (!configured) {
+        TDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                                 void* dqkv, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream) {
+    if (int rc = check_attn_shapes(B, T, H, Dh)) return rc;
+    const int C = (int)(H * 64);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CUtensorMap tq, tdo;
+    if (int rc = tdl_make_tmap_2d_bf16(&tq, qkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
+    if (int rc = tdl_make_tmap_2d_bf16(&tdo, d_out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
+    const long long items = B * T * H * 8;
+    attn_delta_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)d_out, delta,
+                                                                    (int)B, (int)T, (int)H);
+    AttnParams p{};
+    p.B = (int)B; p.T = (int)T; p.H = (int)H; p.C = C;
+    p.scale = 1.0f / sqrtf(64.0f);
+    p.scale_log2 = p.scale * 1.4426950408889634f;
+    p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = (__nv_bfloat16*)dqkv;
+    const int smem = 10 * TILE_BYTES + 64;
+    static bool configured = false;
+    if (!configured) {
+        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
+    attn_bwd_kernel<0><<<grid, 128, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<1><<<grid, 128, smem, s>>>(tq, tdo, p);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,571 @@
+// Memory-bound hot ops of the fused GPT-2 engine and of the security layer:
+//   K10 LayerNorm fwd / bwd (bwd fuses the residual-gradient add and accumulates dgamma/dbeta)
+//   K11 bias gradient (column sums; GELU itself lives in the GEMM epilogue)
+//   K14 fused AdamW (fp32 master + moments, bf16 working copy, optional device-side grad scale)
+//   K15 cross-entropy fwd+bwd in place over the padded vocabulary
+//   K1  bucket pack (fp32 main grad -> bf16 bucket) + local sum of squares
+//   K16 fault-injection (scale / sign flip / Gaussian noise, counter-based RNG)
+//   K9  building blocks: 64-bit shard checksum, drift norm with snapshot refresh
+//   embedding fwd / bwd, multi-tensor squared norms
+// All are single-pass, 16-byte vectorised, fp32 math, bf16 storage.  None of them exist in the
+// reference (torch eager ops + per-tensor .item() syncs).
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ void bf16x8_to_f32(const uint4& u, float (&f)[8]) {
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 f32_to_bf16x8(const float (&f)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]); u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+    return u;
+}
+
+// ------------------------------------------------------------------------------------ LayerNorm
+constexpr int LN_MAX_ITERS = 8;            // C <= 2048, C % 8 == 0; one warp per row
+
+__global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+        const float* __restrict__ w, const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
+        float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int C, float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 4 + warp;
+    if (row >= M) return;
+    const __nv_bfloat16* xr = x + (long long)row * C;
+    float v[LN_MAX_ITERS][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        const int col = i * 256 + lane * 8;
+        if (col < C) {
+            bf16x8_to_f32(*reinterpret_cast<const uint4*>(xr + col), v[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sum += v[i][j];
+        }
+    }
+    const float mean = warp_sum(sum) / C;
+    float var = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        if (i * 256 + lane * 8 < C) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; var += d * d; }
+        }
+    }
+    const float rstd = rsqrtf(warp_sum(var) / C + eps);
+    __nv_bfloat16* yr = y + (long long)row * C;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        const int col = i * 256 + lane * 8;
+        if (col < C) {
+            float o[8];
+            const float4 w0 = *reinterpret_cast<const float4*>(w + col), w1 = *reinterpret_cast<const float4*>(w + col + 4);
+            const float4 b0 = *reinterpret_cast<const float4*>(b + col), b1 = *reinterpret_cast<const float4*>(b + col + 4);
+            const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * ww[j] + bb[j];
+            *reinterpret_cast<uint4*>(yr + col) = f32_to_bf16x8(o);
+        }
+    }
+    if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+}
+
+// dx = dres + LN'(dy) ; dgamma/dbeta accumulated (fp32 atomics) into dw/db.
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
+        const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ mean,
+        const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx,
+        float* __restrict__ dw, float* __restrict__ db, int M, int C) {
+    extern __shared__ float sh[];             // [2][C] block accumulators
+    float* sh_dw = sh;
+    float* sh_db = sh + C;
+    for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float aw[LN_MAX_ITERS][8], ab[LN_MAX_ITERS][8];
+#pragma unroll
+    for (int i = 0; i < LN_MAX_ITERS; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { aw[i][j] = 0.f; ab[i][j] = 0.f; }
+    for (int row = blockIdx.x * nwarps + warp; row < M; row += gridDim.x * nwarps) {
+        const long long off = (long long)row * C;
+        const float mu = mean[row], rs = rstd[row];
+        float g[LN_MAX_ITERS][8], xh[LN_MAX_ITERS][8];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < LN_MAX_ITERS; ++i) {
+            const int col = i * 256 + lane * 8;
+            if (col < C) {
+                float dyv[8], xv[8];
+                bf16x8_to_f32(*reinterpret_cast<const uint4*>(dy + off + col), dyv);
+                bf16x8_to_f32(*reinterpret_cast<const uint4*>(x + off + col), xv);
+                const float4 w0 = *reinterpret_cast<const float4*>(w + col), w1 = *reinterpret_cast<const float4*>(w + col + 4);
+                const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    xh[i][j] = (xv[j] - mu) * rs;
+                    g[i][j] = dyv[j] * ww[j];
+                    s1 += g[i][j];
+                    s2 += g[i][j] * xh[i][j];
+                    aw[i][j] += dyv[j] * xh[i][j];
+                    ab[i][j] += dyv[j];
+                }
+            }
+        }
+        s1 = warp_sum(s1) / C;
+        s2 = warp_sum(s2) / C;
+#pragma unroll
+        for (int i = 0; i < LN_MAX_ITERS; ++i) {
+            const int col = i * 256 + lane * 8;
+            if (col < C) {
+                float o[8];
+                if (dres != nullptr) bf16x8_to_f32(*reinterpret_cast<const uint4*>(dres + off + col), o);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) o[j] = 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] += (g[i][j] - s1 - xh[i][j] * s2) * rs;
+                *reinterpret_cast<uint4*>(dx + off + col) = f32_to_bf16x8(o);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        const int col = i * 256 + lane * 8;
+        if (col < C) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { atomicAdd(&sh_dw[col + j], aw[i][j]); atomicAdd(&sh_db[col + j], ab[i][j]); }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C; i += blockDim.x) { atomicAdd(&dw[i], sh_dw[i]); atomicAdd(&db[i], sh_db[i]); }
+}
+
+// ------------------------------------------------------------------------------------ bias grad
+// db[n] += sum_m dy[m, n];  block = 32 column-groups x 8 row lanes, 256 columns per block
+__global__ void __launch_bounds__(256) bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, float* __restrict__ db,
+                                                        int M, int N, long long ld, int rows_per_block) {
+    __shared__ float sh[8][256 + 8];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int col = blockIdx.x * 256 + tx * 8;
+    const int r0 = blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (col < N) {
+        for (int r = r0 + ty; r < r1; r += 8) {
+            float f[8];
+            bf16x8_to_f32(ld_nc_v4(dy + (long long)r * ld + col), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sh[ty][tx * 8 + j] = acc[j];
+    __syncthreads();
+    const int c = threadIdx.x;
+    if (blockIdx.x * 256 + c < N) {
+        float s = 0.f;
+#pragma unroll
+        for (int y = 0; y < 8; ++y) s += sh[y][c];
+        atomicAdd(&db[blockIdx.x * 256 + c], s);
+    }
+}
+
+// ------------------------------------------------------------------------------------ embedding
+__global__ void __launch_bounds__(128) embedding_fwd_kernel(const long long* __restrict__ idx,
+        const __nv_bfloat16* __restrict__ wte, const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out,
+        int BT, int T, int C) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 4 + warp;
+    if (row >= BT) return;
+    const long long tok = idx[row];
+    const int pos = row % T;
+    for (int col = lane * 8; col < C; col += 256) {
+        float a[8], b[8];
+        bf16x8_to_f32(*reinterpret_cast<const uint4*>(wte + tok * C + col), a);
+        bf16x8_to_f32(*reinterpret_cast<const uint4*>(wpe + (long long)pos * C + col), b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] += b[j];
+        *reinterpret_cast<uint4*>(out + (long long)row * C + col) = f32_to_bf16x8(a);
+    }
+}
+
+__global__ void __launch_bounds__(128) embedding_bwd_kernel(const long long* __restrict__ idx,
+        const __nv_bfloat16* __restrict__ dx, float* __restrict__ dwte, float* __restrict__ dwpe, int BT, int T, int C) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 4 + warp;
+    if (row >= BT) return;
+    const long long tok = idx[row];
+    const int pos = row % T;
+    for (int col = lane * 8; col < C; col += 256) {
+        float g[8];
+        bf16x8_to_f32(*reinterpret_cast<const uint4*>(dx + (long long)row * C + col), g);
+        float* a = dwte + tok * C + col;
+        float* b = dwpe + (long long)pos * C + col;
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(a), "f"(g[0]), "f"(g[1]), "f"(g[2]), "f"(g[3]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(a + 4), "f"(g[4]), "f"(g[5]), "f"(g[6]), "f"(g[7]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(b), "f"(g[0]), "f"(g[1]), "f"(g[2]), "f"(g[3]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(b + 4), "f"(g[4]), "f"(g[5]), "f"(g[6]), "f"(g[7]) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------------------------ AdamW
+template <typename G>
+__global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p32, __nv_bfloat16* __restrict__ p16,
+        const G* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n, long long n_decay,
+        float lr, float b1, float b2, float eps, float wd, float bc1, float bc2, const float* __restrict__ gscale,
+        const float* __restrict__ hyper) {
+    const float gs = gscale != nullptr ? *gscale : 1.0f;
+    if (hyper != nullptr) { lr = hyper[0]; bc1 = hyper[1]; bc2 = hyper[2]; }
+    const long long stride = (long long)gridDim.x * blockDim.x * 4;
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+        float gg[4];
+        if constexpr (sizeof(G) == 4) {
+            const float4 t = *reinterpret_cast<const float4*>(g + i);
+            gg[0] = t.x; gg[1] = t.y; gg[2] = t.z; gg[3] = t.w;
+        } else {
+            const uint2 t = *reinterpret_cast<const uint2*>(g + i);
+            const float2 a = unpack_bf16x2(t.x), b = unpack_bf16x2(t.y);
+            gg[0] = a.x; gg[1] = a.y; gg[2] = b.x; gg[3] = b.y;
+        }
+        float4 pp = *reinterpret_cast<float4*>(p32 + i), mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
+        float* P = reinterpret_cast<float*>(&pp); float* Mv = reinterpret_cast<float*>(&mm); float* V = reinterpret_cast<float*>(&vv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float gj = gg[j] * gs;
+            Mv[j] = b1 * Mv[j] + (1.f - b1) * gj;
+            V[j] = b2 * V[j] + (1.f - b2) * gj * gj;
+            const float mh = Mv[j] / bc1, vh = V[j] / bc2;
+            const float decay = (i + j) < n_decay ? wd : 0.f;
+            P[j] -= lr * (mh / (sqrtf(vh) + eps) + decay * P[j]);
+        }
+        *reinterpret_cast<float4*>(p32 + i) = pp;
+        *reinterpret_cast<float4*>(m + i) = mm;
+        *reinterpret_cast<float4*>(v + i) = vv;
+        if (p16 != nullptr) {
+            uint2 o; o.x = pack_bf16x2(P[0], P[1]); o.y = pack_bf16x2(P[2], P[3]);
+            *reinterpret_cast<uint2*>(p16 + i) = o;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ cross entropy
+// one CTA per row; logits bf16 [M, Vp] overwritten with dlogits; only columns < V are real.
+__global__ void __launch_bounds__(512) xent_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
+        float* __restrict__ row_loss, float* __restrict__ loss_sum, int V, int Vp, float grad_scale) {
+    __shared__ float shm[16], shs[16];
+    const int row = blockIdx.x;
+    __nv_bfloat16* lr = logits + (long long)row * Vp;
+    const int nvec = Vp / 8;
+    float mx = -INFINITY, sum = 0.f;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        float f[8];
+        bf16x8_to_f32(*reinterpret_cast<const uint4*>(lr + i * 8), f);
+        float lm = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (i * 8 + j < V) lm = fmaxf(lm, f[j]);
+        if (lm > mx) { sum *= __expf(mx - lm); mx = lm; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (i * 8 + j < V) sum += __expf(f[j] - mx);
+    }
+    // block combine of (max, sum)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float wm = warp_max(mx);
+    sum = warp_sum(sum * __expf(mx - wm));
+    if (lane == 0) { shm[warp] = wm; shs[warp] = sum; }
+    __syncthreads();
+    float bm = -INFINITY, bs = 0.f;
+    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bm = fmaxf(bm, shm[w2]);
+    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bs += shs[w2] * __expf(shm[w2] - bm);
+    const long long tgt = targets[row];
+    const float inv = 1.0f / bs;
+    if (threadIdx.x == 0) {
+        const float lt = __bfloat162float(lr[tgt]);
+        const float loss = logf(bs) + bm - lt;
+        if (row_loss != nullptr) row_loss[row] = loss;
+        if (loss_sum != nullptr) atomicAdd(loss_sum, loss);
+    }
+    __syncthreads();       // the target logit is read before anyone overwrites it
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        float f[8];
+        bf16x8_to_f32(*reinterpret_cast<const uint4*>(lr + i * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = i * 8 + j;
+            float p = c < V ? __expf(f[j] - bm) * inv : 0.f;
+            if (c == tgt) p -= 1.f;
+            f[j] = p * grad_scale;
+        }
+        *reinterpret_cast<uint4*>(lr + i * 8) = f32_to_bf16x8(f);
+    }
+}
+
+// ------------------------------------------------------------------------------------ K1 pack + norm
+__global__ void __launch_bounds__(256) pack_norm_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                                        long long n, double* __restrict__ sumsq) {
+    __shared__ double sh[8];
+    float acc = 0.f;
+    double dacc = 0.0;
+    int run = 0;
+    const long long stride = (long long)gridDim.x * blockDim.x * 8;
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+        const float4 a = *reinterpret_cast<const float4*>(src + i), b = *reinterpret_cast<const float4*>(src + i + 4);
+        const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+        *reinterpret_cast<uint4*>(dst + i) = f32_to_bf16x8(f);
+        if (++run == 16) { dacc += acc; acc = 0.f; run = 0; }
+    }
+    dacc += acc;
+    for (int o = 16; o > 0; o >>= 1) dacc += __shfl_xor_sync(0xffffffffu, dacc, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = dacc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        atomicAdd(sumsq, t);
+    }
+}
+
+// ------------------------------------------------------------------------------------ multi-tensor sq norm
+template <typename T>
+__global__ void __launch_bounds__(256) multi_sqnorm_kernel(const long long* __restrict__ ptrs, const long long* __restrict__ numels,
+                                                           float* __restrict__ out) {
+    __shared__ float sh[8];
+    const T* x = reinterpret_cast<const T*>(ptrs[blockIdx.y]);
+    const long long n = numels[blockIdx.y];
+    float acc = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = to_f32<T>(x[i]);
+        acc += v * v;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        if (t != 0.f) atomicAdd(&out[blockIdx.y], t);
+    }
+}
+
+// ------------------------------------------------------------------------------------ integrity
+__global__ void __launch_bounds__(256) checksum_kernel(const uint32_t* __restrict__ w, long long n, unsigned long long* __restrict__ out) {
+    __shared__ uint32_t s1s[8], s2s[8];
+    uint32_t s1 = 0, s2 = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const uint32_t v = w[i];
+        s1 += v;
+        s2 += static_cast<uint32_t>((n - i) & 0xFFFFFFFFll) * v;       // all arithmetic mod 2^32
+    }
+    for (int o = 16; o > 0; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+    if ((threadIdx.x & 31) == 0) { s1s[threadIdx.x >> 5] = s1; s2s[threadIdx.x >> 5] = s2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t a = 0, b = 0;
+        for (int k = 0; k < 8; ++k) { a += s1s[k]; b += s2s[k]; }
+        atomicAdd(&out[0], (unsigned long long)a);
+        atomicAdd(&out[1], (unsigned long long)b);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) drift_kernel(const T* __restrict__ cur, T* __restrict__ prev, long long n, float* __restrict__ out) {
+    __shared__ float sh[8];
+    float acc = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float c = to_f32<T>(cur[i]), d = c - to_f32<T>(prev[i]);
+        acc += d * d;
+        prev[i] = cur[i];
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        atomicAdd(out, t);
+    }
+}
+
+// ------------------------------------------------------------------------------------ fault injection
+__device__ __forceinline__ uint32_t mix32(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull; z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return static_cast<uint32_t>((z ^ (z >> 31)) >> 16);
+}
+template <typename T>
+__global__ void __launch_bounds__(256) poison_kernel(T* __restrict__ x, long long n, float a, float b, unsigned long long seed) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float v = a * to_f32<T>(x[i]);
+        if (b != 0.f) {
+            const float u1 = (mix32(seed * 0x100000001B3ull + 2 * i) + 1.0f) * (1.0f / 4294967808.0f);
+            const float u2 = mix32(seed * 0x100000001B3ull + 2 * i + 1) * (1.0f / 4294967296.0f);
+            v += b * sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307f * u2);
+        }
+        x[i] = from_f32<T>(v);
+    }
+}
+
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += (long long)gridDim.x * blockDim.x * 4) {
+        const float4 a = *reinterpret_cast<const float4*>(src + i);
+        uint2 o; o.x = pack_bf16x2(a.x, a.y); o.y = pack_bf16x2(a.z, a.w);
+        *reinterpret_cast<uint2*>(dst + i) = o;
+    }
+}
+
+// advances the optimizer step on the device and refreshes (lr, 1-b1^t, 1-b2^t): graph-replay safe
+__global__ void adam_tick_kernel(float* hyper, float lr, float b1, float b2) {
+    if (threadIdx.x == 0) {
+        const float step = hyper[3] + 1.0f;
+        hyper[3] = step;
+        hyper[0] = lr;
+        hyper[1] = 1.0f - powf(b1, step);
+        hyper[2] = 1.0f - powf(b2, step);
+    }
+}
+
+inline int grid_for(long long n, int per_block) {
+    long long b = (n + per_block - 1) / per_block;
+    const long long cap = (long long)tdl_num_sms() * 8;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace
+
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
+                                 int64_t M, int64_t C, float eps, void* stream) {
+    TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported (need %%8==0, <= %d)", (long long)C, 256 * LN_MAX_ITERS);
+    layernorm_fwd_kernel<<<(unsigned)((M + 3) / 4), 128, 0, STREAM(stream)>>>(
+        (const __nv_bfloat16*)x, w, b, (__nv_bfloat16*)y, mean, rstd, (int)M, (int)C, eps);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
+                                 const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream) {
+    TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported", (long long)C);
+    const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 2);
+    layernorm_bwd_kernel<<<grid, 256, 2 * C * sizeof(float), STREAM(stream)>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx,
+        dw, db, (int)M, (int)C);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream) {
+    TDL_REQUIRE(N % 8 == 0 && ld % 8 == 0, "bias_grad needs N, ld multiples of 8");
+    const int gx = (int)((N + 255) / 256);
+    int gy = std::max(1, (tdl_num_sms() * 4) / gx);
+    int rows = (int)((M + gy - 1) / gy);
+    rows = (rows + 7) / 8 * 8;
+    gy = (int)((M + rows - 1) / rows);
+    bias_grad_kernel<<<dim3(gx, gy), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)dy, db, (int)M, (int)N, ld, rows);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t BT, int64_t T,
+                                 int64_t C, void* stream) {
+    TDL_REQUIRE(C % 8 == 0, "embedding width must be a multiple of 8");
+    embedding_fwd_kernel<<<(unsigned)((BT + 3) / 4), 128, 0, STREAM(stream)>>>(
+        (const long long*)idx, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe, (__nv_bfloat16*)out, (int)BT, (int)T, (int)C);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t BT, int64_t T,
+                                 int64_t C, void* stream) {
+    TDL_REQUIRE(C % 8 == 0, "embedding width must be a multiple of 8");
+    embedding_bwd_kernel<<<(unsigned)((BT + 3) / 4), 128, 0, STREAM(stream)>>>(
+        (const long long*)idx, (const __nv_bfloat16*)dx, dwte, dwpe, (int)BT, (int)T, (int)C);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype, float* m, float* v, int64_t n,
+                         int64_t n_decay, float lr, float beta1, float beta2, float eps, float wd, int64_t step,
+                         const float* grad_scale, const float* hyper_dev, void* stream) {
+    TDL_REQUIRE(n % 4 == 0, "AdamW length must be a multiple of 4 (pad the flat buffer)");
+    const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+    const int grid = grid_for(n, 256 * 4 * 4);
+    if (grad_dtype == TDL_F32)
+        adamw_kernel<float><<<grid, 256, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const float*)grad, m, v, n, n_decay,
+                                                              lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, hyper_dev);
+    else if (grad_dtype == TDL_BF16)
+        adamw_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const __nv_bfloat16*)grad, m, v, n,
+                                                                      n_decay, lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, hyper_dev);
+    else return tdl_set_error("AdamW grads must be fp32 or bf16");
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row_loss, float* loss_sum, int64_t M,
+                                int64_t V, int64_t Vp, float grad_scale, void* stream) {
+    TDL_REQUIRE(Vp % 8 == 0 && V <= Vp, "padded vocab must be a multiple of 8 and >= vocab");
+    xent_kernel<<<(unsigned)M, 512, 0, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets, row_loss, loss_sum,
+                                                         (int)V, (int)Vp, grad_scale);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, void* stream) {
+    TDL_REQUIRE(n % 8 == 0, "bucket length must be a multiple of 8");
+    pack_norm_kernel<<<grid_for(n, 256 * 8 * 4), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_multi_sqnorm(const int64_t* ptrs_dev, const int64_t* numels_dev, int num, int dtype, float* out,
+                                void* stream) {
+    if (num <= 0) return 0;
+    dim3 grid(32, num);
+    if (dtype == TDL_F32) multi_sqnorm_kernel<float><<<grid, 256, 0, STREAM(stream)>>>((const long long*)ptrs_dev, (const long long*)numels_dev, out);
+    else if (dtype == TDL_BF16) multi_sqnorm_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((const long long*)ptrs_dev, (const long long*)numels_dev, out);
+    else if (dtype == TDL_F16) multi_sqnorm_kernel<__half><<<grid, 256, 0, STREAM(stream)>>>((const long long*)ptrs_dev, (const long long*)numels_dev, out);
+    else return tdl_set_error("unsupported dtype %d", dtype);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_checksum64(const void* words, int64_t nwords, void* out2_u64, void* stream) {
+    checksum_kernel<<<grid_for(nwords, 256 * 16), 256, 0, STREAM(stream)>>>((const uint32_t*)words, nwords, (unsigned long long*)out2_u64);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_drift_update(const void* cur, void* prev, int64_t n, int dtype, float* out, void* stream) {
+    const int grid = grid_for(n, 256 * 8);
+    if (dtype == TDL_F32) drift_kernel<float><<<grid, 256, 0, STREAM(stream)>>>((const float*)cur, (float*)prev, n, out);
+    else if (dtype == TDL_BF16) drift_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)cur, (__nv_bfloat16*)prev, n, out);
+    else return tdl_set_error("unsupported dtype %d", dtype);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_poison_inplace(void* x, int64_t n, int dtype, float a, float b, int64_t seed, void* stream) {
+    const int grid = grid_for(n, 256 * 8);
+    if (dtype == TDL_F32) poison_kernel<float><<<grid, 256, 0, STREAM(stream)>>>((float*)x, n, a, b, (unsigned long long)seed);
+    else if (dtype == TDL_BF16) poison_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((__nv_bfloat16*)x, n, a, b, (unsigned long long)seed);
+    else if (dtype == TDL_F16) poison_kernel<__half><<<grid, 256, 0, STREAM(stream)>>>((__half*)x, n, a, b, (unsigned long long)seed);
+    else return tdl_set_error("unsupported dtype %d", dtype);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+    TDL_REQUIRE(n % 4 == 0, "length must be a multiple of 4");
+    cast_f32_bf16_kernel<<<grid_for(n, 256 * 4 * 4), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst, n);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+// hyper (device float[4]): lr, 1-beta1^t, 1-beta2^t, t.  One tick per optimizer step.
+extern "C" int tdl_adam_tick(float* hyper_dev, float lr, float beta1, float beta2, void* stream) {
+    adam_tick_kernel<<<1, 32, 0, STREAM(stream)>>>(hyper_dev, lr, beta1, beta2);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,354 @@
+// K6: persistent, warp-specialised bf16 GEMM on 5th-gen tensor cores (tcgen05.mma, accumulators in
+// TMEM, operands staged by TMA with 128B swizzle) with fused epilogues.
+//
+//   C[M,N] (+)= op(A)[M,K] * op(B)[N,K]^T      fp32 accumulate
+//
+// Operand layouts (so forward, dgrad and wgrad all run without materialising a transpose):
+//   a_mn_major = 0 : A stored [M, K] row-major (K contiguous)       "K-major"
+//   a_mn_major = 1 : A stored [K, M] row-major (M contiguous)       "MN-major"  (wgrad: dY^T)
+//   b_mn_major = 0 : B stored [N, K] row-major (nn.Linear weight)   "K-major"
+//   b_mn_major = 1 : B stored [K, N] row-major                      "MN-major"  (dgrad: W, wgrad: X)
+//
+// Epilogues (runtime flags): +bias[n], GELU(tanh) with the pre-activation saved to aux_out,
+// +residual[m,n], *GELU'(aux_in[m,n]) (dgrad through the MLP activation), bf16 store, or
+// split-K fp32 accumulation with red.global.add (wgrad into the fp32 main-grad buffer).
+//
+// CTA = 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM owner,
+// warps 2..5 = epilogue (each owns one 32-lane TMEM quarter).  Two accumulator stages in TMEM
+// (2 x BLOCK_N columns) let the epilogue of tile i overlap the MMAs of tile i+1.
+// The reference has no GEMM of its own: it would call cuBLAS through torch.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                 // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int EPI_WARP0 = 2;
+
+enum Epilogue { EPI_NONE = 0, EPI_GELU = 1, EPI_RESIDUAL = 2, EPI_DGELU = 3 };
+
+struct GemmParams {
+    int M, N, K;
+    int m_blocks, n_blocks, k_blocks_per_split, split_k;
+    int a_mn_major, b_mn_major;
+    int epilogue, out_f32_atomic, bias_f32;
+    void* C; long long ldc;
+    const void* bias;
+    const void* aux_in; void* aux_out; long long ld_aux;
+};
+
+template <int BLOCK_N> struct Cfg {
+    static constexpr int STAGES = BLOCK_N == 256 ? 4 : 6;
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+    static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TMEM_COLS = 2 * BLOCK_N;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// one 32-column chunk of one accumulator row: bias / activation / residual / store
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, const uint32_t (&r)[32]) {
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        if (p.bias != nullptr) {
+            if (p.bias_f32) {
+                const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += __ldg(b + j);
+            } else {
+                const uint4* b = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint4 u = __ldg(b + q);
+                    float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                    v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
+                    v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
+                }
+            }
+        }
+        if (p.out_f32_atomic) {
+            float* out = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                             :: "l"(out + q * 4), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3]) : "memory");
+            return;
+        }
+        if (p.epilogue == EPI_GELU) {
+            __nv_bfloat16* pre = reinterpret_cast<__nv_bfloat16*>(p.aux_out) + static_cast<long long>(row) * p.ld_aux + col0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 u;
+                u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                *reinterpret_cast<uint4*>(pre + q * 8) = u;
+            }
+            // activation is applied to the value that was stored (bf16-rounded), as backward will see it
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
+        } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU) {
+            const uint4* a = reinterpret_cast<const uint4*>(
+                reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + static_cast<long long>(row) * p.ld_aux + col0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 u = __ldg(a + q);
+                float2 f[4] = {unpack_bf16x2(u.x), unpack_bf16x2(u.y), unpack_bf16x2(u.z), unpack_bf16x2(u.w)};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (p.epilogue == EPI_RESIDUAL) {
+                        v[q * 8 + 2 * e] += f[e].x; v[q * 8 + 2 * e + 1] += f[e].y;
+                    } else {
+                        v[q * 8 + 2 * e] *= gelu_tanh_grad_f(f[e].x); v[q * 8 + 2 * e + 1] *= gelu_tanh_grad_f(f[e].y);
+                    }
+                }
+            }
+        }
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint4 u;
+            u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+            u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+            *reinterpret_cast<uint4*>(out + q * 8) = u;
+        }
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const GemmParams p) {
+    using C = Cfg<BLOCK_N>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + C::STAGES;
+    uint64_t* tmem_full = bars + 2 * C::STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, C::TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int tiles_mn = p.m_blocks * p.n_blocks;
+    const int total_work = tiles_mn * p.split_k;
+    const int total_k_blocks = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+                const int split = w / tiles_mn, t = w % tiles_mn;
+                const int m_idx = (t / p.n_blocks) * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * C::A_BYTES;
+                    uint8_t* sb = smem_b + stage * C::B_BYTES;
+                    if (!p.a_mn_major) {
+                        tma_load_2d(sa, &tmap_a, &full[stage], kb * BLOCK_K, m_idx);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_M / 64; ++j)
+                            tma_load_2d(sa + j * (BLOCK_K * 128), &tmap_a, &full[stage], m_idx + j * 64, kb * BLOCK_K);
+                    }
+                    if (!p.b_mn_major) {
+                        tma_load_2d(sb, &tmap_b, &full[stage], kb * BLOCK_K, n_idx);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_N / 64; ++j)
+                            tma_load_2d(sb + j * (BLOCK_K * 128), &tmap_b, &full[stage], n_idx + j * 64, kb * BLOCK_K);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ==================================
+        const uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, p.a_mn_major, p.b_mn_major);
+        // per-UMMA_K advance of the descriptor start address (bytes)
+        const uint32_t a_kstep = p.a_mn_major ? UMMA_K * 128 : UMMA_K * 2;
+        const uint32_t b_kstep = p.b_mn_major ? UMMA_K * 128 : UMMA_K * 2;
+        const uint32_t a_lbo = p.a_mn_major ? BLOCK_K * 128 : 16;
+        const uint32_t b_lbo = p.b_mn_major ? BLOCK_K * 128 : 16;
+        int stage = 0; uint32_t phase = 0;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+            const int split = w / tiles_mn;
+            const int kb0 = split * p.k_blocks_per_split;
+            const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = smem_u32(smem_a + stage * C::A_BYTES);
+                    const uint32_t sb = smem_u32(smem_b + stage * C::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+                        const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+                        umma_bf16_ss(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty[stage]);                     // smem slot free once these MMAs retire
+                    if (kb == kb1 - 1) umma_commit(&tmem_full[acc]); // accumulator complete
+                }
+                __syncwarp();
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    } else {
+        // ================================ epilogue ====================================
+        const int quarter = warp & 3;                                // TMEM lane quarter this warp may access
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+            const int t = w % tiles_mn;
+            const int m_idx = (t / p.n_blocks) * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m_idx + quarter * 32 + lane;
+            const bool row_ok = row < p.M;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N;
+#pragma unroll 1
+            for (int c = 0; c < BLOCK_N / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr + c * 32, r);
+                tmem_ld_wait();
+                const int col0 = n_idx + c * 32;
+                if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r);
+                __syncwarp();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+}  // namespace
+
+// 2-D bf16 tensor map, 128B swizzle, zero fill out of bounds. dims/box are (inner, outer).
+int tdl_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                          uint32_t box_inner, uint32_t box_outer) {
+    EncodeTiledFn fn = get_encode_fn();
+    TDL_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    TDL_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld_elems * 2) % 16 == 0,
+                "TMA needs 16-byte aligned base and row pitch (base=%p ld=%llu)", base, (unsigned long long)ld_elems);
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld_elems * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    TDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu box=%ux%u)",
+                (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld_elems, box_inner, box_outer);
+    return 0;
+}
+
+template <int BLOCK_N>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
+    using C = Cfg<BLOCK_N>;
+    static bool configured = false;
+    if (!configured) {
+        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       C::SMEM_BYTES));
+        configured = true;
+    }
+    const int work = p.m_blocks * p.n_blocks * p.split_k;
+    const int grid = work < tdl_num_sms() ? work : tdl_num_sms();
+    gemm_bf16_tcgen05_kernel<BLOCK_N><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
+                             int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
+                             const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
+                             int64_t ld_aux, int out_f32_atomic, int split_k, int block_n, void* stream) {
+    TDL_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    TDL_REQUIRE(N % 32 == 0, "N (%lld) must be a multiple of 32", (long long)N);
+    TDL_REQUIRE(ldc % 8 == 0 && (ld_aux % 8 == 0), "ldc/ld_aux must be multiples of 8 elements");
+    if (block_n != 128 && block_n != 256) block_n = (N % 256 == 0 || N > 2048) ? 256 : 128;
+    GemmParams p;
+    p.M = (int)M; p.N = (int)N; p.K = (int)K;
+    p.m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M);
+    p.n_blocks = (int)((N + block_n - 1) / block_n);
+    const int kblocks = (int)((K + BLOCK_K - 1) / BLOCK_K);
+    if (split_k < 1) split_k = 1;
+    if (split_k > kblocks) split_k = kblocks;
+    TDL_REQUIRE(split_k == 1 || out_f32_atomic, "split-K needs the fp32 atomic epilogue");
+    TDL_REQUIRE(!(out_f32_atomic && bias != nullptr), "the fp32 atomic epilogue takes no bias");
+    p.k_blocks_per_split = (kblocks + split_k - 1) / split_k;
+    p.split_k = (kblocks + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+    p.a_mn_major = a_mn_major; p.b_mn_major = b_mn_major;
+    p.epilogue = epilogue; p.out_f32_atomic = out_f32_atomic; p.bias_f32 = bias_f32;
+    p.C = Cout; p.ldc = ldc; p.bias = bias; p.aux_in = aux_in; p.aux_out = aux_out; p.ld_aux = ld_aux;
+    TDL_REQUIRE(!(epilogue == EPI_GELU) || aux_out != nullptr, "GELU epilogue needs aux_out");
+    TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU) || aux_in != nullptr, "epilogue needs aux_in");
+
+    CUtensorMap ta, tb;
+    int rc;
+    if (!a_mn_major) rc = tdl_make_tmap_2d_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BLOCK_K, BLOCK_M);
+    else             rc = tdl_make_tmap_2d_bf16(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BLOCK_K);
+    if (rc) return rc;
+    if (!b_mn_major) rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, (uint32_t)block_n);
+    else             rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BLOCK_K);
+    if (rc) return rc;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    return block_n == 256 ? launch_gemm<256>(ta, tb, p, s) : launch_gemm<128>(ta, tb, p, s);
+}

@@ -1,0 +1,82 @@
+/* C ABI of libtdl_kernels.so — the hand-written sm_100a kernels of trustworthy_dl.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure (tdl_last_error() holds the
+ * reason); pointers are device pointers unless stated; `stream` is a cudaStream_t; dtype codes are
+ * 0 = fp32, 1 = bf16, 2 = fp16.  No function allocates device memory or synchronises the device:
+ * scratch is caller-provided, so every call can be captured into a CUDA graph.
+ *
+ * The reference (Tanmoy058/Trustworthy-Distributed-Deep-Learning) contains no native code
+ * (SURVEY.md 2.6); the comment on each declaration names the Python site whose work it absorbs.
+ */
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* tdl_last_error(void);
+int tdl_version(void);
+int tdl_device_sm_count(void);
+
+/* ---- K5: tensor statistics (reference attack_detector.py:78,185-200) ------------------------- */
+size_t tdl_stats_scratch_bytes(int64_t n);
+/* out12 (float64): mean,std,min,max,median,skewness,kurtosis,p25,p75,L1,L2,Linf */
+int tdl_tensor_stats(const void* x, int dtype, int64_t n, double* out12, void* scratch, size_t scratch_bytes, void* stream);
+/* out10 (float64): n,mean,m2,m3,m4,min,max,L1,sum(x^2),Linf */
+int tdl_tensor_moments(const void* x, int dtype, int64_t n, double* out10, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- K6: tcgen05 GEMM with fused epilogues (cuBLAS calls under distributed_trainer.py:160-161) - */
+/* C[M,N] (+)= A * B^T.  a/b_mn_major: 0 = operand stored [rows, K] (K contiguous), 1 = stored [K, rows].
+ * epilogue: 0 none, 1 GELU (pre-activation saved to aux_out), 2 +residual(aux_in), 3 *GELU'(aux_in).
+ * out_f32_atomic: accumulate into an fp32 C with red.global.add (split_k > 1 allowed). */
+int tdl_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                  int64_t ldc, int a_mn_major, int b_mn_major, const void* bias, int bias_f32, int epilogue,
+                  const void* aux_in, void* aux_out, int64_t ld_aux, int out_f32_atomic, int split_k, int block_n,
+                  void* stream);
+
+/* ---- K12: causal attention, head_dim 64 (ATen/HF attention under :160-161) -------------------- */
+int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
+int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
+                      int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
+
+/* ---- K10/K11/K14/K15 and friends ---------------------------------------------------------------- */
+int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd, int64_t M,
+                      int64_t C, float eps, void* stream);
+int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
+                      const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream);
+int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream);
+int tdl_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t BT, int64_t T, int64_t C, void* stream);
+int tdl_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t BT, int64_t T, int64_t C, void* stream);
+/* optimizer_step (distributed_trainer.py:441-446): fp32 master + bf16 working copy; hyper_dev (lr,bc1,bc2,t) optional */
+int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype, float* m, float* v, int64_t n, int64_t n_decay,
+              float lr, float beta1, float beta2, float eps, float wd, int64_t step, const float* grad_scale,
+              const float* hyper_dev, void* stream);
+int tdl_adam_tick(float* hyper_dev, float lr, float beta1, float beta2, void* stream);
+/* calculate_loss (:435-439): logits bf16 [M,Vp] are overwritten with dlogits */
+int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row_loss, float* loss_sum, int64_t M, int64_t V,
+                     int64_t Vp, float grad_scale, void* stream);
+int tdl_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* ---- K1/K2/K3: trust-weighted all-reduce with fused statistics (README.md:31; attack_detector.py:109-141) */
+int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, void* stream);
+size_t tdl_exchange_pad_bytes(void);
+int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
+                     const float* coeff, double* stats_partial, void* stream);
+int tdl_exchange(void* const* pad_ptrs, int rank, int W, int which, const double* vals, int count,
+                 unsigned int* epoch_counter, int zero_vals, void* stream);
+int tdl_trust_coefficients(const void* my_pad, int W, const float* trust, const int* status, const float* params12,
+                           float* coeff, float* norms_out, void* stream);
+int tdl_trust_finalize(const void* my_pad, int W, const float* norms, const float* out_dev, const float* params12,
+                       float* stats, float* trust, int* status, int* flags_out, int update_trust, void* stream);
+
+/* ---- misc security primitives ------------------------------------------------------------------- */
+int tdl_multi_sqnorm(const int64_t* ptrs_dev, const int64_t* numels_dev, int num, int dtype, float* out, void* stream);
+int tdl_checksum64(const void* words, int64_t nwords, void* out2_u64, void* stream);
+int tdl_drift_update(const void* cur, void* prev, int64_t n, int dtype, float* out, void* stream);
+int tdl_poison_inplace(void* x, int64_t n, int dtype, float a, float b, int64_t seed, void* stream);
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,104 @@
+"""tcgen05 GEMM (K6) vs fp32 matmul of the same bf16 inputs: every operand layout and epilogue."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from trustworthy_dl.ops import reference_impl as R
+
+
+def _mk(shape, dev, scale=1.0):
+    return (torch.randn(*shape, device=dev) * scale).bfloat16()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 128), (384, 768, 256), (1000, 320, 192), (4096, 1024, 1024),
+                                   (130, 96, 72)])
+@pytest.mark.parametrize("block_n", [128, 256])
+def test_gemm_nt_plain(M, N, K, block_n):
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(M + N + K)
+    if K % 8:
+        pytest.skip("K pitch must be 16-byte aligned")
+    a, b = _mk((M, K), dev), _mk((N, K), dev)
+    out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+    Kk.gemm(a, b, out, M, N, K, lda=K, ldb=K, ldc=N, block_n=block_n)
+    ref = a.float() @ b.float().t()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 2e-2 * (ref.abs().max().item() + 1), f"max err {err}"
+
+
+def test_gemm_dgrad_layout_b_mn_major():
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(1)
+    M, N, Kin = 512, 768, 256                      # dy [M,N], w [N,Kin] -> dx [M,Kin]
+    dy, w = _mk((M, N), dev), _mk((N, Kin), dev)
+    dx = torch.zeros(M, Kin, device=dev, dtype=torch.bfloat16)
+    Kk.linear_dgrad(dy, w, dx)
+    ref = dy.float() @ w.float()
+    assert (dx.float() - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+
+
+@pytest.mark.parametrize("split_k", [1, 4])
+def test_gemm_wgrad_layout_both_mn_major(split_k):
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(2)
+    M, N, Kin = 2048, 384, 256                     # dy [M,N], x [M,Kin] -> dw [N,Kin] fp32 accumulate
+    dy, x = _mk((M, N), dev), _mk((M, Kin), dev)
+    dw = torch.ones(N, Kin, device=dev)
+    Kk.linear_wgrad(dy, x, dw, split_k=split_k)
+    ref = dy.float().t() @ x.float() + 1.0
+    assert (dw - ref).abs().max().item() <= 1e-3 * (ref.abs().max().item() + 1)
+
+
+def test_gemm_epilogues():
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(3)
+    M, N, K = 256, 512, 128
+    x, w = _mk((M, K), dev), _mk((N, K), dev, 0.2)
+    bias = torch.randn(N, device=dev)
+    res = _mk((M, N), dev)
+    base = x.float() @ w.float().t() + bias
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, w, out, bias=bias)
+    assert torch.allclose(out.float(), base, atol=5e-2, rtol=2e-2)
+    Kk.linear_fwd(x, w, out, bias=bias.bfloat16())
+    assert torch.allclose(out.float(), x.float() @ w.float().t() + bias.bfloat16().float(), atol=5e-2, rtol=2e-2)
+    Kk.linear_fwd(x, w, out, bias=bias, epilogue=Kk.EPI_RESIDUAL, aux_in=res)
+    assert torch.allclose(out.float(), base + res.float(), atol=6e-2, rtol=2e-2)
+    pre = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, w, out, bias=bias, epilogue=Kk.EPI_GELU, aux_out=pre)
+    assert torch.allclose(pre.float(), base, atol=5e-2, rtol=2e-2)
+    assert torch.allclose(out.float(), R.gelu_tanh(pre), atol=3e-2, rtol=2e-2)
+    # dgrad through GELU
+    dy = _mk((M, K), dev)
+    w2 = _mk((K, N), dev, 0.2)                     # Linear(N -> K): weight [K, N]
+    dpre = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    Kk.linear_dgrad(dy, w2, dpre, epilogue=Kk.EPI_DGELU, aux_in=pre)
+    ref = R.gelu_tanh_bwd(pre, dy.float() @ w2.float())
+    assert torch.allclose(dpre.float(), ref, atol=5e-2, rtol=3e-2)
+
+
+def test_gemm_lm_head_shapes():
+    """N = 50304 (not a multiple of 256) and K = 50304 in the dgrad."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(4)
+    M, C, Vp = 256, 256, 50304
+    x, wte = _mk((M, C), dev), _mk((Vp, C), dev, 0.05)
+    logits = torch.empty(M, Vp, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, wte, logits)
+    ref = x.float() @ wte.float().t()
+    assert (logits.float() - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+    d = _mk((M, Vp), dev, 0.01)
+    dx = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+    Kk.linear_dgrad(d, wte, dx)
+    ref = d.float() @ wte.float()
+    assert (dx.float() - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+    dw = torch.zeros(Vp, C, device=dev)
+    Kk.linear_wgrad(d, x, dw)
+    ref = d.float().t() @ x.float()
+    assert (dw - ref).abs().max().item() <= 1e-3 * (ref.abs().max().item() + 1)

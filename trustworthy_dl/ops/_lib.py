@@ -45,6 +45,8 @@ def lib() -> ctypes.CDLL:
                         "(nvcc -gencode arch=compute_100a,code=sm_100a). CUDA tensors never fall back to eager ops.")
                 _lib = ctypes.CDLL(LIB_PATH)
                 _lib.tdl_last_error.restype = ctypes.c_char_p
+                _lib.tdl_stats_scratch_bytes.restype = ctypes.c_size_t
+                _lib.tdl_exchange_pad_bytes.restype = ctypes.c_size_t
     return _lib
 
 
