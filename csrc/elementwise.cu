@@ -272,12 +272,12 @@ __global__ void __launch_bounds__(512) xent_kernel(__nv_bfloat16* __restrict__ l
     // block combine of (max, sum)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float wm = warp_max(mx);
-    sum = warp_sum(sum * __expf(mx - wm));
+    sum = warp_sum(mx == -INFINITY ? 0.f : sum * __expf(mx - wm));      // idle lanes (Vp/8 < threads) hold -inf
     if (lane == 0) { shm[warp] = wm; shs[warp] = sum; }
     __syncthreads();
     float bm = -INFINITY, bs = 0.f;
     for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bm = fmaxf(bm, shm[w2]);
-    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bs += shs[w2] * __expf(shm[w2] - bm);
+    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bs += shm[w2] == -INFINITY ? 0.f : shs[w2] * __expf(shm[w2] - bm);
     const long long tgt = targets[row];
     const float inv = 1.0f / bs;
     if (threadIdx.x == 0) {
