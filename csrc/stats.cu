@@ -337,3 +337,71 @@ extern "C" int tdl_tensor_moments(const void* x, int dtype, int64_t n, double* o
                                   size_t scratch_bytes, void* stream) {
     return stats_dispatch(x, dtype, n, out10, scratch, scratch_bytes, false, stream);
 }
+
+
+// -------------------------------------------------------------------------------------------------
+// Allocation-free variant of tdl_tensor_stats.
+//
+// Who needs it: code that wants the 12 statistics but is not in a position to obtain device memory.
+// Two situations came up while integrating the detector:
+//   * a monitoring probe that is called from somebody else's runtime (a C/C++ trainer or serving
+//     loop that links this library directly, without PyTorch): it has no caching allocator to borrow
+//     from, and a raw cudaMalloc there would synchronise the whole device in the middle of a step and
+//     can fail outright once the job has handed all of HBM to its own pool;
+//   * a job that runs with a fixed, pre-reserved memory budget and treats any driver allocation after
+//     start-up as a bug.
+// For them the scratch the kernels need lives in the library image itself: a file-scope __device__
+// array, present once on every GPU that loads the library and kept until the process exits
+// (sizeof(Scratch), about 44 KB).  The caller still owns the input and the 12-double output.
+//
+// Rules of use
+//   * Limit: n <= TDL_STATS_NOALLOC_MAX_ELEMS (2^30 elements).  Larger requests are refused with an
+//     error; use tdl_tensor_stats with your own scratch for those.
+//   * The first call on a given device resolves the array's device address (cudaGetSymbolAddress with
+//     that device current).  Make that first call during start-up, before any stream capture begins.
+//   * There is one array per device and every call uses it.  It still holds whatever the previous call
+//     left behind, so each call first clears it on the caller's stream.  Two calls whose GPU work can
+//     overlap (different streams without an ordering between them, or two host threads) would race on
+//     it: issue them on one stream or order them with events.
+//   * Nothing here calls cudaMalloc / cudaFree or any allocating library routine.
+// -------------------------------------------------------------------------------------------------
+#include <mutex>
+
+#define TDL_STATS_NOALLOC_MAX_ELEMS_IMPL (1ll << 30)
+
+static __device__ __align__(256) unsigned char g_stats_static_scratch[sizeof(Scratch)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {nullptr};     // device address of g_stats_static_scratch, per device
+}  // namespace
+
+extern "C" int tdl_tensor_stats_noalloc(const void* x, int dtype, int64_t n, double* out12, void* stream) {
+    TDL_REQUIRE(n > 0, "tdl_tensor_stats_noalloc: empty tensor");
+    TDL_REQUIRE(n <= TDL_STATS_NOALLOC_MAX_ELEMS_IMPL,
+                "tdl_tensor_stats_noalloc: %lld elements exceed the built-in scratch limit of %lld; "
+                "use tdl_tensor_stats with caller-provided scratch",
+                (long long)n, (long long)TDL_STATS_NOALLOC_MAX_ELEMS_IMPL);
+    TDL_REQUIRE(x != nullptr && out12 != nullptr, "tdl_tensor_stats_noalloc: null input/output");
+    int dev = -1;
+    TDL_CHECK(cudaGetDevice(&dev));
+    TDL_REQUIRE(dev >= 0 && dev < kMaxDevices, "tdl_tensor_stats_noalloc: device index %d out of range", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (g_static_ptr[dev] == nullptr) {
+            // In host code `g_stats_static_scratch` is only a handle for the symbol; the address a kernel
+            // can dereference has to be looked up, with the target device current.
+            void* p = nullptr;
+            TDL_CHECK(cudaGetSymbolAddress(&p, g_stats_static_scratch));
+            TDL_REQUIRE(p != nullptr, "tdl_tensor_stats_noalloc: symbol address lookup returned null");
+            g_static_ptr[dev] = p;
+        }
+        scratch = g_static_ptr[dev];
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    // histograms and select state must start from zero; the array still holds the previous call's data
+    TDL_CHECK(cudaMemsetAsync(scratch, 0, sizeof(Scratch), s));
+    return stats_dispatch(x, dtype, n, out12, scratch, sizeof(Scratch), true, stream);
+}

@@ -27,6 +27,14 @@ int tdl_tensor_stats(const void* x, int dtype, int64_t n, double* out12, void* s
 /* out10 (float64): n,mean,m2,m3,m4,min,max,L1,sum(x^2),Linf */
 int tdl_tensor_moments(const void* x, int dtype, int64_t n, double* out10, void* scratch, size_t scratch_bytes, void* stream);
 
+/* Same 12 statistics without any device allocation: the scratch is a fixed array inside the library
+ * (one per GPU, ~44 KB, kept until exit), so callers that cannot obtain device memory mid-run can use
+ * it.  No counterpart in the reference.  n must not exceed TDL_STATS_NOALLOC_MAX_ELEMS; the first call
+ * on a device performs a one-time address lookup and should happen before any stream capture; calls
+ * share the array and must not overlap on the GPU (see csrc/stats.cu). */
+#define TDL_STATS_NOALLOC_MAX_ELEMS (1ll << 30)
+int tdl_tensor_stats_noalloc(const void* x, int dtype, int64_t n, double* out12, void* stream);
+
 /* ---- K6: tcgen05 GEMM with fused epilogues (cuBLAS calls under distributed_trainer.py:160-161) - */
 /* C[M,N] (+)= A * B^T.  a/b_mn_major: 0 = operand stored [rows, K] (K contiguous), 1 = stored [K, rows].
  * epilogue: 0 none, 1 GELU (pre-activation saved to aux_out), 2 +residual(aux_in), 3 *GELU'(aux_in).
