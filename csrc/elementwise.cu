@@ -426,6 +426,26 @@ __global__ void adam_tick_kernel(float* hyper, float lr, float b1, float b2) {
     }
 }
 
+// K7 second half: out[r, c] = sum_s staging[s][r][c] (+ residual[r, c])   (bf16 in/out, fp32 sum)
+__global__ void __launch_bounds__(256) reduce_slots_kernel(const __nv_bfloat16* __restrict__ staging, int W, long long slot_elems,
+        const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ out) {
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < slot_elems; i += (long long)gridDim.x * blockDim.x * 8) {
+        float acc[8];
+        if (residual != nullptr) bf16x8_to_f32(*reinterpret_cast<const uint4*>(residual + i), acc);
+        else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        }
+        for (int s2 = 0; s2 < W; ++s2) {
+            float f[8];
+            bf16x8_to_f32(ld_nc_v4(staging + s2 * slot_elems + i), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+        *reinterpret_cast<uint4*>(out + i) = f32_to_bf16x8(acc);
+    }
+}
+
 inline int grid_for(long long n, int per_block) {
     long long b = (n + per_block - 1) / per_block;
     const long long cap = (long long)tdl_num_sms() * 8;
@@ -566,6 +586,14 @@ extern "C" int tdl_cast_f32_bf16(const float* src, void* dst, int64_t n, void* s
 // hyper (device float[4]): lr, 1-beta1^t, 1-beta2^t, t.  One tick per optimizer step.
 extern "C" int tdl_adam_tick(float* hyper_dev, float lr, float beta1, float beta2, void* stream) {
     adam_tick_kernel<<<1, 32, 0, STREAM(stream)>>>(hyper_dev, lr, beta1, beta2);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_reduce_slots(const void* staging, int W, int64_t slot_elems, const void* residual, void* out, void* stream) {
+    TDL_REQUIRE(slot_elems % 8 == 0, "slot size must be a multiple of 8 elements");
+    reduce_slots_kernel<<<grid_for(slot_elems, 256 * 8 * 2), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)staging, W, slot_elems,
+                                                                                    (const __nv_bfloat16*)residual, (__nv_bfloat16*)out);
     TDL_LAUNCH_CHECK();
     return 0;
 }

@@ -37,7 +37,16 @@ struct GemmParams {
     void* C; long long ldc;
     const void* bias;
     const void* aux_in; void* aux_out; long long ld_aux;
+    // K8 (all-gather -> GEMM): A is row-sharded over `a_shards` peer buffers of `a_shard_rows` rows each, every
+    // shard has its own tensor map; m-blocks are visited starting at `m_block_offset` (own shard first).
+    int a_shards, a_shard_rows, m_block_offset;
+    // K7 (GEMM -> reduce-scatter): output row r belongs to rank r / c_shard_rows; the partial tile is stored
+    // into that rank's staging buffer c_ptrs[owner] at slot `c_src_slot` (P2P stores from the epilogue).
+    int c_scatter, c_shard_rows, c_src_slot;
+    void* c_ptrs[8];
 };
+
+struct TmapArray { CUtensorMap m[8]; };
 
 template <int BLOCK_N> struct Cfg {
     static constexpr int STAGES = BLOCK_N == 256 ? 4 : 6;
@@ -106,7 +115,14 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
                 }
             }
         }
-        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+        __nv_bfloat16* out;
+        if (p.c_scatter) {
+            const int owner = row / p.c_shard_rows;
+            const long long lrow = static_cast<long long>(p.c_src_slot) * p.c_shard_rows + (row - owner * p.c_shard_rows);
+            out = reinterpret_cast<__nv_bfloat16*>(p.c_ptrs[owner]) + lrow * p.ldc + col0;
+        } else {
+            out = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+        }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             uint4 u;
@@ -118,8 +134,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                         const GemmParams p) {
+gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const __grid_constant__ GemmParams p) {
+    const CUtensorMap& tmap_a = tmaps_a.m[0];
     using C = Cfg<BLOCK_N>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -138,6 +155,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
+        for (int i = 1; i < p.a_shards; ++i) tma_prefetch_desc(&tmaps_a.m[i]);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 4); }
         fence_barrier_init();
@@ -161,7 +179,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             int stage = 0; uint32_t phase = 0;
             for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
                 const int split = w / tiles_mn, t = w % tiles_mn;
-                const int m_idx = (t / p.n_blocks) * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
+                int m_blk = t / p.n_blocks + p.m_block_offset;
+                if (m_blk >= p.m_blocks) m_blk -= p.m_blocks;
+                const int m_idx = m_blk * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
+                const CUtensorMap* ta = &tmap_a;
+                int m_local = m_idx;
+                if (p.a_shards > 1) {
+                    const int sh = m_idx / p.a_shard_rows;
+                    ta = &tmaps_a.m[sh];
+                    m_local = m_idx - sh * p.a_shard_rows;
+                }
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
                 for (int kb = kb0; kb < kb1; ++kb) {
@@ -170,7 +197,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
                     uint8_t* sa = smem_a + stage * C::A_BYTES;
                     uint8_t* sb = smem_b + stage * C::B_BYTES;
                     if (!p.a_mn_major) {
-                        tma_load_2d(sa, &tmap_a, &full[stage], kb * BLOCK_K, m_idx);
+                        tma_load_2d(sa, ta, &full[stage], kb * BLOCK_K, m_local);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BLOCK_M / 64; ++j)
@@ -230,7 +257,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         int acc = 0; uint32_t acc_phase = 0;
         for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
             const int t = w % tiles_mn;
-            const int m_idx = (t / p.n_blocks) * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
+            int m_blk = t / p.n_blocks + p.m_block_offset;
+            if (m_blk >= p.m_blocks) m_blk -= p.m_blocks;
+            const int m_idx = m_blk * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const int row = m_idx + quarter * 32 + lane;
@@ -301,7 +330,7 @@ int tdl_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t inner, ui
 }
 
 template <int BLOCK_N>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
+static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
     using C = Cfg<BLOCK_N>;
     static bool configured = false;
     if (!configured) {
@@ -316,15 +345,16 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams&
     return 0;
 }
 
-extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
-                             int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
-                             const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
-                             int64_t ld_aux, int out_f32_atomic, int split_k, int block_n, void* stream) {
+static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_shard_rows, int m_block_offset,
+                       const void* B, void* Cout, void* const* c_ptrs, int c_scatter, int64_t c_shard_rows, int c_src_slot,
+                       int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
+                       const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux,
+                       int out_f32_atomic, int split_k, int block_n, void* stream) {
     TDL_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
     TDL_REQUIRE(N % 32 == 0, "N (%lld) must be a multiple of 32", (long long)N);
     TDL_REQUIRE(ldc % 8 == 0 && (ld_aux % 8 == 0), "ldc/ld_aux must be multiples of 8 elements");
     if (block_n != 128 && block_n != 256) block_n = (N % 256 == 0 || N > 2048) ? 256 : 128;
-    GemmParams p;
+    GemmParams p{};
     p.M = (int)M; p.N = (int)N; p.K = (int)K;
     p.m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M);
     p.n_blocks = (int)((N + block_n - 1) / block_n);
@@ -340,15 +370,66 @@ extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M
     p.C = Cout; p.ldc = ldc; p.bias = bias; p.aux_in = aux_in; p.aux_out = aux_out; p.ld_aux = ld_aux;
     TDL_REQUIRE(!(epilogue == EPI_GELU) || aux_out != nullptr, "GELU epilogue needs aux_out");
     TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU) || aux_in != nullptr, "epilogue needs aux_in");
-
-    CUtensorMap ta, tb;
-    int rc;
-    if (!a_mn_major) rc = tdl_make_tmap_2d_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BLOCK_K, BLOCK_M);
-    else             rc = tdl_make_tmap_2d_bf16(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BLOCK_K);
+    p.a_shards = a_shards; p.a_shard_rows = (int)a_shard_rows; p.m_block_offset = m_block_offset % p.m_blocks;
+    p.c_scatter = c_scatter; p.c_shard_rows = (int)c_shard_rows; p.c_src_slot = c_src_slot;
+    if (a_shards > 1) {
+        TDL_REQUIRE(!a_mn_major && a_shards <= 8 && a_shard_rows % BLOCK_M == 0 && a_shard_rows * a_shards == M,
+                    "sharded A needs K-major layout, <= 8 shards and shard rows that are a multiple of %d", BLOCK_M);
+    }
+    if (c_scatter) {
+        TDL_REQUIRE(!out_f32_atomic && c_shard_rows > 0 && (M + c_shard_rows - 1) / c_shard_rows <= 8, "bad scatter arguments");
+        for (int i = 0; i < (int)((M + c_shard_rows - 1) / c_shard_rows); ++i) p.c_ptrs[i] = c_ptrs[i];
+    }
+    TmapArray ta;
+    CUtensorMap tb;
+    int rc = 0;
+    if (a_shards > 1) {
+        for (int i = 0; i < a_shards && !rc; ++i)
+            rc = tdl_make_tmap_2d_bf16(&ta.m[i], a_shard_ptrs[i], (uint64_t)K, (uint64_t)a_shard_rows, (uint64_t)lda, BLOCK_K, BLOCK_M);
+    } else if (!a_mn_major) {
+        rc = tdl_make_tmap_2d_bf16(&ta.m[0], a_shard_ptrs[0], (uint64_t)K, (uint64_t)M, (uint64_t)lda, BLOCK_K, BLOCK_M);
+    } else {
+        rc = tdl_make_tmap_2d_bf16(&ta.m[0], a_shard_ptrs[0], (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BLOCK_K);
+    }
     if (rc) return rc;
     if (!b_mn_major) rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, (uint32_t)block_n);
     else             rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BLOCK_K);
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     return block_n == 256 ? launch_gemm<256>(ta, tb, p, s) : launch_gemm<128>(ta, tb, p, s);
+}
+
+extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
+                             int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
+                             const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
+                             int64_t ld_aux, int out_f32_atomic, int split_k, int block_n, void* stream) {
+    const void* a1[1] = {A};
+    return gemm_common(a1, 1, M, 0, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, bias_f32,
+                       epilogue, aux_in, aux_out, ld_aux, out_f32_atomic, split_k, block_n, stream);
+}
+
+// K8: all-gather -> GEMM.  A = concat of `W` row shards [shard_rows, K] that live in peer-mapped buffers;
+// the TMA producer reads each tile straight from the owning peer while the tensor core works on earlier
+// tiles.  `my_rank` rotates the tile order so every rank starts on its own shard.
+extern "C" int tdl_allgather_gemm_bf16(const void* const* a_shard_ptrs, int W, int my_rank, int64_t shard_rows, const void* B,
+                                       void* Cout, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                       const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
+                                       int64_t ld_aux, int block_n, void* stream) {
+    const int64_t M = shard_rows * W;
+    const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
+    return gemm_common(a_shard_ptrs, W, shard_rows, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, 0, bias,
+                       bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, stream);
+}
+
+// K7: GEMM -> reduce-scatter (first half).  The partial product tile for rows owned by rank o is stored from
+// the epilogue directly into o's staging buffer c_ptrs[o] ([W slots][shard_rows][ldc] bf16) at slot `my_rank`;
+// after the cross-rank barrier the owner sums its W slots (tdl_reduce_slots, usually fused with residual+LN).
+extern "C" int tdl_gemm_scatter_bf16(const void* A, const void* B, void* const* c_ptrs, int W, int my_rank,
+                                     int64_t shard_rows, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                     int b_mn_major, int block_n, void* stream) {
+    const int64_t M = shard_rows * W;
+    const void* a1[1] = {A};
+    const int offset = (int)(((shard_rows + BLOCK_M - 1) / BLOCK_M) * ((my_rank + 1) % W));   // start on a peer: spread the traffic
+    return gemm_common(a1, 1, M, offset, B, nullptr, c_ptrs, 1, shard_rows, my_rank, M, N, K, lda, ldb, ldc, 0, b_mn_major,
+                       nullptr, 0, 0, nullptr, nullptr, ldc, 0, 1, block_n, stream);
 }

@@ -44,6 +44,17 @@ int tdl_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int64_t N, i
                   const void* aux_in, void* aux_out, int64_t ld_aux, int out_f32_atomic, int split_k, int block_n,
                   void* stream);
 
+/* ---- K8 / K7: GEMM fused with the tensor-parallel collectives over peer-mapped memory ---------- */
+/* all-gather -> GEMM: A is W row shards [shard_rows, K] in peer buffers, read by TMA as the tiles are needed */
+int tdl_allgather_gemm_bf16(const void* const* a_shard_ptrs, int W, int my_rank, int64_t shard_rows, const void* B, void* C,
+                            int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, const void* bias, int bias_f32,
+                            int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux, int block_n, void* stream);
+/* GEMM -> reduce-scatter: partial tiles are stored from the epilogue into the owner rank's staging slots */
+int tdl_gemm_scatter_bf16(const void* A, const void* B, void* const* c_ptrs, int W, int my_rank, int64_t shard_rows,
+                          int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major, int block_n,
+                          void* stream);
+int tdl_reduce_slots(const void* staging, int W, int64_t slot_elems, const void* residual, void* out, void* stream);
+
 /* ---- K12: causal attention, head_dim 64 (ATen/HF attention under :160-161) -------------------- */
 int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
 int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
@@ -78,6 +89,17 @@ int tdl_trust_coefficients(const void* my_pad, int W, const float* trust, const 
                            float* coeff, float* norms_out, void* stream);
 int tdl_trust_finalize(const void* my_pad, int W, const float* norms, const float* out_dev, const float* params12,
                        float* stats, float* trust, int* status, int* flags_out, int update_trust, void* stream);
+
+/* ---- K9: parameter all-gather with fused checksum + drift ("Param Monitor", README.md:22) -------- */
+int tdl_param_gather(const void* const* shard_ptrs, int W, int dtype, void* dst, void* prev, int64_t shard_elems,
+                     void* sums_u64, double* drift, void* stream);
+
+/* ---- K13: conv epilogue (ResNet/VGG stages left unimplemented at distributed_trainer.py:137-144) */
+int tdl_conv_epilogue_fwd(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t N,
+                          int64_t C, int64_t HW, int dtype, int channels_last, int relu, void* stream);
+int tdl_conv_epilogue_bwd(const void* dy, const void* y, const void* x, const float* scale, void* dx, void* dres,
+                          float* dscale, float* dshift, int64_t N, int64_t C, int64_t HW, int dtype, int channels_last,
+                          int relu, void* stream);
 
 /* ---- misc security primitives ------------------------------------------------------------------- */
 int tdl_multi_sqnorm(const int64_t* ptrs_dev, const int64_t* numels_dev, int num, int dtype, float* out, void* stream);

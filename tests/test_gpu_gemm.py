@@ -102,3 +102,37 @@ def test_gemm_lm_head_shapes():
     Kk.linear_wgrad(d, x, dw)
     ref = d.float().t() @ x.float()
     assert (dw - ref).abs().max().item() <= 1e-3 * (ref.abs().max().item() + 1)
+
+
+@pytest.mark.parametrize("W", [2, 4, 8])
+def test_allgather_gemm_and_gemm_scatter_emulated_ranks(W):
+    """K8 / K7 with all "ranks" on one GPU: shard pointers are local, the kernels are the real ones."""
+    from trustworthy_dl.ops import nn as Kk, tp_ops
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(W)
+    shard_rows, Kd, N = 256, 256, 512
+    M = shard_rows * W
+    shards = [_mk((shard_rows, Kd), dev) for _ in range(W)]
+    w = _mk((N, Kd), dev, 0.2)
+    bias = torch.randn(N, device=dev)
+    ref = torch.cat(shards).float() @ w.float().t() + bias
+    for rank in (0, W - 1):
+        out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+        tp_ops.allgather_gemm([s.data_ptr() for s in shards], rank, shard_rows, w, out, bias=bias)
+        assert torch.allclose(out.float(), ref, atol=6e-2, rtol=2e-2), (out.float() - ref).abs().max().item()
+    # row-parallel: every rank holds a K-slice; partial products are scattered into the owners' slots
+    Kfull = 128 * W
+    x = _mk((M, Kfull), dev)
+    w2 = _mk((N, Kfull), dev, 0.2)
+    staging = [torch.zeros(W, shard_rows, N, device=dev, dtype=torch.bfloat16) for _ in range(W)]
+    for rank in range(W):
+        xs = x[:, rank * 128:(rank + 1) * 128].contiguous()
+        ws = w2[:, rank * 128:(rank + 1) * 128].contiguous()
+        tp_ops.gemm_scatter(xs, ws, [s.data_ptr() for s in staging], rank, shard_rows)
+    ref2 = x.float() @ w2.float().t()
+    res = _mk((shard_rows, N), dev)
+    for owner in range(W):
+        out = torch.empty(shard_rows, N, device=dev, dtype=torch.bfloat16)
+        tp_ops.reduce_slots(staging[owner], W, out, residual=res)
+        exp = ref2[owner * shard_rows:(owner + 1) * shard_rows] + res.float()
+        assert torch.allclose(out.float(), exp, atol=0.15, rtol=3e-2), (out.float() - exp).abs().max().item()

@@ -208,3 +208,46 @@ def test_device_trust_state_machine_matches_host(dev):
         assert r.coeff.item() == pytest.approx(1.0) and torch.equal(r.buffer, before)
         assert r.stats[0, 0].item() == pytest.approx(before.float().norm().item(), rel=1e-3)
         assert r.stats[0, 3].item() == pytest.approx(1.0, abs=1e-3) and r.flags.item() == 0
+
+
+def test_param_gather_checksum_and_drift(dev):
+    from trustworthy_dl.parallel.param_gather import gather_shards
+    W, n = 4, 8 * 4001
+    torch.manual_seed(0)
+    shards = [torch.randn(n, device=dev).bfloat16() for _ in range(W)]
+    dst = torch.zeros(W * n, device=dev, dtype=torch.bfloat16)
+    prev = torch.cat(shards).clone()
+    prev[n:2 * n] += 0.25                                     # shard 1 drifted
+    checks, drift = gather_shards([s.data_ptr() for s in shards], W, torch.bfloat16, dst, prev, n)
+    assert torch.equal(dst, torch.cat(shards)) and torch.equal(prev, dst)
+    for i in range(W):
+        assert checks[i] == R.fletcher64(shards[i].cpu())
+    d = drift.sqrt().cpu()
+    assert d[0] == 0 and d[2] == 0 and d[1] > 10
+    shards[2][100] += 1.0                                     # tamper after "publication"
+    checks2, _ = gather_shards([s.data_ptr() for s in shards], W, torch.bfloat16, dst, None, n)
+    assert checks2[2] != checks[2] and checks2[0] == checks[0]
+
+
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_conv_epilogue(dev, channels_last):
+    from trustworthy_dl.ops.conv_epilogue import fused_affine_add_relu, fused_bias_relu
+    torch.manual_seed(0)
+    x = torch.randn(4, 16, 8, 8, device=dev, requires_grad=True)
+    res = torch.randn(4, 16, 8, 8, device=dev, requires_grad=True)
+    if channels_last:
+        x = x.detach().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        res = res.detach().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    scale = (torch.rand(16, device=dev) + 0.5).requires_grad_(True)
+    shift = torch.randn(16, device=dev, requires_grad=True)
+    y = fused_affine_add_relu(x, scale, shift, res)
+    ref = torch.relu(x * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1) + res)
+    assert torch.allclose(y, ref, atol=1e-5)
+    g = torch.randn_like(ref)
+    got = torch.autograd.grad(y, (x, scale, shift, res), g)
+    exp = torch.autograd.grad(ref, (x, scale, shift, res), g)
+    for a, b in zip(got, exp):
+        assert torch.allclose(a, b, atol=1e-3, rtol=1e-3)
+    xb = torch.randn(2, 8, 4, 4, device=dev).bfloat16()
+    b = torch.randn(8, device=dev)
+    assert torch.allclose(fused_bias_relu(xb, b).float(), torch.relu(xb.float() + b.view(1, -1, 1, 1)), atol=2e-2)

@@ -1,0 +1,49 @@
+"""Tensor-parallel GEMMs fused with their collectives over peer-mapped memory (K7, K8).
+
+* :func:`allgather_gemm` — column-parallel linear on a sequence-sharded input: every rank holds
+  ``[M/W, K]`` rows; the GEMM's TMA producer reads each A tile from the owning peer as it is needed, so the
+  "all-gather" is spread over the whole main loop instead of preceding it.
+* :func:`gemm_scatter` + :func:`reduce_slots` — row-parallel linear: each rank's partial ``[M, N]`` product
+  is stored tile by tile from the epilogue into the owner's staging slots; after the barrier the owner sums
+  its W slots (fused with the residual add).
+Callers provide the peer pointer lists (from :class:`trustworthy_dl.parallel.symm.SymmetricBuffer`) and place a
+cross-rank barrier (``tdl_exchange``) between producer and consumer kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import i32, i64, ptr, stream_ptr
+
+
+def _arr(ptrs: List[int]):
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)
+
+
+def allgather_gemm(a_shard_ptrs: List[int], rank: int, shard_rows: int, w: torch.Tensor, out: torch.Tensor, *,
+                   bias: Optional[torch.Tensor] = None, epilogue: int = 0, aux_in=None, aux_out=None, block_n: int = 0):
+    W = len(a_shard_ptrs)
+    N, K = w.shape
+    bias_f32 = 1 if (bias is not None and bias.dtype == torch.float32) else 0
+    _lib.call("tdl_allgather_gemm_bf16", _arr(a_shard_ptrs), i32(W), i32(rank), i64(shard_rows), ptr(w), ptr(out), i64(N), i64(K),
+              i64(K), i64(K), i64(N), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in), ptr(aux_out), i64(N), i32(block_n),
+              stream_ptr())
+
+
+def gemm_scatter(a: torch.Tensor, w: torch.Tensor, staging_ptrs: List[int], rank: int, shard_rows: int, *,
+                 b_mn: bool = False, block_n: int = 0):
+    """a [M, K] @ w[N, K]^T (or w [K, N] when b_mn) -> partial rows scattered to the owners' slot `rank`."""
+    W = len(staging_ptrs)
+    M, K = a.shape
+    N = w.shape[1] if b_mn else w.shape[0]
+    assert M == shard_rows * W
+    _lib.call("tdl_gemm_scatter_bf16", ptr(a), ptr(w), _arr(staging_ptrs), i32(W), i32(rank), i64(shard_rows), i64(N), i64(K),
+              i64(K), i64(w.shape[1]), i64(N), i32(b_mn), i32(block_n), stream_ptr())
+
+
+def reduce_slots(staging: torch.Tensor, W: int, out: torch.Tensor, residual: Optional[torch.Tensor] = None):
+    _lib.call("tdl_reduce_slots", ptr(staging), i32(W), i64(out.numel()), ptr(residual), ptr(out), stream_ptr())
