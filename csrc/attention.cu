@@ -140,34 +140,31 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         tc_fence_after();
 
         // ---- online softmax over this thread's row --------------------------------------------
+        // The whole S row (128 fp32) is pulled into registers with one round of TMEM loads; max and
+        // exp are then pure register passes (1 FMNMX, then FFMA + EX2 + FADD per element).
         const bool diag = (j == qb);
-        float mx = m_run;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t raw[32];
-            tmem_ld_32x32(tmem_s + lane_base + c * 32, raw);
-            tmem_ld_wait();
+        uint32_t sraw[128];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float s = __uint_as_float(raw[i]) * p.scale_log2;
-                if (!diag || (c * 32 + i) <= r) mx = fmaxf(mx, s);
-            }
+        for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
+        tmem_ld_wait();
+        float mraw = -INFINITY;
+        if (!diag) {
+#pragma unroll
+            for (int i = 0; i < 128; ++i) mraw = fmaxf(mraw, __uint_as_float(sraw[i]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < 128; ++i) if (i <= r) mraw = fmaxf(mraw, __uint_as_float(sraw[i]));
         }
+        const float mx = fmaxf(m_run, mraw * p.scale_log2);
         const float alpha = exp2f(m_run - mx);
         float rs = 0.f;
-#pragma unroll 1
+#pragma unroll
         for (int c = 0; c < 4; ++c) {
-            uint32_t raw[32];
-            tmem_ld_32x32(tmem_s + lane_base + c * 32, raw);
-            tmem_ld_wait();
             float pv[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                const float s = __uint_as_float(raw[i]) * p.scale_log2;
-                float e = exp2f(s - mx);
+                float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));
                 if (diag && (c * 32 + i) > r) e = 0.f;
-                // the tensor core consumes the bf16-rounded probability: keep the row sum consistent
-                e = __bfloat162float(__float2bfloat16_rn(e));
                 pv[i] = e;
                 rs += e;
             }
@@ -258,7 +255,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // TMEM: S [0,128) dP [128,256) acc0 [256,320) acc1 [320,384)
 // =================================================================================================
 template <int MODE>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(256, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const AttnParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sFix0 = smem;                         // MODE0: K   MODE1: Q
@@ -294,7 +291,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_s = tmem, tmem_dp = tmem + 128, tmem_a0 = tmem + 256, tmem_a1 = tmem + 320;
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    // 256 threads: two threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns column half
+    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
 
     auto load_stream = [&](int i, int buf) {      // called by thread 0
         uint8_t* s0 = sStr + buf * 2 * TILE_BYTES;
@@ -322,7 +322,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
     const uint32_t idesc_kv = umma_idesc_bf16(128, 64, 1, 1);       // dV, dK: MN-major A x MN-major B
     const uint32_t idesc_dq = umma_idesc_bf16(128, 64, 0, 1);       // dQ    : K-major A x MN-major B
-    const int r = tid;
+    const int r = quarter * 32 + (tid & 31);
     // MODE 1: this thread's query row is fixed for the whole kernel
     float lse2_fix = 0.f, delta_fix = 0.f;
     if (MODE == 1) {
@@ -367,8 +367,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
         mbar_wait(bar_s, it & 1);
         __syncwarp();
         tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int c = half * 2; c < half * 2 + 2; ++c) {
             uint32_t rs_[32], rd_[32];
             tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
             tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
@@ -376,7 +376,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
             float pv[32], dsv[32];
 #pragma unroll
             for (int k = 0; k < 32; ++k) {
-                float e = exp2f(__uint_as_float(rs_[k]) * p.scale_log2 - lse2);
+                float e = exp2f(fmaf(__uint_as_float(rs_[k]), p.scale_log2, -lse2));
                 if (diag && (c * 32 + k) > r) e = 0.f;
                 pv[k] = e;
                 dsv[k] = e * (__uint_as_float(rd_[k]) - dlt);
@@ -412,8 +412,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     tc_fence_after();
     const long long grow = (long long)(row0 + ob * 128 + r);
     auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul) {
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
+        {
+            const int c = half;                    // each of the two row threads writes 32 of the 64 columns
             uint32_t raw[32];
             tmem_ld_32x32(taddr + lane_base + c * 32, raw);
             tmem_ld_wait();
@@ -498,8 +498,8 @@ extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d
         configured = true;
     }
     const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
-    attn_bwd_kernel<0><<<grid, 128, smem, s>>>(tq, tdo, p);
-    attn_bwd_kernel<1><<<grid, 128, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }

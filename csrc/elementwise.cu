@@ -26,6 +26,9 @@ __device__ __forceinline__ uint4 f32_to_bf16x8(const float (&f)[8]) {
 // ------------------------------------------------------------------------------------ LayerNorm
 constexpr int LN_MAX_ITERS = 8;            // C <= 2048, C % 8 == 0; one warp per row
 
+// Templated on the number of 256-column slices per row so the per-lane register arrays are exactly as
+// large as the row needs (C = 1024 -> 4 slices); the generic 8-slice version spilled.
+template <int ITERS>
 __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x,
         const float* __restrict__ w, const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
         float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int C, float eps) {
@@ -33,10 +36,10 @@ __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16*
     const int row = blockIdx.x * 4 + warp;
     if (row >= M) return;
     const __nv_bfloat16* xr = x + (long long)row * C;
-    float v[LN_MAX_ITERS][8];
+    float v[ITERS][8];
     float sum = 0.f;
 #pragma unroll
-    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+    for (int i = 0; i < ITERS; ++i) {
         const int col = i * 256 + lane * 8;
         if (col < C) {
             bf16x8_to_f32(*reinterpret_cast<const uint4*>(xr + col), v[i]);
@@ -47,7 +50,7 @@ __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16*
     const float mean = warp_sum(sum) / C;
     float var = 0.f;
 #pragma unroll
-    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+    for (int i = 0; i < ITERS; ++i) {
         if (i * 256 + lane * 8 < C) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; var += d * d; }
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16*
     const float rstd = rsqrtf(warp_sum(var) / C + eps);
     __nv_bfloat16* yr = y + (long long)row * C;
 #pragma unroll
-    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+    for (int i = 0; i < ITERS; ++i) {
         const int col = i * 256 + lane * 8;
         if (col < C) {
             float o[8];
@@ -73,7 +76,10 @@ __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16*
 }
 
 // dx = dres + LN'(dy) ; dgamma/dbeta accumulated (fp32 atomics) into dw/db.
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
+// Register budget: the row stays in registers as raw bf16 (dy, x) and is unpacked twice; only the
+// per-lane dgamma/dbeta partials are fp32 arrays -> 2 blocks of 256 threads per SM.
+template <int ITERS>
+__global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
         const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ mean,
         const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx,
         float* __restrict__ dw, float* __restrict__ db, int M, int C) {
@@ -83,32 +89,39 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
     for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    float aw[LN_MAX_ITERS][8], ab[LN_MAX_ITERS][8];
+    float aw[ITERS][8], ab[ITERS][8];
 #pragma unroll
-    for (int i = 0; i < LN_MAX_ITERS; ++i)
+    for (int i = 0; i < ITERS; ++i)
 #pragma unroll
         for (int j = 0; j < 8; ++j) { aw[i][j] = 0.f; ab[i][j] = 0.f; }
     for (int row = blockIdx.x * nwarps + warp; row < M; row += gridDim.x * nwarps) {
         const long long off = (long long)row * C;
         const float mu = mean[row], rs = rstd[row];
-        float g[LN_MAX_ITERS][8], xh[LN_MAX_ITERS][8];
+        uint4 rdy[ITERS], rx[ITERS];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-        for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        for (int i = 0; i < ITERS; ++i) {
+            const int col = i * 256 + lane * 8;
+            if (col < C) {
+                rdy[i] = ld_nc_v4(dy + off + col);
+                rx[i] = ld_nc_v4(x + off + col);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
             const int col = i * 256 + lane * 8;
             if (col < C) {
                 float dyv[8], xv[8];
-                bf16x8_to_f32(*reinterpret_cast<const uint4*>(dy + off + col), dyv);
-                bf16x8_to_f32(*reinterpret_cast<const uint4*>(x + off + col), xv);
-                const float4 w0 = *reinterpret_cast<const float4*>(w + col), w1 = *reinterpret_cast<const float4*>(w + col + 4);
+                bf16x8_to_f32(rdy[i], dyv);
+                bf16x8_to_f32(rx[i], xv);
+                const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + col)), w1 = __ldg(reinterpret_cast<const float4*>(w + col + 4));
                 const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    xh[i][j] = (xv[j] - mu) * rs;
-                    g[i][j] = dyv[j] * ww[j];
-                    s1 += g[i][j];
-                    s2 += g[i][j] * xh[i][j];
-                    aw[i][j] += dyv[j] * xh[i][j];
+                    const float xh = (xv[j] - mu) * rs, g = dyv[j] * ww[j];
+                    s1 += g;
+                    s2 += g * xh;
+                    aw[i][j] += dyv[j] * xh;
                     ab[i][j] += dyv[j];
                 }
             }
@@ -116,23 +129,30 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const __nv_bfloat16*
         s1 = warp_sum(s1) / C;
         s2 = warp_sum(s2) / C;
 #pragma unroll
-        for (int i = 0; i < LN_MAX_ITERS; ++i) {
+        for (int i = 0; i < ITERS; ++i) {
             const int col = i * 256 + lane * 8;
             if (col < C) {
-                float o[8];
-                if (dres != nullptr) bf16x8_to_f32(*reinterpret_cast<const uint4*>(dres + off + col), o);
+                float dyv[8], xv[8], o[8];
+                bf16x8_to_f32(rdy[i], dyv);
+                bf16x8_to_f32(rx[i], xv);
+                const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + col)), w1 = __ldg(reinterpret_cast<const float4*>(w + col + 4));
+                const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+                if (dres != nullptr) bf16x8_to_f32(ld_nc_v4(dres + off + col), o);
                 else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) o[j] = 0.f;
                 }
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] += (g[i][j] - s1 - xh[i][j] * s2) * rs;
+                for (int j = 0; j < 8; ++j) {
+                    const float xh = (xv[j] - mu) * rs;
+                    o[j] += (dyv[j] * ww[j] - s1 - xh * s2) * rs;
+                }
                 *reinterpret_cast<uint4*>(dx + off + col) = f32_to_bf16x8(o);
             }
         }
     }
 #pragma unroll
-    for (int i = 0; i < LN_MAX_ITERS; ++i) {
+    for (int i = 0; i < ITERS; ++i) {
         const int col = i * 256 + lane * 8;
         if (col < C) {
 #pragma unroll
@@ -459,8 +479,13 @@ inline int grid_for(long long n, int per_block) {
 extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                                  int64_t M, int64_t C, float eps, void* stream) {
     TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported (need %%8==0, <= %d)", (long long)C, 256 * LN_MAX_ITERS);
-    layernorm_fwd_kernel<<<(unsigned)((M + 3) / 4), 128, 0, STREAM(stream)>>>(
-        (const __nv_bfloat16*)x, w, b, (__nv_bfloat16*)y, mean, rstd, (int)M, (int)C, eps);
+#define LN_FWD(I) layernorm_fwd_kernel<I><<<(unsigned)((M + 3) / 4), 128, 0, STREAM(stream)>>>( \
+        (const __nv_bfloat16*)x, w, b, (__nv_bfloat16*)y, mean, rstd, (int)M, (int)C, eps)
+    switch ((C + 255) / 256) {
+        case 1: LN_FWD(1); break; case 2: LN_FWD(2); break; case 3: LN_FWD(3); break; case 4: LN_FWD(4); break;
+        case 5: LN_FWD(5); break; case 6: LN_FWD(6); break; case 7: LN_FWD(7); break; default: LN_FWD(8); break;
+    }
+#undef LN_FWD
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -468,10 +493,15 @@ extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, 
 extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
                                  const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream) {
     TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported", (long long)C);
-    const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 2);
-    layernorm_bwd_kernel<<<grid, 256, 2 * C * sizeof(float), STREAM(stream)>>>(
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx,
-        dw, db, (int)M, (int)C);
+    const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 4);
+#define LN_BWD(I) layernorm_bwd_kernel<I><<<grid, 256, 2 * C * sizeof(float), STREAM(stream)>>>( \
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, \
+        dw, db, (int)M, (int)C)
+    switch ((C + 255) / 256) {
+        case 1: LN_BWD(1); break; case 2: LN_BWD(2); break; case 3: LN_BWD(3); break; case 4: LN_BWD(4); break;
+        case 5: LN_BWD(5); break; case 6: LN_BWD(6); break; case 7: LN_BWD(7); break; default: LN_BWD(8); break;
+    }
+#undef LN_BWD
     TDL_LAUNCH_CHECK();
     return 0;
 }

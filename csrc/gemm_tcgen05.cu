@@ -13,19 +13,19 @@
 // +residual[m,n], *GELU'(aux_in[m,n]) (dgrad through the MLP activation), bf16 store, or
 // split-K fp32 accumulation with red.global.add (wgrad into the fp32 main-grad buffer).
 //
-// CTA = 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM owner,
-// warps 2..5 = epilogue (each owns one 32-lane TMEM quarter).  Two accumulator stages in TMEM
+// CTA = 320 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM owner,
+// warps 2..9 = epilogue (each owns one 32-lane TMEM quarter x one column half).  Two accumulator stages in TMEM
 // (2 x BLOCK_N columns) let the epilogue of tile i overlap the MMAs of tile i+1.
 // The reference has no GEMM of its own: it would call cuBLAS through torch.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;                 // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
-constexpr int EPI_WARP0 = 2;
+constexpr int NUM_THREADS = 320;            // TMA warp + MMA warp + 8 epilogue warps
 
 enum Epilogue { EPI_NONE = 0, EPI_GELU = 1, EPI_RESIDUAL = 2, EPI_DGELU = 3 };
 
@@ -48,8 +48,8 @@ struct GemmParams {
 
 struct TmapArray { CUtensorMap m[8]; };
 
-template <int BLOCK_N> struct Cfg {
-    static constexpr int STAGES = BLOCK_N == 256 ? 4 : 6;
+template <int BLOCK_N, int STAGES_> struct Cfg {
+    static constexpr int STAGES = STAGES_;
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -57,87 +57,99 @@ template <int BLOCK_N> struct Cfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-// one 32-column chunk of one accumulator row: bias / activation / residual / store
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, const uint32_t (&r)[32]) {
-        float v[32];
+// one 32-column chunk of one accumulator row: bias / activation / residual / store.
+// `aux` holds the 32 bf16 of aux_in for this chunk (prefetched one chunk ahead by the caller).
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, const uint32_t (&r)[32],
+                                               const uint4 (&aux)[4]) {
+    float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        if (p.bias != nullptr) {
-            if (p.bias_f32) {
-                const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    if (p.bias != nullptr) {
+        if (p.bias_f32) {
+            const float4* b = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] += __ldg(b + j);
-            } else {
-                const uint4* b = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    uint4 u = __ldg(b + q);
-                    float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
-                    v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
-                    v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
-                }
+            for (int q = 0; q < 8; ++q) {
+                const float4 t = __ldg(b + q);
+                v[q * 4 + 0] += t.x; v[q * 4 + 1] += t.y; v[q * 4 + 2] += t.z; v[q * 4 + 3] += t.w;
             }
-        }
-        if (p.out_f32_atomic) {
-            float* out = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
-                             :: "l"(out + q * 4), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3]) : "memory");
-            return;
-        }
-        if (p.epilogue == EPI_GELU) {
-            __nv_bfloat16* pre = reinterpret_cast<__nv_bfloat16*>(p.aux_out) + static_cast<long long>(row) * p.ld_aux + col0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint4 u;
-                u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-                u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-                *reinterpret_cast<uint4*>(pre + q * 8) = u;
-            }
-            // activation is applied to the value that was stored (bf16-rounded), as backward will see it
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
-        } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU) {
-            const uint4* a = reinterpret_cast<const uint4*>(
-                reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + static_cast<long long>(row) * p.ld_aux + col0);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint4 u = __ldg(a + q);
-                float2 f[4] = {unpack_bf16x2(u.x), unpack_bf16x2(u.y), unpack_bf16x2(u.z), unpack_bf16x2(u.w)};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    if (p.epilogue == EPI_RESIDUAL) {
-                        v[q * 8 + 2 * e] += f[e].x; v[q * 8 + 2 * e + 1] += f[e].y;
-                    } else {
-                        v[q * 8 + 2 * e] *= gelu_tanh_grad_f(f[e].x); v[q * 8 + 2 * e + 1] *= gelu_tanh_grad_f(f[e].y);
-                    }
-                }
-            }
-        }
-        __nv_bfloat16* out;
-        if (p.c_scatter) {
-            const int owner = row / p.c_shard_rows;
-            const long long lrow = static_cast<long long>(p.c_src_slot) * p.c_shard_rows + (row - owner * p.c_shard_rows);
-            out = reinterpret_cast<__nv_bfloat16*>(p.c_ptrs[owner]) + lrow * p.ldc + col0;
         } else {
-            out = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+            const uint4* b = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 u = __ldg(b + q);
+                float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
+                v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
+            }
         }
+    }
+    if (p.out_f32_atomic) {
+        float* out = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                         :: "l"(out + q * 4), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3]) : "memory");
+        return;
+    }
+    if (p.epilogue == EPI_GELU) {
+        __nv_bfloat16* pre = reinterpret_cast<__nv_bfloat16*>(p.aux_out) + static_cast<long long>(row) * p.ld_aux + col0;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             uint4 u;
             u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
             u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-            *reinterpret_cast<uint4*>(out + q * 8) = u;
+            *reinterpret_cast<uint4*>(pre + q * 8) = u;
         }
+        // activation is applied to the value that was stored (bf16-rounded), as backward will see it
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
+    } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint4 u = aux[q];
+            float2 f[4] = {unpack_bf16x2(u.x), unpack_bf16x2(u.y), unpack_bf16x2(u.z), unpack_bf16x2(u.w)};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (p.epilogue == EPI_RESIDUAL) {
+                    v[q * 8 + 2 * e] += f[e].x; v[q * 8 + 2 * e + 1] += f[e].y;
+                } else {
+                    v[q * 8 + 2 * e] *= gelu_tanh_grad_f(f[e].x); v[q * 8 + 2 * e + 1] *= gelu_tanh_grad_f(f[e].y);
+                }
+            }
+        }
+    }
+    __nv_bfloat16* out;
+    if (p.c_scatter) {
+        const int owner = row / p.c_shard_rows;
+        const long long lrow = static_cast<long long>(p.c_src_slot) * p.c_shard_rows + (row - owner * p.c_shard_rows);
+        out = reinterpret_cast<__nv_bfloat16*>(p.c_ptrs[owner]) + lrow * p.ldc + col0;
+    } else {
+        out = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+        u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+        *reinterpret_cast<uint4*>(out + q * 8) = u;
+    }
 }
 
-template <int BLOCK_N>
+__device__ __forceinline__ void load_aux(const GemmParams& p, int row, int col0, bool ok, uint4 (&aux)[4]) {
+    if (ok && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU)) {
+        const uint4* a = reinterpret_cast<const uint4*>(
+            reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + static_cast<long long>(row) * p.ld_aux + col0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) aux[q] = __ldg(a + q);
+    }
+}
+
+template <int BLOCK_N, int STAGES_>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
                          const __grid_constant__ GemmParams p) {
     const CUtensorMap& tmap_a = tmaps_a.m[0];
-    using C = Cfg<BLOCK_N>;
+    using C = Cfg<BLOCK_N, STAGES_>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
@@ -157,7 +169,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid
         tma_prefetch_desc(&tmap_b);
         for (int i = 1; i < p.a_shards; ++i) tma_prefetch_desc(&tmaps_a.m[i]);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 8); }
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -253,30 +265,45 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid
         }
     } else {
         // ================================ epilogue ====================================
-        const int quarter = warp & 3;                                // TMEM lane quarter this warp may access
+        // 8 warps: warp (2+e) reads TMEM lane quarter (warp & 3) and column half (e >> 2).  TMEM loads are
+        // double-buffered in registers (chunk c+1 is in flight while chunk c is processed), aux_in is
+        // prefetched one chunk ahead, and the accumulator stage is released as soon as it is in registers.
+        const int e = warp - 2;
+        const int quarter = warp & 3;
+        const int half = e >> 2;
+        constexpr int NC = BLOCK_N / 64;                              // 32-column chunks per warp
         int acc = 0; uint32_t acc_phase = 0;
         for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
             const int t = w % tiles_mn;
             int m_blk = t / p.n_blocks + p.m_block_offset;
             if (m_blk >= p.m_blocks) m_blk -= p.m_blocks;
-            const int m_idx = m_blk * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N;
-            mbar_wait(&tmem_full[acc], acc_phase);
-            tc_fence_after();
+            const int m_idx = m_blk * BLOCK_M, n_idx = (t % p.n_blocks) * BLOCK_N + half * (BLOCK_N / 2);
             const int row = m_idx + quarter * 32 + lane;
             const bool row_ok = row < p.M;
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N;
-#pragma unroll 1
-            for (int c = 0; c < BLOCK_N / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32(taddr + c * 32, r);
+            uint4 aux[2][4];
+            load_aux(p, row, n_idx, row_ok && n_idx < p.N, aux[0]);
+            mbar_wait(&tmem_full[acc], acc_phase);
+            __syncwarp();
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + half * (BLOCK_N / 2);
+            uint32_t r[2][32];
+            tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
                 tmem_ld_wait();
+                if (c + 1 < NC) {
+                    tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    load_aux(p, row, n_idx + (c + 1) * 32, row_ok && n_idx + (c + 1) * 32 < p.N, aux[(c + 1) & 1]);
+                } else {
+                    // everything this warp needs from the accumulator stage is in registers: hand it back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                }
                 const int col0 = n_idx + c * 32;
-                if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r);
+                if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r[c & 1], aux[c & 1]);
                 __syncwarp();
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
@@ -329,18 +356,18 @@ int tdl_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t inner, ui
     return 0;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int STAGES_>
 static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
-    using C = Cfg<BLOCK_N>;
+    using C = Cfg<BLOCK_N, STAGES_>;
     static bool configured = false;
     if (!configured) {
-        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES_>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        C::SMEM_BYTES));
         configured = true;
     }
     const int work = p.m_blocks * p.n_blocks * p.split_k;
     const int grid = work < tdl_num_sms() ? work : tdl_num_sms();
-    gemm_bf16_tcgen05_kernel<BLOCK_N><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+    gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES_><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -396,7 +423,10 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     else             rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BLOCK_K);
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    return block_n == 256 ? launch_gemm<256>(ta, tb, p, s) : launch_gemm<128>(ta, tb, p, s);
+    static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
+    if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
+    if (block_n == 256) return exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
+    return exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s) : launch_gemm<128, 6>(ta, tb, p, s);
 }
 
 extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
