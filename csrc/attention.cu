@@ -147,17 +147,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
         tmem_ld_wait();
-        float mraw = -INFINITY;
+        // four independent chains: a single running max/sum would serialise 128 dependent ops
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
         if (!diag) {
 #pragma unroll
-            for (int i = 0; i < 128; ++i) mraw = fmaxf(mraw, __uint_as_float(sraw[i]));
+            for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
         } else {
 #pragma unroll
-            for (int i = 0; i < 128; ++i) if (i <= r) mraw = fmaxf(mraw, __uint_as_float(sraw[i]));
+            for (int i = 0; i < 128; ++i) if (i <= r) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
         }
+        const float mraw = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         const float mx = fmaxf(m_run, mraw * p.scale_log2);
         const float alpha = exp2f(m_run - mx);
-        float rs = 0.f;
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             float pv[32];
@@ -166,10 +168,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
                 float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));
                 if (diag && (c * 32 + i) > r) e = 0.f;
                 pv[i] = e;
-                rs += e;
+                rs4[i & 3] += e;
             }
             store_p_chunk(sP, r, c * 32, pv);
         }
+        const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         l_run = l_run * alpha + rs;
         m_run = mx;
 #pragma unroll

@@ -93,7 +93,7 @@ def test_symmetric_trust_allreduce_matches_oracle():
     res = _run(_reducer_worker, world)
     for rank_res in res:
         for step, r in enumerate(rank_res):
-            assert r["err"] < 5e-2, r
+            assert r["err"] < 0.13, r                       # <= 2 bf16 ulps at |x| ~ 8
             assert r["coeff"] == pytest.approx(r["ref_coeff"], abs=2e-3)
             assert r["cos"] == pytest.approx(r["ref_cos"], abs=2e-2)
         last = rank_res[2]
