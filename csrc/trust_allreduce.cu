@@ -199,7 +199,7 @@ __global__ void coefficients_kernel(const double* __restrict__ gathered /*[W][EX
     }
     if (k == 0) { for (int i = 0; i < W; ++i) coeff[i] = 0.f; return; }
     for (int a = 1; a < k; ++a) { float v = sorted[a]; int b = a - 1; while (b >= 0 && sorted[b] > v) { sorted[b + 1] = sorted[b]; --b; } sorted[b + 1] = v; }
-    const float med = (k & 1) ? sorted[k / 2] : 0.5f * (sorted[k / 2 - 1] + sorted[k / 2]);
+    const float med = sorted[(k - 1) / 2];       // lower median: robust against one exploding norm even for k = 2
     float tot = 0.f;
     bool valid[MAX_W];
     for (int i = 0; i < W; ++i) { valid[i] = live[i] && (n[i] <= tp.norm_ratio_max * med || med <= 0.f); if (valid[i]) tot += w[i]; }
@@ -231,7 +231,7 @@ __global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W
     float srt[MAX_W]; int k = 0;
     for (int i = 0; i < W; ++i) if (isfinite(norms[i])) srt[k++] = norms[i];
     for (int a = 1; a < k; ++a) { float v = srt[a]; int b = a - 1; while (b >= 0 && srt[b] > v) { srt[b + 1] = srt[b]; --b; } srt[b + 1] = v; }
-    const float ref = k ? ((k & 1) ? srt[k / 2] : 0.5f * (srt[k / 2 - 1] + srt[k / 2])) : 0.f;
+    const float ref = k ? srt[(k - 1) / 2] : 0.f;
     for (int i = 0; i < W; ++i) {
         const float n = norms[i];
         const float cosv = (n > 0.f && mn > 0.f) ? (float)(dot[i] / ((double)n * mn)) : 1.f;

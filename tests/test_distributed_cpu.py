@@ -108,3 +108,42 @@ def test_data_parallel_trust_weighted_allreduce(mode):
     assert res[0]["owner"][1] != 1                                       # its data shard was reassigned
     assert res[0]["coeff"][1] == 0.0                                     # and it no longer contributes
     assert res[0]["trust"][1] < 0.5
+
+
+def _tp_worker(rank, world, steps, attack_step):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = None
+    if attack_step is not None:
+        att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5,
+                                               start_step=attack_step))
+        att.activate_attacks()
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=4, num_nodes=world, learning_rate=1e-2,
+                         checkpoint_interval=0, device="cpu", parallelism="tensor", optimizer="sgd", seq_len=32,
+                         model_kwargs={"n_positions": 32})
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 4, num_batches=steps, seq_len=32)]
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history],
+            "trust": t.trust_manager.trust_vector().tolist()}
+
+
+def test_tensor_parallel_matches_single_process():
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=4, num_nodes=1, learning_rate=1e-2,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd", seq_len=32, model_kwargs={"n_positions": 32},
+                         attack_detection_enabled=False)
+    t = DistributedTrainer(cfg)
+    single = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 4, num_batches=4, seq_len=32)]
+    res = run_distributed(_tp_worker, 2, 4, None)
+    assert res[0]["losses"] == pytest.approx(res[1]["losses"])
+    assert res[0]["losses"] == pytest.approx(single, rel=2e-3)
+
+
+def test_tensor_parallel_flags_poisoned_rank():
+    res = run_distributed(_tp_worker, 2, 6, 3)
+    assert res[0]["attacks"] == res[1]["attacks"] and res[0]["attacks"][0] == (1, 3)
+    assert res[0]["trust"][1] < 0.5 < res[0]["trust"][0]

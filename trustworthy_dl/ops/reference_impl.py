@@ -211,7 +211,7 @@ def robust_coefficients(norms: torch.Tensor, trust_weights: torch.Tensor, clip_r
                         norm_ratio_max: float = 2.5) -> torch.Tensor:
     """Per-rank reduction coefficients (oracle of the device-side weight kernel, K3):
     ``c_i = w_i * valid_i * min(1, clip_ratio*med/norm_i) / sum_j(w_j * valid_j)`` where ``med`` is the
-    median bucket norm over ranks with non-zero trust weight and ``valid_i`` rejects non-finite or
+    (lower) median bucket norm over ranks with non-zero trust weight and ``valid_i`` rejects non-finite or
     ``> norm_ratio_max * med`` norms *in the same step* (the cosine check lags one step)."""
     n = norms.double()
     w = trust_weights.double().to(n.device)
@@ -221,7 +221,7 @@ def robust_coefficients(norms: torch.Tensor, trust_weights: torch.Tensor, clip_r
         return torch.zeros_like(n, dtype=torch.float32)
     vals, _ = torch.sort(n[live])
     k = vals.numel()
-    med = vals[k // 2] if k % 2 else 0.5 * (vals[k // 2 - 1] + vals[k // 2])
+    med = vals[(k - 1) // 2]          # lower median: one exploding norm cannot drag the reference up (k = 2!)
     valid = live & ((n <= norm_ratio_max * med) | (med <= 0))
     clip = torch.ones_like(n)
     if clip_ratio > 0 and float(med) > 0:

@@ -88,7 +88,8 @@ class GradientVerifier:
             cos = np.where((norms > 0) & (med_norm > 0), dots / (norms * med_norm), 1.0)
         if W >= 3:
             ok &= cos >= self.cosine_min
-        ref = np.median(norms[np.isfinite(norms)]) if np.isfinite(norms).any() else 0.0
+        fin = np.sort(norms[np.isfinite(norms)])
+        ref = float(fin[(fin.size - 1) // 2]) if fin.size else 0.0          # lower median (robust for W = 2)
         if W >= 2 and ref > 0:
             ok &= norms <= self.rank_norm_ratio_max * ref
         for r in np.nonzero(~ok)[0]:
