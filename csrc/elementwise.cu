@@ -323,15 +323,16 @@ __global__ void __launch_bounds__(512) xent_kernel(__nv_bfloat16* __restrict__ l
 
 // ------------------------------------------------------------------------------------ K1 pack + norm
 __global__ void __launch_bounds__(256) pack_norm_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
-                                                        long long n, double* __restrict__ sumsq) {
+                                                        long long n, double* __restrict__ sumsq, const float* __restrict__ gscale) {
     __shared__ double sh[8];
+    const float gs = gscale != nullptr ? *gscale : 1.0f;      // fault-injection hook: a poisoned rank scales / flips its bucket
     float acc = 0.f;
     double dacc = 0.0;
     int run = 0;
     const long long stride = (long long)gridDim.x * blockDim.x * 8;
     for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
         const float4 a = *reinterpret_cast<const float4*>(src + i), b = *reinterpret_cast<const float4*>(src + i + 4);
-        const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        const float f[8] = {a.x * gs, a.y * gs, a.z * gs, a.w * gs, b.x * gs, b.y * gs, b.z * gs, b.w * gs};
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
         *reinterpret_cast<uint4*>(dst + i) = f32_to_bf16x8(f);
@@ -562,9 +563,9 @@ extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row
     return 0;
 }
 
-extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, void* stream) {
+extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, const float* scale_dev, void* stream) {
     TDL_REQUIRE(n % 8 == 0, "bucket length must be a multiple of 8");
-    pack_norm_kernel<<<grid_for(n, 256 * 8 * 4), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq);
+    pack_norm_kernel<<<grid_for(n, 256 * 8 * 4), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq, scale_dev);
     TDL_LAUNCH_CHECK();
     return 0;
 }

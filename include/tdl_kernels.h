@@ -79,7 +79,8 @@ int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row_loss, floa
 int tdl_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 
 /* ---- K1/K2/K3: trust-weighted all-reduce with fused statistics (README.md:31; attack_detector.py:109-141) */
-int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, void* stream);
+/* scale_dev: optional device float multiplied into the bucket (fault injection: scale / sign flip) */
+int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, const float* scale_dev, void* stream);
 size_t tdl_exchange_pad_bytes(void);
 int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
                      const float* coeff, double* stats_partial, void* stream);

@@ -135,6 +135,8 @@ def test_pack_norm_multinorm_checksum_drift_poison(dev):
     K.pack_norm(src, dst, ss)
     assert ss.item() == pytest.approx(src.double().pow(2).sum().item(), rel=1e-6)
     assert torch.equal(dst, src.bfloat16())
+    ss.zero_(); K.pack_norm(src, dst, ss, torch.full((1,), -3.0, device=dev))
+    assert torch.equal(dst, (src * -3.0).bfloat16()) and ss.item() == pytest.approx(9 * src.double().pow(2).sum().item(), rel=1e-6)
     ts = [torch.randn(s, device=dev) for s in (7, 1000, 12345, 1 << 16)]
     norms = per_tensor_l2norms(ts)
     assert torch.allclose(norms, torch.stack([t.norm() for t in ts]), rtol=1e-4)

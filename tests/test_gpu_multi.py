@@ -123,3 +123,60 @@ def test_data_parallel_engine_replicas_stay_in_sync():
     assert len({round(r["psum"], 4) for r in res}) == 1                     # identical parameters on every rank
     assert all(r["losses"][-1] < r["losses"][0] for r in res)
     assert res[0]["coeff"] == pytest.approx([1.0 / world] * world, abs=0.05)
+
+
+def _trainer_dp_worker(rank, world):
+    """Public API on the fused path: DistributedTrainer(parallelism='data', engine='fused') + attacker."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5, start_step=5))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=2 * world, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, parallelism="data", engine="fused", dtype="bf16", seq_len=128,
+                         model_kwargs={"n_positions": 128, "n_embd": 128, "n_head": 2, "vocab_size": 512, "padded_vocab_size": 512})
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 2 * world, num_batches=8, seq_len=128)]
+    eng = t._backend_impl.engine
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history], "owner": list(t.stage_map.owner),
+            "trust": t.trust_manager.trust_vector().tolist(), "psum": float(eng.p32.double().sum().item()),
+            "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
+
+
+def test_trainer_fused_dp_detects_poisoned_rank():
+    world = torch.cuda.device_count()
+    res = _run(_trainer_dp_worker, world)
+    assert len({round(r["psum"], 4) for r in res}) == 1
+    assert all(r["attacks"] == res[0]["attacks"] for r in res) and res[0]["attacks"][0] == (1, 5)
+    assert res[0]["owner"][1] != 1 and res[0]["trust"][1] < 0.3 < res[0]["trust"][0]
+    assert res[0]["status"][1] == "compromised"
+
+
+def _tp_worker(rank, world):
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    from trustworthy_dl.parallel import tensor_parallel as tp
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=4, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, parallelism="tensor", dtype="bf16", seq_len=128, optimizer="sgd",
+                         model_kwargs={"n_positions": 128, "n_embd": 256, "n_head": 4, "vocab_size": 512, "padded_vocab_size": 512})
+    t = DistributedTrainer(cfg)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 4, num_batches=4, seq_len=128)]
+    return {"losses": losses, "fused": tp._FUSED is not None}
+
+
+def test_tensor_parallel_fused_kernels_on_gpus():
+    world = torch.cuda.device_count()
+    if world not in (2, 4):
+        pytest.skip("tiny TP config needs 2 or 4 ranks")
+    res = _run(_tp_worker, world)
+    assert res[0]["fused"] and res[0]["losses"] == pytest.approx(res[1]["losses"], rel=1e-3)
+    # compare with the single-process fp32 model on the same batches
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=4, num_nodes=1, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd", seq_len=128, attack_detection_enabled=False,
+                         model_kwargs={"n_positions": 128, "n_embd": 256, "n_head": 4, "vocab_size": 512, "padded_vocab_size": 512})
+    t = DistributedTrainer(cfg)
+    single = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 4, num_batches=4, seq_len=128)]
+    assert res[0]["losses"] == pytest.approx(single, rel=3e-2)

@@ -101,6 +101,8 @@ class GPT2Engine:
         self.bucket = self.reducer.bucket.tensor[: self.P]
         self.world, self.rank = self.reducer.world, self.reducer.rank
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.attack_scale = torch.ones(1, dtype=torch.float32, device=dev)      # fault-injection hook (1 = honest)
+        self._attack_scale_host = 1.0
         # GPT-2 initialisation (same on every rank: replicas start identical)
         g = torch.Generator(device="cpu").manual_seed(seed)
         for name, (o, shape) in self.offsets.items():
@@ -260,7 +262,7 @@ class GPT2Engine:
         r = self.reducer
         if self.security:
             tensor_statistics_device(self.res[self.L].view(-1), out=self.act_stats)       # K5 on the last residual
-        K.pack_norm(self.g32, self.bucket, r.sumsq)                                       # K1
+        K.pack_norm(self.g32, self.bucket, r.sumsq, self.attack_scale)                    # K1 (+ fault-injection scale)
         if self.security or self.world > 1:
             r.enqueue_reduce(update_trust=self.security)                                  # K2 + K3
         K.adam_tick(self.hyper, self.lr, self.betas[0], self.betas[1])
@@ -299,9 +301,13 @@ class GPT2Engine:
             self._graph.replay()
         self.step_count += 1
 
-    def train_step(self, idx: torch.Tensor, targets: torch.Tensor, **_ignored) -> float:
+    def train_step(self, idx: torch.Tensor, targets: torch.Tensor, attack_scale: float = 1.0, **_ignored) -> float:
         """Public step: ``idx``/``targets`` may live on the host (pinned or not) or the device.
-        Returns the mean loss (one 4-byte D2H read)."""
+        Returns the mean loss (one 4-byte D2H read).  ``attack_scale`` != 1 makes this rank poison its
+        gradient bucket (scale / sign flip) before aggregation — the fault-injection path of the attacker."""
+        if attack_scale != self._attack_scale_host:
+            self.attack_scale.fill_(float(attack_scale))
+            self._attack_scale_host = float(attack_scale)
         if idx.device.type == "cpu":
             self.idx_host.copy_(idx.view(self.B, self.T))
             self.tgt_host.copy_(targets.view(self.B, self.T))

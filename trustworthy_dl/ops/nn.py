@@ -96,8 +96,8 @@ def xent_fwd_bwd(logits, targets, row_loss, loss_sum, V, grad_scale):
               f32(grad_scale), stream_ptr())
 
 
-def pack_norm(src32, dst16, sumsq):
-    _lib.call("tdl_pack_norm", ptr(src32), ptr(dst16), i64(src32.numel()), ptr(sumsq), stream_ptr())
+def pack_norm(src32, dst16, sumsq, scale=None):
+    _lib.call("tdl_pack_norm", ptr(src32), ptr(dst16), i64(src32.numel()), ptr(sumsq), ptr(scale), stream_ptr())
 
 
 def cast_f32_bf16(src, dst):

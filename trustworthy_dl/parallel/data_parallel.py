@@ -67,9 +67,10 @@ class DataParallelStrategy:
             from ..engine.gpt2_engine import GPT2Engine
             self.engine = GPT2Engine.from_module(model, batch_size=max(1, c.batch_size // self.world),
                                                  seq_len=c.seq_len or model.config.n_positions,
-                                                 lr=c.learning_rate, weight_decay=c.weight_decay,
-                                                 world=self.world, rank=self.rank)
+                                                 lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
+                                                 trust_threshold=c.trust_threshold)
             self.reducer = self.engine.reducer
+            t.model_partitions[0] = model
         else:
             self.params = [p for p in model.parameters() if p.requires_grad]
             gdtype = torch.float32
@@ -164,11 +165,49 @@ class DataParallelStrategy:
         return loss
 
     def _engine_step(self, batch, t0) -> float:
-        t = self.t
-        local = self._local_batch(batch)
-        loss = self.engine.train_step(local["input"], local["target"], trust_manager=t.trust_manager,
-                                      attacker=t.attacker, step=t.global_step, trainer=t)
+        """Fused path: the whole step (fwd, bwd, statistics, trust-weighted reduction, trust state machine,
+        AdamW) runs on the device; afterwards the host trust manager / histories are refreshed from the
+        device-resident state (a few hundred bytes) so the public API keeps reporting what happened."""
+        from ..core.trust_manager import NodeStatus, STATUS_CODES
+        t, c = self.t, self.t.config
+        step = t.global_step
+        # static shapes on this path: every rank always processes its own slice; a compromised rank simply gets
+        # coefficient 0 in the reduction (its shard is recorded as reassigned)
+        local = {"input": batch["input"].chunk(self.world)[self.rank], "target": batch["target"].chunk(self.world)[self.rank]}
+        scale = 1.0
+        if t.attacker is not None and t.attacker._armed("gradient_poisoning", step, self.rank):
+            i = t.attacker.config.intensity
+            scale = -(1.0 + 4.0 * i) if t.attacker.config.gradient_mode == "sign_flip" else 1.0 + 20.0 * i
+            t.attacker._record("gradient_poisoning", step, self.rank, mode=t.attacker.config.gradient_mode)
+        loss = self.engine.train_step(local["input"], local["target"], attack_scale=scale)
+        ts = time.perf_counter()
+        snap = self.engine.security_snapshot()
+        trust, status, flags = snap["trust"].tolist(), snap["status"].tolist(), snap["flags"].tolist()
+        tm = t.trust_manager
+        for node in range(self.world):
+            if flags[node] & 1 and tm.get_node_status(node) is not NodeStatus.COMPROMISED:
+                t.attack_history.append({"node_id": node, "timestamp": time.time(), "step": step,
+                                         "attack_type": "gradient_poisoning",
+                                         "gradient_stats": {"total_norm": float(snap["stats"][node, 0]),
+                                                            "cosine_to_median": float(snap["stats"][node, 3])}})
+                tm.attack_history[node].append({"timestamp": tm.clock(), "attack_type": "gradient_poisoning",
+                                                "previous_trust": tm.get_trust_score(node)})
+                t.metrics_collector.record_event("attack", node_id=node, type="gradient_poisoning", step=step)
+                self.reassign(node)
+                from ..core.distributed_trainer import TrainingState
+                t.training_state = TrainingState.UNDER_ATTACK
+            tm._value[node] = trust[node]                   # device state is authoritative on this path
+            tm._status[node] = status[node]
+            tm._count[node] += 1
+        if c.attack_detection_enabled:
+            res = t.attack_detector.observe_stats(snap["act_stats"].numpy(), self.rank, step)
+            if res.is_attack:
+                t.metrics_collector.record_event("output_anomaly", node_id=self.rank, step=step)
+        self._sec_s += time.perf_counter() - ts
         self._step_s += time.perf_counter() - t0
+        t.metrics_collector.collect_batch_metrics({
+            "loss": loss, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
+            "step_time": time.perf_counter() - t0, "samples": batch["input"].numel()})
         return loss
 
     def _deviation(self, node: int, st) -> float:
