@@ -232,6 +232,17 @@ __global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W
     for (int i = 0; i < W; ++i) if (isfinite(norms[i])) srt[k++] = norms[i];
     for (int a = 1; a < k; ++a) { float v = srt[a]; int b = a - 1; while (b >= 0 && srt[b] > v) { srt[b + 1] = srt[b]; --b; } srt[b + 1] = v; }
     const float ref = k ? srt[(k - 1) / 2] : 0.f;
+    // gradient-consistency input of the trust formula is the cosine *relative to the typical rank*: with noisy
+    // mini-batch gradients honest ranks all sit at a modest absolute cosine to the median, and must not lose
+    // trust for that; a rank far below the typical value does.
+    float cs[MAX_W]; int kc = 0;
+    for (int i = 0; i < W; ++i) {
+        const float n = norms[i];
+        const float c0 = (n > 0.f && mn > 0.f) ? (float)(dot[i] / ((double)n * mn)) : 1.f;
+        if (isfinite(c0)) cs[kc++] = c0;
+    }
+    for (int a = 1; a < kc; ++a) { float v = cs[a]; int b = a - 1; while (b >= 0 && cs[b] > v) { cs[b + 1] = cs[b]; --b; } cs[b + 1] = v; }
+    const float med_cos = kc ? cs[(kc - 1) / 2] : 1.f;
     for (int i = 0; i < W; ++i) {
         const float n = norms[i];
         const float cosv = (n > 0.f && mn > 0.f) ? (float)(dot[i] / ((double)n * mn)) : 1.f;
@@ -243,7 +254,7 @@ __global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W
         if (update_trust) {
             if (!ok && status[i] != 2) { trust[i] = tp.penalty; status[i] = 2; fl |= 2; }      // mark_compromised
             const float dev = out_dev != nullptr ? out_dev[i] : 0.f;
-            const float gc = W >= 3 ? fminf(fmaxf(cosv, 0.f), 1.f) : (ok ? 1.f : 0.f);
+            const float gc = !ok ? 0.f : (W >= 3 && med_cos > 0.f ? fminf(fmaxf(cosv / med_cos, 0.f), 1.f) : 1.f);
             const float inst = fminf(fmaxf(tp.w_dev * (1.f - fminf(1.f, dev)) + tp.w_gc * gc + tp.base_score, 0.f), 1.f);
             const float t = fminf(fmaxf((1.f - tp.alpha) * trust[i] + tp.alpha * inst, 0.f), 1.f);
             trust[i] = t;

@@ -144,8 +144,7 @@ class DataParallelStrategy:
         for node in range(self.world):
             st = t._last_step_info["out_stats"].get(node)
             dev = 1.0 if st is None else self._deviation(node, st)
-            gc = float(np.clip(cos[node], 0.0, 1.0)) if self.world >= 3 else \
-                (0.0 if node in t._last_step_info["invalid_nodes"] else 1.0)
+            gc = self._consistency(cos, node, node in t._last_step_info["invalid_nodes"])
             t.trust_manager.update_trust_score(node, dev, gc)
             if st is not None and node not in flagged:
                 t.node_monitor.record_output(node, *st)
@@ -244,6 +243,17 @@ class DataParallelStrategy:
             n += 1
         model.train()
         return total / max(1, n)
+
+    def _consistency(self, cos, node: int, invalid: bool) -> float:
+        """Gradient-consistency trust input: cosine to the median *relative to the typical rank* (noisy honest
+        gradients all have a modest absolute cosine; only a rank far below the typical value is penalised)."""
+        if invalid:
+            return 0.0
+        if self.world < 3:
+            return 1.0
+        fin = np.sort(np.asarray(cos, dtype=np.float64)[np.isfinite(cos)])
+        med = float(fin[(fin.size - 1) // 2]) if fin.size else 1.0
+        return float(np.clip(cos[node] / med, 0.0, 1.0)) if med > 0 else 1.0
 
     def comm_fraction(self) -> float:
         return self._sec_s / self._step_s if self._step_s > 0 else 0.0

@@ -317,8 +317,7 @@ class TensorParallelStrategy:
                     t._last_step_info["invalid_nodes"].add(node)
                     t.handle_gradient_attack(node, [])
         for node in range(self.world):
-            gc = float(np.clip(stats[node, 3], 0.0, 1.0)) if self.world >= 3 else \
-                (0.0 if node in t._last_step_info["invalid_nodes"] else 1.0)
+            gc = self._consistency(stats[:, 3], node, node in t._last_step_info["invalid_nodes"])
             t.trust_manager.update_trust_score(node, 0.0, gc)
         self._sec_s += time.perf_counter() - ts
         if c.clip_norm > 0:
@@ -364,6 +363,17 @@ class TensorParallelStrategy:
             total += float(lt.item())
             n += 1
         return total / max(1, n)
+
+    def _consistency(self, cos, node: int, invalid: bool) -> float:
+        """Gradient-consistency trust input: cosine to the median *relative to the typical rank* (noisy honest
+        gradients all have a modest absolute cosine; only a rank far below the typical value is penalised)."""
+        if invalid:
+            return 0.0
+        if self.world < 3:
+            return 1.0
+        fin = np.sort(np.asarray(cos, dtype=np.float64)[np.isfinite(cos)])
+        med = float(fin[(fin.size - 1) // 2]) if fin.size else 1.0
+        return float(np.clip(cos[node] / med, 0.0, 1.0)) if med > 0 else 1.0
 
     def comm_fraction(self) -> float:
         return self._sec_s / self._step_s if self._step_s > 0 else 0.0
