@@ -147,15 +147,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
         tmem_ld_wait();
+        // causal mask only exists in the diagonal block: fold it into the scores there (one FSEL per element,
+        // warp-uniform branch) so the common path carries no predicate arithmetic at all
+        if (diag) {
+#pragma unroll
+            for (int i = 0; i < 128; ++i) if (i > r) sraw[i] = 0xff800000u;           // -inf
+        }
         // four independent chains: a single running max/sum would serialise 128 dependent ops
         float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-        if (!diag) {
 #pragma unroll
-            for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-        } else {
-#pragma unroll
-            for (int i = 0; i < 128; ++i) if (i <= r) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-        }
+        for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
         const float mraw = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         const float mx = fmaxf(m_run, mraw * p.scale_log2);
         const float alpha = exp2f(m_run - mx);
@@ -165,8 +166,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
             float pv[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));
-                if (diag && (c * 32 + i) > r) e = 0.f;
+                const float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));   // exp2(-inf) = 0 under the mask
                 pv[i] = e;
                 rs4[i & 3] += e;
             }
@@ -376,11 +376,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
             tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
             tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
             tmem_ld_wait();
+            if (diag) {                                   // causal mask only in the diagonal block (warp-uniform)
+#pragma unroll
+                for (int k = 0; k < 32; ++k) if ((c * 32 + k) > r) rs_[k] = 0xff800000u;   // -inf -> P = 0
+            }
             float pv[32], dsv[32];
 #pragma unroll
             for (int k = 0; k < 32; ++k) {
-                float e = exp2f(fmaf(__uint_as_float(rs_[k]), p.scale_log2, -lse2));
-                if (diag && (c * 32 + k) > r) e = 0.f;
+                const float e = exp2f(fmaf(__uint_as_float(rs_[k]), p.scale_log2, -lse2));
                 pv[k] = e;
                 dsv[k] = e * (__uint_as_float(rd_[k]) - dlt);
             }

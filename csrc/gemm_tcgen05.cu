@@ -316,6 +316,244 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid
     }
 }
 
+
+// =================================================================================================
+// 2-CTA variant: a cluster of two CTAs (one TPC) computes a 256 x BLOCK_N tile with cta_group::2 MMAs.
+// Each CTA stages its own 128 rows of A and only HALF of the B tile (the tensor core reads the other half
+// from the peer's shared memory), so L2->SM traffic per FLOP drops by a third and a stage shrinks from
+// 48 KB to 32 KB (6 stages instead of 4 in flight).  Only the leader CTA (cluster rank 0) issues MMAs; both
+// CTAs run TMA producers (their transaction bytes land on the leader's `full` barrier) and epilogues (each
+// drains its own 128 TMEM lanes).  tcgen05.commit multicasts the `empty` / `tmem_full` arrivals to both CTAs.
+// =================================================================================================
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same smem offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+        :: "r"(smem_u32(bar)), "r"(cta) : "memory");
+}
+// TMA load whose completion bytes are credited to the LEADER CTA's barrier (peer bit cleared)
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    const uint32_t mbar = smem_u32(bar) & 0xFEFFFFFFu;
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(mbar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {      // arrives on `bar` in both CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)) : "memory");
+}
+
+template <int BLOCK_N, int STAGES_> struct Cfg2 {
+    static constexpr int STAGES = STAGES_;
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;                 // this CTA's 128 rows
+    static constexpr int B_BYTES = (BLOCK_N / 2) * BLOCK_K * 2;           // this CTA's half of the B tile
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TMEM_COLS = 2 * BLOCK_N;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <int BLOCK_N, int STAGES_>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
+                              const __grid_constant__ GemmParams p) {
+    using C = Cfg2<BLOCK_N, STAGES_>;
+    const CUtensorMap& tmap_a = tmaps_a.m[0];
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;                       // used in the leader only
+    uint64_t* empty = bars + C::STAGES;          // one per CTA
+    uint64_t* tmem_full = bars + 2 * C::STAGES;  // one per CTA
+    uint64_t* tmem_empty = tmem_full + 2;        // used in the leader only
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta = cluster_ctarank();
+    const bool leader = cta == 0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int i = 1; i < p.a_shards; ++i) tma_prefetch_desc(&tmaps_a.m[i]);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], 2); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 16); }
+        fence_barrier_init();
+    }
+    cluster_sync_all();                          // peers' barriers exist before anyone arrives remotely
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(tmem_slot)), "r"(C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int m_blocks2 = (p.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+    const int tiles_mn = m_blocks2 * p.n_blocks;
+    const int total_work = tiles_mn * p.split_k;
+    const int total_k_blocks = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    const int m2_offset = p.m_block_offset >> 1;
+
+    if (warp == 0) {
+        // ================================ TMA producer (both CTAs) ================================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int w = cluster_id; w < total_work; w += n_clusters) {
+                const int split = w / tiles_mn, t = w % tiles_mn;
+                int m2 = t / p.n_blocks + m2_offset;
+                if (m2 >= m_blocks2) m2 -= m_blocks2;
+                const int m_idx = m2 * 2 * BLOCK_M + (int)cta * BLOCK_M;
+                const int n_idx = (t % p.n_blocks) * BLOCK_N + (int)cta * (BLOCK_N / 2);
+                const CUtensorMap* ta = &tmap_a;
+                int m_local = m_idx;
+                if (p.a_shards > 1) {
+                    const int sh = m_idx / p.a_shard_rows;
+                    ta = &tmaps_a.m[sh < p.a_shards ? sh : p.a_shards - 1];
+                    m_local = m_idx - sh * p.a_shard_rows;
+                }
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+                    else mbar_arrive_remote(&full[stage], 0);
+                    uint8_t* sa = smem_a + stage * C::A_BYTES;
+                    uint8_t* sb = smem_b + stage * C::B_BYTES;
+                    if (!p.a_mn_major) {
+                        tma_load_2d_2sm(sa, ta, &full[stage], kb * BLOCK_K, m_local);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_M / 64; ++j)
+                            tma_load_2d_2sm(sa + j * (BLOCK_K * 128), &tmap_a, &full[stage], m_idx + j * 64, kb * BLOCK_K);
+                    }
+                    if (!p.b_mn_major) {
+                        tma_load_2d_2sm(sb, &tmap_b, &full[stage], kb * BLOCK_K, n_idx);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_N / 2 / 64; ++j)
+                            tma_load_2d_2sm(sb + j * (BLOCK_K * 128), &tmap_b, &full[stage], n_idx + j * 64, kb * BLOCK_K);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer (leader CTA only) ============================
+        if (leader) {
+            const uint32_t idesc = umma_idesc_bf16(2 * BLOCK_M, BLOCK_N, p.a_mn_major, p.b_mn_major);
+            const uint32_t a_kstep = p.a_mn_major ? UMMA_K * 128 : UMMA_K * 2;
+            const uint32_t b_kstep = p.b_mn_major ? UMMA_K * 128 : UMMA_K * 2;
+            const uint32_t a_lbo = p.a_mn_major ? BLOCK_K * 128 : 16;
+            const uint32_t b_lbo = p.b_mn_major ? BLOCK_K * 128 : 16;
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int w = cluster_id; w < total_work; w += n_clusters) {
+                const int split = w / tiles_mn;
+                const int kb0 = split * p.k_blocks_per_split;
+                const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = smem_u32(smem_a + stage * C::A_BYTES);
+                        const uint32_t sb = smem_u32(smem_b + stage * C::B_BYTES);
+#pragma unroll
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+                            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+                            umma_bf16_ss_2cta(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit_2cta(&empty[stage]);
+                        if (kb == kb1 - 1) umma_commit_2cta(&tmem_full[acc]);
+                    }
+                    __syncwarp();
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ================================ epilogue (both CTAs) ====================================
+        const int e = warp - 2;
+        const int quarter = warp & 3;
+        const int half = e >> 2;
+        constexpr int NC = BLOCK_N / 64;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int w = cluster_id; w < total_work; w += n_clusters) {
+            const int t = w % tiles_mn;
+            int m2 = t / p.n_blocks + m2_offset;
+            if (m2 >= m_blocks2) m2 -= m_blocks2;
+            const int m_idx = m2 * 2 * BLOCK_M + (int)cta * BLOCK_M;
+            const int n_idx = (t % p.n_blocks) * BLOCK_N + half * (BLOCK_N / 2);
+            const int row = m_idx + quarter * 32 + lane;
+            const bool row_ok = row < p.M;
+            uint4 aux[2][4];
+            load_aux(p, row, n_idx, row_ok && n_idx < p.N, aux[0]);
+            mbar_wait(&tmem_full[acc], acc_phase);
+            __syncwarp();
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + half * (BLOCK_N / 2);
+            uint32_t r[2][32];
+            tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                tmem_ld_wait();
+                if (c + 1 < NC) {
+                    tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    load_aux(p, row, n_idx + (c + 1) * 32, row_ok && n_idx + (c + 1) * 32 < p.N, aux[(c + 1) & 1]);
+                } else {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (leader) mbar_arrive(&tmem_empty[acc]);
+                        else mbar_arrive_remote(&tmem_empty[acc], 0);
+                    }
+                }
+                const int col0 = n_idx + c * 32;
+                if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r[c & 1], aux[c & 1]);
+                __syncwarp();
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(C::TMEM_COLS) : "memory");
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -372,6 +610,24 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
     return 0;
 }
 
+template <int BLOCK_N, int STAGES_>
+static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
+    using C = Cfg2<BLOCK_N, STAGES_>;
+    static bool configured = false;
+    if (!configured) {
+        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        configured = true;
+    }
+    const int m_blocks2 = (p.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+    const int work = m_blocks2 * p.n_blocks * p.split_k;
+    const int max_clusters = tdl_num_sms() / 2;
+    const int clusters = work < max_clusters ? work : max_clusters;
+    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
 static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_shard_rows, int m_block_offset,
                        const void* B, void* Cout, void* const* c_ptrs, int c_scatter, int64_t c_shard_rows, int c_src_slot,
                        int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
@@ -386,6 +642,19 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     p.m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M);
     p.n_blocks = (int)((N + block_n - 1) / block_n);
     const int kblocks = (int)((K + BLOCK_K - 1) / BLOCK_K);
+    if (split_k <= 0 && out_f32_atomic) {
+        // auto split-K: pick the split whose work-unit count fills whole waves of the persistent grid
+        // (74 CTA pairs for 256-row tiles), keeping at least 16 k-blocks per unit; ties go to the smaller split
+        const bool pair = block_n == 256 && M >= 512;
+        const int units = pair ? tdl_num_sms() / 2 : tdl_num_sms();
+        const int tiles = (int)((M + (pair ? 255 : 127)) / (pair ? 256 : 128)) * p.n_blocks;
+        double best = -1.0;
+        for (int sk = 1; sk <= 16 && kblocks / sk >= 16; ++sk) {
+            const int work = tiles * sk;
+            const double eff = (double)work / (double)(((work + units - 1) / units) * units);
+            if (eff > best + 0.02) { best = eff; split_k = sk; }
+        }
+    }
     if (split_k < 1) split_k = 1;
     if (split_k > kblocks) split_k = kblocks;
     TDL_REQUIRE(split_k == 1 || out_f32_atomic, "split-K needs the fp32 atomic epilogue");
@@ -419,10 +688,17 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         rc = tdl_make_tmap_2d_bf16(&ta.m[0], a_shard_ptrs[0], (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BLOCK_K);
     }
     if (rc) return rc;
-    if (!b_mn_major) rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, (uint32_t)block_n);
+    // 2-CTA (cta_group::2) path: 256-row tiles; chosen when M is large enough to keep all SM pairs busy
+    static int use_2cta = -1;
+    if (use_2cta < 0) { const char* e = getenv("TDL_GEMM_2CTA"); use_2cta = e ? atoi(e) : 1; }
+    const bool two_cta = use_2cta && block_n == 256 && M >= 512 && (a_shards <= 1 || a_shard_rows % 256 == 0) &&
+                         (p.m_block_offset % 2 == 0);
+    const uint32_t b_box_rows = two_cta ? (uint32_t)block_n / 2 : (uint32_t)block_n;
+    if (!b_mn_major) rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, b_box_rows);
     else             rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BLOCK_K);
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (two_cta) return launch_gemm_2cta<256, 6>(ta, tb, p, s);
     static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
     if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
     if (block_n == 256) return exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);

@@ -214,9 +214,8 @@ class GPT2Engine:
         self.loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
     def _split_k(self, n_out: int, k_in: int) -> int:
-        tiles = ((n_out + 127) // 128) * ((k_in + 255) // 256)
-        want = max(1, (2 * 148 + tiles - 1) // tiles)
-        return int(min(want, 16, max(1, self.M // 64 // 8)))
+        """0 = let the kernel library choose the split that fills whole waves of the persistent grid."""
+        return 0
 
     # ------------------------------------------------------------------ forward / backward
     def _forward(self) -> None:
