@@ -119,21 +119,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     float m_run = -INFINITY, l_run = 0.f;
     const int r = tid;                               // query row inside the tile
 
+    // S(j+1) = Q K_{j+1}^T is queued on the tensor pipe right behind P_j V_j (the S accumulator is already in
+    // registers by then), so the next block's scores are ready when the softmax warps come back for them.
+    auto issue_s = [&](int jj) {                     // thread 0 only
+        const int b2 = jj & 1;
+        mbar_wait(&bar_kv[b2], (jj >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+            umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + b2 * TILE_BYTES, k), idesc_s, k > 0);
+        umma_commit(bar_s);
+    };
+    if (tid == 0) { mbar_wait(bar_q, 0); issue_s(0); }
     for (int j = 0; j < n_kv; ++j) {
         const int buf = j & 1;
-        if (tid == 0) {
-            if (j + 1 < n_kv) {                      // prefetch next K/V into the other buffer
-                mbar_arrive_expect_tx(&bar_kv[buf ^ 1], 2 * TILE_BYTES);
-                tma_load_2d(sK + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], p.C + h * D, row0 + (j + 1) * BK);
-                tma_load_2d(sV + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], 2 * p.C + h * D, row0 + (j + 1) * BK);
-            }
-            if (j == 0) mbar_wait(bar_q, 0);
-            mbar_wait(&bar_kv[buf], (j >> 1) & 1);
-            tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < D / 16; ++k)
-                umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + buf * TILE_BYTES, k), idesc_s, k > 0);
-            umma_commit(bar_s);
+        if (tid == 0 && j + 1 < n_kv) {              // prefetch next K/V into the other buffer
+            mbar_arrive_expect_tx(&bar_kv[buf ^ 1], 2 * TILE_BYTES);
+            tma_load_2d(sK + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], p.C + h * D, row0 + (j + 1) * BK);
+            tma_load_2d(sV + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], 2 * p.C + h * D, row0 + (j + 1) * BK);
         }
         mbar_wait(bar_s, j & 1);
         __syncwarp();
@@ -188,6 +191,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
                 umma_bf16_ss(tmem_o, desc_kmajor(sP + (k >> 2) * TILE_BYTES, k & 3),
                              desc_mnmajor(sV + buf * TILE_BYTES, k, TILE_BYTES), idesc_o, k > 0);
             umma_commit(bar_o);
+            if (j + 1 < n_kv) issue_s(j + 1);
         }
         mbar_wait(bar_o, j & 1);
         __syncwarp();
@@ -334,6 +338,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
         delta_fix = p.delta[idx];
     }
 
+    // S and dP of iteration it+1 are queued right behind the accumulate-MMAs of iteration it (thread 0 only)
+    auto issue_sdp = [&](int it2) {
+        const int b2 = it2 & 1;
+        uint8_t* q0 = sStr + b2 * 2 * TILE_BYTES;
+        const uint8_t* xQ = MODE == 0 ? q0 : sFix0;
+        const uint8_t* xdO = MODE == 0 ? q0 + TILE_BYTES : sFix1;
+        const uint8_t* xK = MODE == 0 ? sFix0 : q0;
+        const uint8_t* xV = MODE == 0 ? sFix1 : q0 + TILE_BYTES;
+        mbar_wait(&bar_str[b2], (it2 >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_s, desc_kmajor(xQ, k), desc_kmajor(xK, k), idesc_s, k > 0);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(xdO, k), desc_kmajor(xV, k), idesc_s, k > 0);
+        umma_commit(bar_s);
+    };
     int it = 0;
     for (int i = i_begin; i < i_end; ++i, ++it) {
         const int buf = it & 1;
@@ -344,16 +364,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
         const uint8_t* tdO = MODE == 0 ? s1 : sFix1;
         const uint8_t* tK = MODE == 0 ? sFix0 : s0;
         const uint8_t* tV = MODE == 0 ? sFix1 : s1;
-        if (tid == 0) {
-            if (it == 0) mbar_wait(bar_fix, 0);
-            mbar_wait(&bar_str[buf], (it >> 1) & 1);
-            tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_s, desc_kmajor(tQ, k), desc_kmajor(tK, k), idesc_s, k > 0);
-#pragma unroll
-            for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(tdO, k), desc_kmajor(tV, k), idesc_s, k > 0);
-            umma_commit(bar_s);
-        }
+        if (tid == 0 && it == 0) { mbar_wait(bar_fix, 0); issue_sdp(0); }
         // the previous iteration's accumulate-MMAs must be done before P/dS (and the other stream
         // buffer) are overwritten
         if (it > 0) { mbar_wait(bar_acc, (it - 1) & 1); tc_fence_after(); }
@@ -410,6 +421,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
                     umma_bf16_ss(tmem_a0, desc_kmajor(sdS + (k >> 2) * TILE_BYTES, k & 3), desc_mnmajor(tK, k, TILE_BYTES), idesc_dq, (it > 0 || k > 0));
             }
             umma_commit(bar_acc);
+            if (i + 1 < i_end) issue_sdp(it + 1);
         }
     }
     // ---- write the accumulators ------------------------------------------------------------------

@@ -361,31 +361,54 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {      // arrive
                  :: "r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)) : "memory");
 }
 
-template <int BLOCK_N, int STAGES_> struct Cfg2 {
+constexpr int PANEL_BYTES = 128 * 64 * 2;        // one [128 rows x 64 cols] bf16 staging panel (128B-swizzled)
+
+template <int BLOCK_N, int STAGES_, bool AUX> struct Cfg2 {
     static constexpr int STAGES = STAGES_;
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;                 // this CTA's 128 rows
     static constexpr int B_BYTES = (BLOCK_N / 2) * BLOCK_K * 2;           // this CTA's half of the B tile
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = 2 * BLOCK_N;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    // epilogue staging: one output panel per column half (+ one aux panel per half when the epilogue reads or
+    // writes a second tensor); the output leaves through TMA stores, aux_in arrives through TMA loads
+    static constexpr int STAGING_BYTES = (AUX ? 4 : 2) * PANEL_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 + 256;
 };
 
-template <int BLOCK_N, int STAGES_>
+struct EpiMaps { CUtensorMap c, aux; };
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+// byte offset of 16-byte piece q8 (0..7) of row r in a 128B-swizzled [rows x 64] bf16 panel
+__device__ __forceinline__ uint32_t panel_off(uint32_t r, uint32_t q8) { return r * 128u + ((q8 ^ (r & 7u)) << 4); }
+
+
+template <int BLOCK_N, int STAGES_, bool AUX>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
-                              const __grid_constant__ GemmParams p) {
-    using C = Cfg2<BLOCK_N, STAGES_>;
+                              const __grid_constant__ EpiMaps emaps, const __grid_constant__ GemmParams p) {
+    using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     const CUtensorMap& tmap_a = tmaps_a.m[0];
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;                 // [half][out | aux] panels
+    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
     uint64_t* full = bars;                       // used in the leader only
     uint64_t* empty = bars + C::STAGES;          // one per CTA
     uint64_t* tmem_full = bars + 2 * C::STAGES;  // one per CTA
     uint64_t* tmem_empty = tmem_full + 2;        // used in the leader only
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* aux_bar = tmem_empty + 2;          // [2]: aux_in panel landed (one per column half)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -397,7 +420,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
         tma_prefetch_desc(&tmap_b);
         for (int i = 1; i < p.a_shards; ++i) tma_prefetch_desc(&tmaps_a.m[i]);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], 2); mbar_init(&empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 16); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 16); mbar_init(&aux_bar[s], 1); }
         fence_barrier_init();
     }
     cluster_sync_all();                          // peers' barriers exist before anyone arrives remotely
@@ -506,6 +529,15 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
         const int quarter = warp & 3;
         const int half = e >> 2;
         constexpr int NC = BLOCK_N / 64;
+        const bool staged = !p.out_f32_atomic && !p.c_scatter;          // coalesced path: smem panels + TMA
+        const bool aux_in = AUX && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU);
+        const bool aux_out = AUX && p.epilogue == EPI_GELU;
+        uint8_t* out_panel = staging + half * (AUX ? 2 : 1) * PANEL_BYTES;
+        uint8_t* aux_panel = out_panel + PANEL_BYTES;                   // only dereferenced when AUX
+        const bool group_leader = (e & 3) == 0 && lane == 0;            // one thread per column half issues TMA
+        const int bar_id = 1 + half;
+        const uint32_t lrow = quarter * 32 + lane;                      // row inside the 128-row tile
+        uint32_t aux_phase = 0;
         int acc = 0; uint32_t acc_phase = 0;
         for (int w = cluster_id; w < total_work; w += n_clusters) {
             const int t = w % tiles_mn;
@@ -515,34 +547,145 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
             const int n_idx = (t % p.n_blocks) * BLOCK_N + half * (BLOCK_N / 2);
             const int row = m_idx + quarter * 32 + lane;
             const bool row_ok = row < p.M;
-            uint4 aux[2][4];
-            load_aux(p, row, n_idx, row_ok && n_idx < p.N, aux[0]);
-            mbar_wait(&tmem_full[acc], acc_phase);
-            __syncwarp();
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + half * (BLOCK_N / 2);
-            uint32_t r[2][32];
-            tmem_ld_32x32(taddr, r[0]);
+            if (!staged) {
+                // ---- direct path (split-K atomics, scatter to peers): per-thread global accesses -----------
+                uint4 aux[2][4];
+                load_aux(p, row, n_idx, row_ok && n_idx < p.N, aux[0]);
+                mbar_wait(&tmem_full[acc], acc_phase);
+                __syncwarp();
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + half * (BLOCK_N / 2);
+                uint32_t r[2][32];
+                tmem_ld_32x32(taddr, r[0]);
 #pragma unroll
-            for (int c = 0; c < NC; ++c) {
-                tmem_ld_wait();
-                if (c + 1 < NC) {
-                    tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-                    load_aux(p, row, n_idx + (c + 1) * 32, row_ok && n_idx + (c + 1) * 32 < p.N, aux[(c + 1) & 1]);
-                } else {
-                    tc_fence_before();
+                for (int c = 0; c < NC; ++c) {
+                    tmem_ld_wait();
+                    if (c + 1 < NC) {
+                        tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                        load_aux(p, row, n_idx + (c + 1) * 32, row_ok && n_idx + (c + 1) * 32 < p.N, aux[(c + 1) & 1]);
+                    } else {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (leader) mbar_arrive(&tmem_empty[acc]);
+                            else mbar_arrive_remote(&tmem_empty[acc], 0);
+                        }
+                    }
+                    const int col0 = n_idx + c * 32;
+                    if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r[c & 1], aux[c & 1]);
                     __syncwarp();
-                    if (lane == 0) {
-                        if (leader) mbar_arrive(&tmem_empty[acc]);
-                        else mbar_arrive_remote(&tmem_empty[acc], 0);
+                }
+            } else {
+                // ---- staged path: 2 panels of 64 columns per half; outputs leave by TMA store, aux_in arrives by
+                //      TMA load into the aux panel (issued before the accumulator is even ready) -------------
+                if (aux_in && group_leader) {
+                    mbar_arrive_expect_tx(&aux_bar[half], PANEL_BYTES);
+                    tma_load_2d(aux_panel, &emaps.aux, &aux_bar[half], n_idx, m_idx);
+                }
+                mbar_wait(&tmem_full[acc], acc_phase);
+                __syncwarp();
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + half * (BLOCK_N / 2);
+                uint32_t r[2][32];
+                tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    const int pi = c >> 1, cc = c & 1;                  // panel index, 32-col chunk inside the panel
+                    tmem_ld_wait();
+                    if (c + 1 < NC) {
+                        tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+                    } else {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (leader) mbar_arrive(&tmem_empty[acc]);
+                            else mbar_arrive_remote(&tmem_empty[acc], 0);
+                        }
+                    }
+                    const int col0 = n_idx + c * 32;
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[c & 1][j]);
+                    if (p.bias != nullptr && col0 < p.N) {
+                        if (p.bias_f32) {
+                            const float4* bp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 tb4 = __ldg(bp + q);
+                                v[q * 4 + 0] += tb4.x; v[q * 4 + 1] += tb4.y; v[q * 4 + 2] += tb4.z; v[q * 4 + 3] += tb4.w;
+                            }
+                        } else {
+                            const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const uint4 u = __ldg(bp + q);
+                                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                                v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
+                                v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
+                            }
+                        }
+                    }
+                    if (cc == 0) {
+                        // the panel buffers are about to be rewritten: the previous TMA stores must have read them
+                        if (group_leader) tma_store_wait_read();
+                        if (aux_in) mbar_wait(&aux_bar[half], aux_phase);
+                        named_bar_sync(bar_id, 128);
+                    }
+                    if (aux_in) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint4 u = *reinterpret_cast<const uint4*>(aux_panel + panel_off(lrow, cc * 4 + q));
+                            const float2 f[4] = {unpack_bf16x2(u.x), unpack_bf16x2(u.y), unpack_bf16x2(u.z), unpack_bf16x2(u.w)};
+#pragma unroll
+                            for (int e2 = 0; e2 < 4; ++e2) {
+                                if (p.epilogue == EPI_RESIDUAL) {
+                                    v[q * 8 + 2 * e2] += f[e2].x; v[q * 8 + 2 * e2 + 1] += f[e2].y;
+                                } else {
+                                    v[q * 8 + 2 * e2] *= gelu_tanh_grad_f(f[e2].x); v[q * 8 + 2 * e2 + 1] *= gelu_tanh_grad_f(f[e2].y);
+                                }
+                            }
+                        }
+                    }
+                    if (aux_out) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 u;
+                            u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                            u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                            *reinterpret_cast<uint4*>(aux_panel + panel_off(lrow, cc * 4 + q)) = u;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        uint4 u;
+                        u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                        u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                        *reinterpret_cast<uint4*>(out_panel + panel_off(lrow, cc * 4 + q)) = u;
+                    }
+                    if (cc == 1) {
+                        fence_proxy_async_smem();                       // generic-proxy writes -> visible to TMA
+                        named_bar_sync(bar_id, 128);
+                        if (group_leader) {
+                            const int pc = n_idx + pi * 64;
+                            if (pc < p.N) {
+                                tma_store_2d(&emaps.c, out_panel, pc, m_idx);
+                                if (aux_out) tma_store_2d(&emaps.aux, aux_panel, pc, m_idx);
+                            }
+                            tma_store_commit();
+                            if (aux_in && pi + 1 < NC / 2) {            // next panel's aux tile (aux panel is free: all 4 warps passed the barrier)
+                                mbar_arrive_expect_tx(&aux_bar[half], PANEL_BYTES);
+                                tma_load_2d(aux_panel, &emaps.aux, &aux_bar[half], pc + 64, m_idx);
+                            }
+                        }
+                        if (aux_in) aux_phase ^= 1;
                     }
                 }
-                const int col0 = n_idx + c * 32;
-                if (row_ok && col0 < p.N) epilogue_chunk(p, row, col0, r[c & 1], aux[c & 1]);
-                __syncwarp();
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (staged && group_leader) tma_store_wait_all();
     }
 
     tc_fence_before();
@@ -610,12 +753,12 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
     return 0;
 }
 
-template <int BLOCK_N, int STAGES_>
-static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
-    using C = Cfg2<BLOCK_N, STAGES_>;
+template <int BLOCK_N, int STAGES_, bool AUX>
+static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const EpiMaps& em, GemmParams& p, cudaStream_t stream) {
+    using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     static bool configured = false;
     if (!configured) {
-        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_>,
+        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured = true;
     }
@@ -623,7 +766,7 @@ static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, GemmPara
     const int work = m_blocks2 * p.n_blocks * p.split_k;
     const int max_clusters = tdl_num_sms() / 2;
     const int clusters = work < max_clusters ? work : max_clusters;
-    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, em, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -698,7 +841,22 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     else             rc = tdl_make_tmap_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BLOCK_K);
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if (two_cta) return launch_gemm_2cta<256, 6>(ta, tb, p, s);
+    if (two_cta) {
+        EpiMaps em;
+        const bool staged = !out_f32_atomic && !c_scatter;
+        const bool needs_aux = epilogue != EPI_NONE;
+        if (staged) {
+            rc = tdl_make_tmap_2d_bf16(&em.c, Cout, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 128);
+            if (rc) return rc;
+            const void* auxp = epilogue == EPI_GELU ? aux_out : aux_in;
+            rc = tdl_make_tmap_2d_bf16(&em.aux, needs_aux ? auxp : Cout, (uint64_t)N, (uint64_t)M, (uint64_t)(needs_aux ? ld_aux : ldc), 64, 128);
+            if (rc) return rc;
+        } else {
+            em.c = tb; em.aux = tb;                     // unused on the direct path
+        }
+        return (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, p, s)
+                                     : launch_gemm_2cta<256, 6, false>(ta, tb, em, p, s);
+    }
     static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
     if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
     if (block_n == 256) return exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
