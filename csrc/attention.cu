@@ -18,6 +18,7 @@
 //   dQ kernel      one CTA per query block, loops over key blocks; dQ += dS K
 // The reference reaches attention only through torch/HF eager ops.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -222,6 +223,242 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 
     __syncthreads();
     if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+}
+
+// =================================================================================================
+// forward, warp-specialised ping-pong version (used when T/128 is even)
+//
+// One CTA (320 threads, 1 per SM) owns TWO query tiles of one head: blocks i and nblk-1-i, so every CTA does
+// the same causal work (nblk+1 key blocks) and both tiles share each K/V block it loads.
+//   warps 0-3  softmax warpgroup of tile A          warps 4-7  softmax warpgroup of tile B
+//   warp 8     MMA issuer (one lane)                warp 9     TMA producer (one lane)
+// While one warpgroup runs exp on its scores the tensor core computes the other tile's S = QK^T and PV, and
+// S_t(j+1) is issued as soon as the warpgroup has pulled S_t(j) into registers.  O accumulates in TMEM across
+// key blocks (tcgen05.mma accumulate); the running max is only refreshed when it grows by more than 2^8
+// ("lazy rescale"), in which case the warpgroup scales its O tile in TMEM (tcgen05.ld / st) before the next PV.
+// TMEM: S_A [0,128) S_B [128,256) O_A [256,320) O_B [320,384).  smem: Q x2, 3 K/V stages, P x2 = 192 KB.
+// =================================================================================================
+constexpr int WS_NST = 3;
+constexpr int WS_THREADS = 320;
+
+__global__ void __launch_bounds__(WS_THREADS, 1)
+attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;                                   // [2] tiles
+    uint8_t* sKV = smem + 2 * TILE_BYTES;                 // [WS_NST][K | V]
+    uint8_t* sP = smem + (2 + 2 * WS_NST) * TILE_BYTES;   // [2][128 x 128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 + 2 * WS_NST + 4) * TILE_BYTES);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;
+    uint64_t* kv_empty = bars + 1 + WS_NST;
+    uint64_t* s_full = bars + 1 + 2 * WS_NST;
+    uint64_t* s_free = s_full + 2;
+    uint64_t* p_full = s_free + 2;
+    uint64_t* o_done = p_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nblk = p.T / 128;
+    const int pi = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+    const int qblk0 = pi, qblk1 = nblk - 1 - pi;          // tile A / tile B query blocks
+    const int nkv0 = pi + 1, nkv1 = nblk - pi;            // causal key-block counts
+    const int nmax = nkv1;
+    const int row0 = b * p.T;
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        tma_prefetch_desc(&tmap_qkv);
+        mbar_init(q_full, 1);
+        for (int s2 = 0; s2 < WS_NST; ++s2) { mbar_init(&kv_full[s2], 1); mbar_init(&kv_empty[s2], 1); }
+        for (int t = 0; t < 2; ++t) { mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 4); mbar_init(&p_full[t], 4); mbar_init(&o_done[t], 1); }
+        fence_barrier_init();
+    }
+    if (warp == 8) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 9) {
+        // ===================================== TMA producer =====================================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, 2 * TILE_BYTES);
+            tma_load_2d(sQ, &tmap_qkv, q_full, h * D, row0 + qblk0 * 128);
+            tma_load_2d(sQ + TILE_BYTES, &tmap_qkv, q_full, h * D, row0 + qblk1 * 128);
+            for (int j = 0; j < nmax; ++j) {
+                const int st = j % WS_NST;
+                mbar_wait(&kv_empty[st], ((j / WS_NST) & 1) ^ 1);
+                mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
+                tma_load_2d(sKV + st * 2 * TILE_BYTES, &tmap_qkv, &kv_full[st], p.C + h * D, row0 + j * 128);
+                tma_load_2d(sKV + st * 2 * TILE_BYTES + TILE_BYTES, &tmap_qkv, &kv_full[st], 2 * p.C + h * D, row0 + j * 128);
+            }
+        }
+    } else if (warp == 8) {
+        // ===================================== MMA issuer ========================================
+        if (lane == 0) {
+            const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+            const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+            auto issue_s = [&](int t, int j) {
+                const uint8_t* kt = sKV + (j % WS_NST) * 2 * TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16_ss(tmem + t * 128, desc_kmajor(sQ + t * TILE_BYTES, k), desc_kmajor(kt, k), idesc_s, k > 0);
+                umma_commit(&s_full[t]);
+            };
+            auto issue_pv = [&](int t, int j) {
+                const uint8_t* vt = sKV + (j % WS_NST) * 2 * TILE_BYTES + TILE_BYTES;
+                const uint8_t* pt = sP + t * 2 * TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16_ss(tmem + 256 + t * 64, desc_kmajor(pt + (k >> 2) * TILE_BYTES, k & 3),
+                                 desc_mnmajor(vt, k, TILE_BYTES), idesc_o, (j > 0 || k > 0));
+                umma_commit(&o_done[t]);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_s(0, 0);
+            issue_s(1, 0);
+            // Event-driven issue: whichever tile has something ready (its S row has been pulled out of TMEM, or its
+            // P tile has been written) is served first, so the two warpgroups genuinely alternate instead of marching
+            // in lock-step behind one blocking wait.
+            int js[2] = {1, 1};                                  // next S block to issue per tile
+            int jp[2] = {0, 0};                                  // next PV block to issue per tile
+            const int nt[2] = {nkv0, nkv1};
+            int kv_ready = 1;                                    // K/V blocks known to have landed
+            while (jp[0] < nt[0] || jp[1] < nt[1]) {
+#pragma unroll
+                for (int t = 0; t < 2; ++t) {
+                    if (js[t] < nt[t]) {
+                        const int j = js[t];
+                        if (kv_ready <= j && mbar_try_wait(&kv_full[j % WS_NST], (j / WS_NST) & 1)) kv_ready = j + 1;
+                        if (kv_ready > j && mbar_try_wait(&s_free[t], (j - 1) & 1)) {
+                            tc_fence_after();
+                            issue_s(t, j);
+                            ++js[t];
+                        }
+                    }
+                    if (jp[t] < nt[t] && mbar_try_wait(&p_full[t], jp[t] & 1)) {
+                        const int j = jp[t];
+                        tc_fence_after();
+                        issue_pv(t, j);
+                        ++jp[t];
+                        const int o = t ^ 1;
+                        if (jp[o] > j || nt[o] <= j) umma_commit(&kv_empty[j % WS_NST]);   // both tiles are past block j
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================================== softmax warpgroups ================================
+        const int t = warp >> 2;
+        const int r = (warp & 3) * 32 + lane;
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        const uint32_t tmem_s = tmem + t * 128, tmem_o = tmem + 256 + t * 64;
+        uint8_t* myP = sP + t * 2 * TILE_BYTES;
+        float m_ref = -INFINITY, l_run = 0.f;
+        const int n = t == 0 ? nkv0 : nkv1;
+        const int my_qblk = t == 0 ? qblk0 : qblk1;
+        for (int j = 0; j < n; ++j) {
+            const bool diag = (j == n - 1);
+            mbar_wait(&s_full[t], j & 1);
+            __syncwarp();
+            tc_fence_after();
+            // ---- pass 1 over the S row (32 columns at a time, next chunk in flight): row max ------------
+            uint32_t raw[2][32];
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            tmem_ld_32x32(tmem_s + lane_base, raw[0]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld_wait();
+                if (c + 1 < 4) tmem_ld_32x32(tmem_s + lane_base + (c + 1) * 32, raw[(c + 1) & 1]);
+                if (diag) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) if (c * 32 + i > r) raw[c & 1][i] = 0xff800000u;
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(raw[c & 1][i]));
+            }
+            const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2;
+            float alpha = 1.f;
+            if (m_blk > m_ref + 8.f) { alpha = exp2f(m_ref - m_blk); m_ref = m_blk; }   // lazy: p stays <= 2^8 otherwise
+            const bool any_rescale = __any_sync(0xffffffffu, alpha != 1.f);
+            if (j > 0) {                                         // PV_t(j-1) must be done before P / O are touched
+                mbar_wait(&o_done[t], (j - 1) & 1);
+                __syncwarp();
+                tc_fence_after();
+                if (any_rescale) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t o[32];
+                        tmem_ld_32x32(tmem_o + lane_base + c * 32, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st_32x32(tmem_o + lane_base + c * 32, o);
+                    }
+                    tmem_st_wait();
+                }
+            }
+            // ---- pass 2: exp2, row sum, P -> smem (bf16, swizzled) ---------------------------------------
+            float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+            tmem_ld_32x32(tmem_s + lane_base, raw[0]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld_wait();
+                if (c + 1 < 4) {
+                    tmem_ld_32x32(tmem_s + lane_base + (c + 1) * 32, raw[(c + 1) & 1]);
+                } else {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_free[t]);      // the tensor core may overwrite S_t now
+                }
+                if (diag) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) if (c * 32 + i > r) raw[c & 1][i] = 0xff800000u;
+                }
+                float pv[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float e = exp2f(fmaf(__uint_as_float(raw[c & 1][i]), p.scale_log2, -m_ref));
+                    pv[i] = e;
+                    rs4[i & 3] += e;
+                }
+                store_p_chunk(myP, r, c * 32, pv);
+            }
+            l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[t]);
+        }
+        // ---- epilogue: O_t / l -> bf16, logsumexp ------------------------------------------------
+        mbar_wait(&o_done[t], (n - 1) & 1);
+        __syncwarp();
+        tc_fence_after();
+        const float inv = 1.0f / l_run;
+        const long long grow = (long long)(row0 + my_qblk * 128 + r);
+        __nv_bfloat16* orow = p.out + grow * p.C + h * D;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(tmem_o + lane_base + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 u;
+                u.x = pack_bf16x2(__uint_as_float(o[q * 8 + 0]) * inv, __uint_as_float(o[q * 8 + 1]) * inv);
+                u.y = pack_bf16x2(__uint_as_float(o[q * 8 + 2]) * inv, __uint_as_float(o[q * 8 + 3]) * inv);
+                u.z = pack_bf16x2(__uint_as_float(o[q * 8 + 4]) * inv, __uint_as_float(o[q * 8 + 5]) * inv);
+                u.w = pack_bf16x2(__uint_as_float(o[q * 8 + 6]) * inv, __uint_as_float(o[q * 8 + 7]) * inv);
+                *reinterpret_cast<uint4*>(orow + c * 32 + q * 8) = u;
+            }
+        }
+        p.lse[((long long)b * p.H + h) * p.T + my_qblk * 128 + r] = (m_ref + log2f(l_run)) * 0.6931471805599453f;
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
 // =================================================================================================
@@ -482,10 +719,21 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.out = (__nv_bfloat16*)out; p.lse = lse;
     const int smem = 7 * TILE_BYTES + 64;
+    const int smem_ws = (2 + 2 * WS_NST + 4) * TILE_BYTES + 256;
     static bool configured = false;
+    static int use_ws = 1;
     if (!configured) {
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        TDL_CHECK(cudaFuncSetAttribute(attn_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
+        const char* e = getenv("TDL_ATTN_WS");
+        if (e) use_ws = atoi(e);
         configured = true;
+    }
+    if (use_ws && (T / 128) % 2 == 0) {
+        attn_fwd_ws_kernel<<<dim3((unsigned)(T / 256), (unsigned)H, (unsigned)B), WS_THREADS, smem_ws,
+                             reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+        TDL_LAUNCH_CHECK();
+        return 0;
     }
     attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
     TDL_LAUNCH_CHECK();

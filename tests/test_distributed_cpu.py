@@ -147,3 +147,42 @@ def test_tensor_parallel_flags_poisoned_rank():
     res = run_distributed(_tp_worker, 2, 6, 3)
     assert res[0]["attacks"] == res[1]["attacks"] and res[0]["attacks"][0] == (1, 3)
     assert res[0]["trust"][1] < 0.5 < res[0]["trust"][0]
+
+
+def _hybrid_worker(rank, world, attack_step, steps):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = None
+    if attack_step is not None:
+        att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[3], intensity=0.5,
+                                               start_step=attack_step))
+        att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=16, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=2, pp_size=2, dp_size=2,
+                         optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 16, num_batches=steps)]
+    own = t._backend_impl._my_stages()
+    wsum = float(sum(p.detach().double().sum() for s in own for p in t.model_partitions[s].parameters()))
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history], "owner": list(t.stage_map.owner),
+            "reassign": [(r["from_node"], r["to_node"], r["step"]) for r in t.reassignment_history], "own": own, "wsum": wsum}
+
+
+def test_pipeline_x_data_parallel_hybrid_with_compromise():
+    """BASELINE config 5 plumbing (PP x DP): 2 pipeline replicas of 2 stages, rank 3 (replica 1, stage 1) poisons its
+    gradients mid-run -> excluded from the DP aggregation in the same step, compromised, its stage migrates to rank 2."""
+    res = run_distributed(_hybrid_worker, 4, 10, 14, timeout=400.0)
+    assert all(r["losses"] == pytest.approx(res[0]["losses"]) for r in res)
+    assert res[0]["attacks"][0] == (3, 10) and res[0]["reassign"][0] == (3, 2, 10)
+    assert res[0]["owner"] == [0, 1, 2, 2]
+    assert all(torch.isfinite(torch.tensor(res[0]["losses"])))
+    # DP replicas of the same stage stayed identical until the compromise (stage 0: ranks 0 and 2 own it)
+    assert res[0]["own"] == [0] and 0 in res[2]["own"]
+
+
+def test_hybrid_replicas_stay_in_sync_without_attack():
+    res = run_distributed(_hybrid_worker, 4, None, 6, timeout=400.0)
+    assert res[0]["own"] == [0] and res[2]["own"] == [0] and res[0]["wsum"] == pytest.approx(res[2]["wsum"], rel=1e-6)
+    assert res[1]["wsum"] == pytest.approx(res[3]["wsum"], rel=1e-6)

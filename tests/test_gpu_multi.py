@@ -180,3 +180,27 @@ def test_tensor_parallel_fused_kernels_on_gpus():
     t = DistributedTrainer(cfg)
     single = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 4, num_batches=4, seq_len=128)]
     assert res[0]["losses"] == pytest.approx(single, rel=3e-2)
+
+
+def _pp_worker(rank, world):
+    """BASELINE config 1/2 plumbing on GPUs: stages over NCCL p2p, poisoned rank -> migration without restart."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5, start_step=10))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=16, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, parallelism="pipeline", micro_batches=4, optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 16, num_batches=14)]
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history],
+            "reassign": [(r["from_node"], r["to_node"], r["step"]) for r in t.reassignment_history], "owner": list(t.stage_map.owner)}
+
+
+def test_pipeline_over_nccl_with_reassignment():
+    world = torch.cuda.device_count()
+    res = _run(_pp_worker, world)
+    assert all(r["losses"] == pytest.approx(res[0]["losses"], rel=1e-4) for r in res)
+    assert res[0]["attacks"] == [(1, 10)] and res[0]["reassign"][0][0] == 1 and res[0]["reassign"][0][2] == 10
+    assert 1 not in res[0]["owner"] and len(res[0]["losses"]) == 14

@@ -97,19 +97,31 @@ class PipelineStrategy:
             logger.warning("num_nodes (%d) != world size (%d): using world size", c.num_nodes, self.world)
             c.num_nodes = self.world
             t.trust_manager.resize(self.world)
+        # hybrid layout (BASELINE config 5): world = pp x dp; rank r is pipeline position r % pp of replica r // pp
+        self.dp = max(1, int(c.dp_size)) if c.dp_size > 1 else 1
+        assert self.world % self.dp == 0, "world size must be divisible by dp_size"
+        self.pp = self.world // self.dp
+        self.replica = self.rank // self.pp
         model = t._build_model()
-        if hasattr(model, "untie_head") and self.world > 1:
+        if hasattr(model, "untie_head") and self.pp > 1:
             model.untie_head()
-        parts = t.create_model_partitions()
+        t.config.num_nodes, saved = self.pp, t.config.num_nodes
+        parts = t.create_model_partitions()                         # pp stages per replica
+        t.config.num_nodes = saved
         self.stages = [parts[i] for i in range(len(parts))]
-        t.stage_map = StageMap(len(self.stages), self.world)
+        self.S = len(self.stages)
+        # one global map: entry d*S + s is the rank that runs stage s of replica d
+        t.stage_map = StageMap(self.dp * self.S, self.world)
+        t.stage_map.owner = [d * self.pp + (s % self.pp) for d in range(self.dp) for s in range(self.S)]
+        t.stage_costs = list(t.stage_costs) * self.dp
         for sid, st in enumerate(self.stages):
             t.model_partitions[sid] = st
-            if t.stage_map.owner[sid] == self.rank:
+            if self._owner(sid) == self.rank:
                 self._adopt(sid)
         kind = "1f1b" if c.parallelism == "pipeline" else "gpipe"
         self.micro = max(1, c.micro_batches if c.parallelism == "pipeline" else 1)
-        self.schedule = make_schedule(len(self.stages), self.micro, kind)
+        self.schedule = make_schedule(self.S, self.micro, kind)
+        self._dp_groups: Dict[Tuple[int, ...], Any] = {}
 
     def _adopt(self, sid: int) -> None:
         st = self.stages[sid].to(self.device)
@@ -118,17 +130,64 @@ class PipelineStrategy:
             self.t.optimizers[sid] = self.t._make_optimizer(params)
             self.t.schedulers[sid] = self.t._make_scheduler(self.t.optimizers[sid])
 
-    def _owner(self, sid: int) -> int:
-        return self.t.stage_map.owner[sid]
+    def _owner(self, sid: int, replica: Optional[int] = None) -> int:
+        """Rank that runs stage ``sid`` of ``replica`` (default: this rank's replica)."""
+        d = self.replica if replica is None else replica
+        return self.t.stage_map.owner[d * self.S + sid]
+
+    def _my_stages(self, rank: Optional[int] = None) -> List[int]:
+        r = self.rank if rank is None else rank
+        return [g % self.S for g in self.t.stage_map.stages_of(r)]
+
+    def _dp_group(self, ranks: Tuple[int, ...]):
+        """Process group of the ranks that hold the same stage in every replica (created collectively, cached)."""
+        if ranks not in self._dp_groups:
+            self._dp_groups[ranks] = dist.new_group(list(ranks))
+        return self._dp_groups[ranks]
+
+    def _sync_dp_grads(self, step: int) -> Dict[int, float]:
+        """Trust-weighted aggregation of each stage's gradients across the data-parallel replicas (robust
+        coefficients from the bucket norms exclude an exploding replica in the same step).  Returns the norm
+        every participating rank contributed (own rank only)."""
+        from ..ops.reference_impl import robust_coefficients, trust_weighted_reduce
+        t = self.t
+        tw_all = t.trust_manager.aggregation_weights()
+        for sid in range(self.S):
+            ranks = tuple(self._owner(sid, d) for d in range(self.dp))
+            if len(set(ranks)) < len(ranks):
+                continue
+            group = self._dp_group(ranks)                            # every rank calls new_group in the same order
+            if self.rank not in ranks:
+                continue
+            params = [p for p in self.stages[sid].parameters() if p.grad is not None]
+            if not params:
+                continue
+            flat = torch.cat([p.grad.reshape(-1).float() for p in params])
+            dev = torch.device("cpu") if comm.is_gloo() else flat.device
+            flat_c = flat.to(dev)
+            gathered = [torch.empty_like(flat_c) for _ in ranks]
+            dist.all_gather(gathered, flat_c, group=group)
+            norms = torch.stack([g.norm() for g in gathered])
+            w = torch.tensor([tw_all[r] for r in ranks], dtype=torch.float32)
+            w = w / w.sum() if float(w.sum()) > 0 else torch.full((len(ranks),), 1.0 / len(ranks))
+            coeff = robust_coefficients(norms.cpu(), w)
+            reduced, _ = trust_weighted_reduce(gathered, coeff.to(dev), 0.0, norms)
+            reduced = reduced.to(flat.device)
+            off = 0
+            for p in params:
+                n = p.numel()
+                p.grad.copy_(reduced[off:off + n].view_as(p.grad).to(p.grad.dtype))
+                off += n
+        return {}
 
     # ------------------------------------------------------------- one step
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
         t, c = self.t, self.t.config
         t0 = time.perf_counter()
-        S, M = len(self.stages), self.micro
+        S, M = self.S, self.micro
         step = t.global_step
-        xs = batch["input"].chunk(M)
-        ys = batch["target"].chunk(M)
+        xs = batch["input"].chunk(self.dp)[self.replica].chunk(M)
+        ys = batch["target"].chunk(self.dp)[self.replica].chunk(M)
         acts: Dict[Tuple[int, int], Tuple[Optional[torch.Tensor], torch.Tensor]] = {}
         pending_sends: List = []
         stage_stats = torch.zeros(S, NUM_STATS, dtype=torch.float64)
@@ -189,11 +248,14 @@ class PipelineStrategy:
         self._grad_handoff.clear()
 
         # ---- local gradients: fault injection + norm --------------------------------
-        my_grads = [p.grad for sid in t.stage_map.stages_of(self.rank) for p in self.stages[sid].parameters()
-                    if p.grad is not None]
+        my_grads = [p.grad for sid in self._my_stages() for p in self.stages[sid].parameters() if p.grad is not None]
         if t.attacker is not None:
             t.attacker.poison_gradients(self.rank, my_grads, step)
         my_norm = t.gradient_verifier.total_norm(my_grads) if my_grads else 0.0
+        if self.dp > 1:
+            tc = time.perf_counter()
+            self._sync_dp_grads(step)
+            comm_s += time.perf_counter() - tc
         loss_local = float(sum(l.detach() for l in losses).item()) if losses else 0.0
 
         # ---- replicated decisions ---------------------------------------------------
@@ -205,12 +267,11 @@ class PipelineStrategy:
         ss = table[:, :S * NUM_STATS].reshape(self.world, S, NUM_STATS)
         hv = table[:, S * NUM_STATS:S * NUM_STATS + S]
         norms = table[:, -3]
-        loss = float(table[table[:, -1] > 0, -2].sum())
+        loss = float(table[table[:, -1] > 0, -2].sum()) / self.dp  # mean over replicas
         out_stats: Dict[int, np.ndarray] = {}
         for s in range(S):
-            src = np.nonzero(hv[:, s] > 0)[0]
-            if src.size:
-                out_stats[self._owner(s)] = ss[src[0], s]          # a node's last stage wins
+            for src in np.nonzero(hv[:, s] > 0)[0]:                 # reporter verified stage s of ITS replica
+                out_stats[self._owner(s, int(src) // self.pp)] = ss[src, s]   # a node's last stage wins
         t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
                              "invalid_nodes": set(), "grad_norms": {}}
         if c.attack_detection_enabled:
@@ -220,6 +281,8 @@ class PipelineStrategy:
                     t.handle_detected_attack(node, None, result=res)
         if c.gradient_verification_enabled:
             for node in range(self.world):
+                if node in {a["node_id"] for a in t.attack_history if a["step"] == step}:
+                    continue
                 if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
                     t._last_step_info["invalid_nodes"].add(node)
                     t.handle_gradient_attack(node, [])
@@ -261,20 +324,24 @@ class PipelineStrategy:
 
     # ---------------------------------------------------------- reassignment
     def reassign(self, src: int) -> Optional[int]:
-        """Move every stage of ``src`` to the best trusted rank: parameters and optimizer state are
+        """Move every stage of ``src`` to the best trusted rank of the same pipeline replica: parameters are
         sent p2p; all ranks update the (replicated) stage map.  No process restarts."""
         t = self.t
-        moved = t.stage_map.stages_of(src)
-        if not moved or not t.planner.allowed(src):
+        moved_global = t.stage_map.stages_of(src)
+        if not moved_global or not t.planner.allowed(src):
             return None
+        rep = src // self.pp
         loads = [t.stage_map.load(n, t.stage_costs) for n in range(self.world)]
-        dst = t.planner.choose_target(src, loads)
-        if dst is None:
-            logger.error("No trusted nodes available for reassignment")
+        mean_load = (sum(loads) / max(1, sum(1 for l in loads if l > 0))) or 1.0
+        cands = [n for n in t.trust_manager.get_trusted_nodes() if n != src and n // self.pp == rep]
+        if not cands:
+            logger.error("No trusted nodes available for reassignment in replica %d", rep)
             return None
+        dst = max(cands, key=lambda n: (t.trust_manager.get_trust_score(n) - t.planner.load_weight * loads[n] / mean_load, -n))
         t.planner.note_attempt(src)
         t0 = time.perf_counter()
-        numel = sum(p.numel() for s in moved for p in self.stages[s].parameters())
+        moved = [g % self.S for g in moved_global]
+        numel = sum(p.numel() for s2 in moved for p in self.stages[s2].parameters())
         for sid in moved:
             self._migrate(sid, src, dst)
         t.stage_map.move_all(src, dst)
@@ -286,7 +353,7 @@ class PipelineStrategy:
         for obj in (t.attack_detector, t.node_monitor, t.gradient_verifier):
             (obj.reset_node_history if hasattr(obj, "reset_node_history") else obj.reset_node)(dst)
         if dst in t.node_configs:
-            t.node_configs[dst].model_partition = "+".join(f"partition_{s}" for s in t.stage_map.stages_of(dst))
+            t.node_configs[dst].model_partition = "+".join(f"partition_{s2}" for s2 in self._my_stages(dst))
         return dst
 
     def _migrate(self, sid: int, src: int, dst: int) -> None:
@@ -318,7 +385,7 @@ class PipelineStrategy:
     # ------------------------------------------------------------------ misc
     @torch.no_grad()
     def validate(self, loader) -> float:
-        S = len(self.stages)
+        S = self.S
         total, n = 0.0, 0
         for batch in loader:
             x = None
@@ -326,7 +393,7 @@ class PipelineStrategy:
                 if self._owner(s) != self.rank:
                     continue
                 if s == 0:
-                    x = batch["input"].to(self.device)
+                    x = batch["input"].chunk(self.dp)[self.replica].to(self.device)
                 elif self._owner(s - 1) != self.rank:
                     x = comm.recv_tensor(self._owner(s - 1), self.device, tag=3)
                 x = self.stages[s](x)
@@ -334,8 +401,9 @@ class PipelineStrategy:
                     comm.send_tensor(x, self._owner(s + 1), tag=3)
             loss = 0.0
             if self._owner(S - 1) == self.rank:
-                loss = float(self.t.calculate_loss(x, batch["target"]).item())
-            total += comm.broadcast_float(loss, self._owner(S - 1))
+                loss = float(self.t.calculate_loss(x, batch["target"].chunk(self.dp)[self.replica]).item())
+            vals = comm.all_gather_vector(torch.tensor([loss, 1.0 if self._owner(S - 1) == self.rank else 0.0]))
+            total += float((vals[:, 0] * vals[:, 1]).sum() / max(1.0, float(vals[:, 1].sum())))
             n += 1
         return total / max(1, n)
 
