@@ -68,7 +68,7 @@ __device__ __forceinline__ uint64_t desc_mnmajor(const uint8_t* tile, int k16, u
 // =================================================================================================
 // forward
 // =================================================================================================
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(256, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sQ = smem;
@@ -81,8 +81,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     uint64_t* bar_s = bars + 3;
     uint64_t* bar_o = bars + 4;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+    float* s_max = reinterpret_cast<float*>(bars + 6);   // [2 halves][128 rows] partial row maxima
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // heaviest (longest causal row) tiles first
     const int qb = (gridDim.x - 1) - blockIdx.x;
     const int h = blockIdx.y, b = blockIdx.z;
@@ -102,7 +103,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    // 256 threads: two threads per query row.  Warp w reads TMEM lane quarter (w & 3); `half` = w >> 2 selects which
+    // 64 of the 128 score columns (and which 32 of the 64 output columns) the thread owns.  The only cross-thread
+    // quantity is the row maximum (exchanged through smem once per key block); the row sum is combined at the end.
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
+    const int r = quarter * 32 + lane;               // query row inside the tile
 
     if (tid == 0) {
         mbar_arrive_expect_tx(bar_q, TILE_BYTES);
@@ -114,11 +120,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 
     const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
     const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    float o_acc[64];
+    float o_acc[32];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) o_acc[i] = 0.f;
+    for (int i = 0; i < 32; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    const int r = tid;                               // query row inside the tile
 
     // S(j+1) = Q K_{j+1}^T is queued on the tensor pipe right behind P_j V_j (the S accumulator is already in
     // registers by then), so the next block's scores are ready when the softmax warps come back for them.
@@ -143,30 +148,29 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         __syncwarp();
         tc_fence_after();
 
-        // ---- online softmax over this thread's row --------------------------------------------
-        // The whole S row (128 fp32) is pulled into registers with one round of TMEM loads; max and
-        // exp are then pure register passes (1 FMNMX, then FFMA + EX2 + FADD per element).
+        // ---- online softmax: this thread's 64 columns of its row, held in registers ----------------
         const bool diag = (j == qb);
-        uint32_t sraw[128];
+        uint32_t sraw[64];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
+        for (int c = 0; c < 2; ++c)
+            tmem_ld_32x32(tmem_s + lane_base + half * 64 + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
         tmem_ld_wait();
-        // causal mask only exists in the diagonal block: fold it into the scores there (one FSEL per element,
-        // warp-uniform branch) so the common path carries no predicate arithmetic at all
-        if (diag) {
+        if (diag) {                                  // causal mask only in the diagonal block (warp-uniform branch)
 #pragma unroll
-            for (int i = 0; i < 128; ++i) if (i > r) sraw[i] = 0xff800000u;           // -inf
+            for (int i = 0; i < 64; ++i) if (half * 64 + i > r) sraw[i] = 0xff800000u;     // -inf
         }
-        // four independent chains: a single running max/sum would serialise 128 dependent ops
         float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-        const float mraw = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
+        const float mpart = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        s_max[half * 128 + r] = mpart;
+        __syncthreads();                             // (also: everyone has pulled S out of TMEM)
+        const float mraw = fmaxf(mpart, s_max[(half ^ 1) * 128 + r]);
         const float mx = fmaxf(m_run, mraw * p.scale_log2);
         const float alpha = exp2f(m_run - mx);
         float rs4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
             float pv[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
@@ -174,13 +178,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
                 pv[i] = e;
                 rs4[i & 3] += e;
             }
-            store_p_chunk(sP, r, c * 32, pv);
+            store_p_chunk(sP, r, half * 64 + c * 32, pv);
         }
-        const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
-        l_run = l_run * alpha + rs;
+        l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
         m_run = mx;
 #pragma unroll
-        for (int i = 0; i < 64; ++i) o_acc[i] *= alpha;
+        for (int i = 0; i < 32; ++i) o_acc[i] *= alpha;
 
         fence_proxy_async_smem();                    // P (generic proxy) -> visible to the tensor core
         tc_fence_before();
@@ -197,29 +200,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         mbar_wait(bar_o, j & 1);
         __syncwarp();
         tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
+        {
             uint32_t raw[32];
-            tmem_ld_32x32(tmem_o + lane_base + c * 32, raw);
+            tmem_ld_32x32(tmem_o + lane_base + half * 32, raw);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(raw[i]);
+            for (int i = 0; i < 32; ++i) o_acc[i] += __uint_as_float(raw[i]);
         }
         tc_fence_before();
     }
 
-    // ---- epilogue -----------------------------------------------------------------------------
-    const float inv = 1.0f / l_run;
+    // ---- epilogue: combine the two half-row sums, normalise, store ---------------------------------
+    __syncthreads();
+    s_max[half * 128 + r] = l_run;
+    __syncthreads();
+    const float l_tot = l_run + s_max[(half ^ 1) * 128 + r];
+    const float inv = 1.0f / l_tot;
     const long long grow = (long long)(row0 + qb * BQ + r);
-    __nv_bfloat16* orow = p.out + grow * p.C + h * D;
+    __nv_bfloat16* orow = p.out + grow * p.C + h * D + half * 32;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < 4; ++q) {
         uint4 u;
         u.x = pack_bf16x2(o_acc[q * 8 + 0] * inv, o_acc[q * 8 + 1] * inv); u.y = pack_bf16x2(o_acc[q * 8 + 2] * inv, o_acc[q * 8 + 3] * inv);
         u.z = pack_bf16x2(o_acc[q * 8 + 4] * inv, o_acc[q * 8 + 5] * inv); u.w = pack_bf16x2(o_acc[q * 8 + 6] * inv, o_acc[q * 8 + 7] * inv);
         *reinterpret_cast<uint4*>(orow + q * 8) = u;
     }
-    p.lse[((long long)b * p.H + h) * p.T + qb * BQ + r] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+    if (half == 0) p.lse[((long long)b * p.H + h) * p.T + qb * BQ + r] = (m_run + log2f(l_tot)) * 0.6931471805599453f;
 
     __syncthreads();
     if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
@@ -499,7 +505,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // TMEM: S [0,128) dP [128,256) acc0 [256,320) acc1 [320,384)
 // =================================================================================================
 template <int MODE>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(512, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const AttnParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sFix0 = smem;                         // MODE0: K   MODE1: Q
@@ -535,9 +541,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_s = tmem, tmem_dp = tmem + 128, tmem_a0 = tmem + 256, tmem_a1 = tmem + 320;
-    // 256 threads: two threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns column half
-    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).
-    const int quarter = warp & 3, half = warp >> 2;
+    // 512 threads: four threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns the 32-column chunk
+    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).  16 warps per
+    // SM instead of 4 is what hides the tcgen05.ld / MUFU / st.shared latencies here.
+    const int quarter = warp & 3, cq = warp >> 2;
     const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
 
     auto load_stream = [&](int i, int buf) {      // called by thread 0
@@ -618,8 +625,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
         mbar_wait(bar_s, it & 1);
         __syncwarp();
         tc_fence_after();
-#pragma unroll
-        for (int c = half * 2; c < half * 2 + 2; ++c) {
+        {
+            const int c = cq;
             uint32_t rs_[32], rd_[32];
             tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
             tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
@@ -668,18 +675,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     const long long grow = (long long)(row0 + ob * 128 + r);
     auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul) {
         {
-            const int c = half;                    // each of the two row threads writes 32 of the 64 columns
-            uint32_t raw[32];
-            tmem_ld_32x32(taddr + lane_base + c * 32, raw);
+            const int c = cq;                      // each of the four row threads writes 16 of the 64 columns
+            uint32_t raw[16];
+            tmem_ld_32x16(taddr + lane_base + c * 16, raw);
             tmem_ld_wait();
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < 2; ++q) {
                 uint4 u;
                 u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
                 u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
                 u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
                 u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
-                *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
+                *reinterpret_cast<uint4*>(dst + c * 16 + q * 8) = u;
             }
         }
     };
@@ -718,10 +725,10 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     p.scale = 1.0f / sqrtf(64.0f);
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.out = (__nv_bfloat16*)out; p.lse = lse;
-    const int smem = 7 * TILE_BYTES + 64;
+    const int smem = 7 * TILE_BYTES + 64 + 1024;
     const int smem_ws = (2 + 2 * WS_NST + 4) * TILE_BYTES + 256;
     static bool configured = false;
-    static int use_ws = 1;
+    static int use_ws = 0;                 // the simple 2-CTA/SM kernel is faster (profiles/README.md); TDL_ATTN_WS=1 selects the ping-pong one
     if (!configured) {
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
@@ -735,7 +742,7 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
         TDL_LAUNCH_CHECK();
         return 0;
     }
-    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 256, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -764,8 +771,8 @@ extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d
         configured = true;
     }
     const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
-    attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
-    attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<0><<<grid, 512, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<1><<<grid, 512, smem, s>>>(tq, tdo, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }

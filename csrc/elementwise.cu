@@ -494,7 +494,7 @@ extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, 
 extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
                                  const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream) {
     TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported", (long long)C);
-    const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 4);
+    const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 2);   // one resident wave: fewer dgamma/dbeta atomics
 #define LN_BWD(I) layernorm_bwd_kernel<I><<<grid, 256, 2 * C * sizeof(float), STREAM(stream)>>>( \
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, \
         dw, db, (int)M, (int)C)

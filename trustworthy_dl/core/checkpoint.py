@@ -23,6 +23,9 @@ def _path(directory: str, step: int, rank: Optional[int]) -> str:
 def save_checkpoint(trainer, directory: Optional[str] = None, rank: Optional[int] = None) -> str:
     directory = directory or trainer.config.checkpoint_dir
     os.makedirs(directory, exist_ok=True)
+    engine = getattr(getattr(trainer, "_backend_impl", None), "engine", None)
+    if engine is not None:                       # fused path: weights live in the engine's flat buffers
+        engine.export_to_module(trainer.model_partitions[0])
     ckpt: Dict[str, Any] = {
         # ---- reference schema ----
         "epoch": trainer.current_epoch,
@@ -45,6 +48,8 @@ def save_checkpoint(trainer, directory: Optional[str] = None, rank: Optional[int
         "config": dict(trainer.config.__dict__),
         "format_version": 1,
     }
+    if engine is not None:
+        ckpt["engine"] = {k: v.cpu() for k, v in engine.state_dict().items()}
     path = _path(directory, trainer.global_step, rank)
     tmp = path + ".tmp"
     torch.save(ckpt, tmp)
@@ -82,6 +87,9 @@ def load_checkpoint(trainer, path: str, strict: bool = True, restore_rng: bool =
     trainer.reassignment_history = list(ckpt.get("reassignment_history", []))
     if "training_state" in ckpt:
         trainer.training_state = type(trainer.training_state)(ckpt["training_state"])
+    engine = getattr(getattr(trainer, "_backend_impl", None), "engine", None)
+    if engine is not None and ckpt.get("engine"):
+        engine.load_state_dict({k: v.to(engine.device) if v.dim() else v for k, v in ckpt["engine"].items()})
     if restore_rng and ckpt.get("rng"):
         torch.set_rng_state(ckpt["rng"]["torch"])
         if ckpt["rng"].get("cuda") is not None and torch.cuda.is_available():

@@ -18,14 +18,26 @@ _CFG = {
 }
 
 
+class _ConvBiasReLU(nn.Conv2d):
+    """3x3 conv whose bias + ReLU run as one fused epilogue kernel on CUDA (csrc/conv_epilogue.cu, K13): the
+    convolution itself stays in cuDNN without bias, the epilogue is a single pass over the activation."""
+
+    def forward(self, x):
+        if x.is_cuda and self.bias is not None:
+            from ..ops.conv_epilogue import fused_bias_relu
+            y = F.conv2d(x, self.weight, None, self.stride, self.padding, self.dilation, self.groups)
+            return fused_bias_relu(y, self.bias)
+        return F.relu(super().forward(x))
+
+
 class _ConvGroup(nn.Sequential):
     def __init__(self, cin, widths, batch_norm):
         layers = []
         for w in widths:
-            layers.append(nn.Conv2d(cin, w, 3, padding=1))
             if batch_norm:
-                layers.append(nn.BatchNorm2d(w))
-            layers.append(nn.ReLU(inplace=True))
+                layers += [nn.Conv2d(cin, w, 3, padding=1), nn.BatchNorm2d(w), nn.ReLU(inplace=True)]
+            else:
+                layers.append(_ConvBiasReLU(cin, w, 3, padding=1))
             cin = w
         layers.append(nn.MaxPool2d(2, 2))
         super().__init__(*layers)
