@@ -20,6 +20,21 @@
 #include "common.cuh"
 #include <cstdlib>
 
+#ifdef TDL_ATTN_TRACE
+// poor man's tracer (bench/attn_trace.cu): one thread of one CTA stamps clock64() at phase boundaries
+__device__ long long g_trace[8192];
+__device__ int g_trace_n;
+#define TRACE_AT(tag)                                                                                   \
+    do {                                                                                                \
+        if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == TDL_ATTN_TRACE_TID) { \
+            int _i = g_trace_n;                                                                         \
+            if (_i < 4096) { g_trace[2 * _i] = (tag); g_trace[2 * _i + 1] = clock64(); g_trace_n = _i + 1; } \
+        }                                                                                               \
+    } while (0)
+#else
+#define TRACE_AT(tag) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int D = 64;            // head dim
@@ -68,7 +83,7 @@ __device__ __forceinline__ uint64_t desc_mnmajor(const uint8_t* tile, int k16, u
 // =================================================================================================
 // forward
 // =================================================================================================
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(128, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sQ = smem;
@@ -81,7 +96,176 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     uint64_t* bar_s = bars + 3;
     uint64_t* bar_o = bars + 4;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
-    float* s_max = reinterpret_cast<float*>(bars + 6);   // [2 halves][128 rows] partial row maxima
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    // heaviest (longest causal row) tiles first
+    const int qb = (gridDim.x - 1) - blockIdx.x;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int row0 = b * p.T;
+    const int n_kv = qb + 1;
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        tma_prefetch_desc(&tmap_qkv);
+        mbar_init(bar_q, 1); mbar_init(&bar_kv[0], 1); mbar_init(&bar_kv[1], 1);
+        mbar_init(bar_s, 1); mbar_init(bar_o, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+    if (tid == 0) {
+        mbar_arrive_expect_tx(bar_q, TILE_BYTES);
+        tma_load_2d(sQ, &tmap_qkv, bar_q, h * D, row0 + qb * BQ);
+        mbar_arrive_expect_tx(&bar_kv[0], 2 * TILE_BYTES);
+        tma_load_2d(sK, &tmap_qkv, &bar_kv[0], p.C + h * D, row0);
+        tma_load_2d(sV, &tmap_qkv, &bar_kv[0], 2 * p.C + h * D, row0);
+    }
+
+    const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+    const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+    float o_acc[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) o_acc[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const int r = tid;                               // query row inside the tile
+
+    // S(j+1) = Q K_{j+1}^T is queued on the tensor pipe right behind P_j V_j (the S accumulator is already in
+    // registers by then), so the next block's scores are ready when the softmax warps come back for them.
+    auto issue_s = [&](int jj) {                     // thread 0 only
+        const int b2 = jj & 1;
+        mbar_wait(&bar_kv[b2], (jj >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+            umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + b2 * TILE_BYTES, k), idesc_s, k > 0);
+        umma_commit(bar_s);
+    };
+    if (tid == 0) { mbar_wait(bar_q, 0); issue_s(0); }
+    for (int j = 0; j < n_kv; ++j) {
+        const int buf = j & 1;
+        if (tid == 0 && j + 1 < n_kv) {              // prefetch next K/V into the other buffer
+            mbar_arrive_expect_tx(&bar_kv[buf ^ 1], 2 * TILE_BYTES);
+            tma_load_2d(sK + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], p.C + h * D, row0 + (j + 1) * BK);
+            tma_load_2d(sV + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], 2 * p.C + h * D, row0 + (j + 1) * BK);
+        }
+        TRACE_AT(1);
+        mbar_wait(bar_s, j & 1);
+        __syncwarp();
+        tc_fence_after();
+        TRACE_AT(2);
+
+        // ---- online softmax over this thread's row --------------------------------------------
+        // The whole S row (128 fp32) is pulled into registers with one round of TMEM loads; max and
+        // exp are then pure register passes (1 FMNMX, then FFMA + EX2 + FADD per element).
+        const bool diag = (j == qb);
+        uint32_t sraw[128];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
+        tmem_ld_wait();
+        TRACE_AT(3);
+        // causal mask only exists in the diagonal block: fold it into the scores there (one FSEL per element,
+        // warp-uniform branch) so the common path carries no predicate arithmetic at all
+        if (diag) {
+#pragma unroll
+            for (int i = 0; i < 128; ++i) if (i > r) sraw[i] = 0xff800000u;           // -inf
+        }
+        // four independent chains: a single running max/sum would serialise 128 dependent ops
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
+        const float mraw = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        const float mx = fmaxf(m_run, mraw * p.scale_log2);
+        const float alpha = exp2f(m_run - mx);
+        TRACE_AT(4);
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float pv[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));   // exp2(-inf) = 0 under the mask
+                pv[i] = e;
+                rs4[i & 3] += e;
+            }
+            store_p_chunk(sP, r, c * 32, pv);
+        }
+        const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        TRACE_AT(5);
+        l_run = l_run * alpha + rs;
+        m_run = mx;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) o_acc[i] *= alpha;
+
+        TRACE_AT(6);
+        fence_proxy_async_smem();                    // P (generic proxy) -> visible to the tensor core
+        tc_fence_before();
+        __syncthreads();
+        TRACE_AT(7);
+        if (tid == 0) {
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+                umma_bf16_ss(tmem_o, desc_kmajor(sP + (k >> 2) * TILE_BYTES, k & 3),
+                             desc_mnmajor(sV + buf * TILE_BYTES, k, TILE_BYTES), idesc_o, k > 0);
+            umma_commit(bar_o);
+            if (j + 1 < n_kv) issue_s(j + 1);
+        }
+        TRACE_AT(8);
+        mbar_wait(bar_o, j & 1);
+        __syncwarp();
+        tc_fence_after();
+        TRACE_AT(9);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_o + lane_base + c * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(raw[i]);
+        }
+        tc_fence_before();
+        TRACE_AT(10);
+    }
+
+    // ---- epilogue -----------------------------------------------------------------------------
+    const float inv = 1.0f / l_run;
+    const long long grow = (long long)(row0 + qb * BQ + r);
+    __nv_bfloat16* orow = p.out + grow * p.C + h * D;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(o_acc[q * 8 + 0] * inv, o_acc[q * 8 + 1] * inv); u.y = pack_bf16x2(o_acc[q * 8 + 2] * inv, o_acc[q * 8 + 3] * inv);
+        u.z = pack_bf16x2(o_acc[q * 8 + 4] * inv, o_acc[q * 8 + 5] * inv); u.w = pack_bf16x2(o_acc[q * 8 + 6] * inv, o_acc[q * 8 + 7] * inv);
+        *reinterpret_cast<uint4*>(orow + q * 8) = u;
+    }
+    p.lse[((long long)b * p.H + h) * p.T + qb * BQ + r] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+}
+
+// ---- variant with two threads per query row (256 threads, still 2 CTAs per SM) -------------------------------
+__global__ void __launch_bounds__(256, 2)
+attn_fwd_t2_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + TILE_BYTES;              // 2 buffers
+    uint8_t* sV = smem + 3 * TILE_BYTES;          // 2 buffers
+    uint8_t* sP = smem + 5 * TILE_BYTES;          // [128 x 128] = 2 sub-tiles
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * TILE_BYTES);
+    uint64_t* bar_q = bars;
+    uint64_t* bar_kv = bars + 1;                  // [2]
+    uint64_t* bar_s = bars + 3;
+    uint64_t* bar_o = bars + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+    __half* s_max = reinterpret_cast<__half*>(bars + 6);  // [2 halves][128 rows] partial row maxima (fp16: 512 B keeps 2 CTAs/SM)
+    float* s_sum = reinterpret_cast<float*>(sP);          // epilogue only: P tile is dead by then
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // heaviest (longest causal row) tiles first
@@ -162,10 +346,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-        const float mpart = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-        s_max[half * 128 + r] = mpart;
+        // both threads of a row must use the SAME maximum: each rounds its partial up to fp16 and both take the max
+        // of the two rounded values (softmax is shift-invariant, so the rounding itself is harmless)
+        const __half mh = __float2half_ru(fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
+        s_max[half * 128 + r] = mh;
         __syncthreads();                             // (also: everyone has pulled S out of TMEM)
-        const float mraw = fmaxf(mpart, s_max[(half ^ 1) * 128 + r]);
+        const float mraw = fmaxf(__half2float(mh), __half2float(s_max[(half ^ 1) * 128 + r]));
         const float mx = fmaxf(m_run, mraw * p.scale_log2);
         const float alpha = exp2f(m_run - mx);
         float rs4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -212,9 +398,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 
     // ---- epilogue: combine the two half-row sums, normalise, store ---------------------------------
     __syncthreads();
-    s_max[half * 128 + r] = l_run;
+    s_sum[half * 128 + r] = l_run;
     __syncthreads();
-    const float l_tot = l_run + s_max[(half ^ 1) * 128 + r];
+    const float l_tot = l_run + s_sum[(half ^ 1) * 128 + r];
     const float inv = 1.0f / l_tot;
     const long long grow = (long long)(row0 + qb * BQ + r);
     __nv_bfloat16* orow = p.out + grow * p.C + h * D + half * 32;
@@ -234,8 +420,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 // =================================================================================================
 // forward, warp-specialised ping-pong version (used when T/128 is even)
 //
-// One CTA (320 threads, 1 per SM) owns TWO query tiles of one head: blocks i and nblk-1-i, so every CTA does
-// the same causal work (nblk+1 key blocks) and both tiles share each K/V block it loads.
+// One CTA (320 threads, 1 per SM) owns TWO adjacent query tiles of one head (blocks 2i and 2i+1): both tiles share
+// every K/V block the CTA loads and have nearly equal causal work, so the two warpgroups stay busy together.
 //   warps 0-3  softmax warpgroup of tile A          warps 4-7  softmax warpgroup of tile B
 //   warp 8     MMA issuer (one lane)                warp 9     TMA producer (one lane)
 // While one warpgroup runs exp on its scores the tensor core computes the other tile's S = QK^T and PV, and
@@ -245,7 +431,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 // TMEM: S_A [0,128) S_B [128,256) O_A [256,320) O_B [320,384).  smem: Q x2, 3 K/V stages, P x2 = 192 KB.
 // =================================================================================================
 constexpr int WS_NST = 3;
-constexpr int WS_THREADS = 320;
+constexpr int WS_THREADS = 384;                // 2 softmax warpgroups + 1 helper warpgroup (MMA warp, TMA warp, 2 idle)
 
 __global__ void __launch_bounds__(WS_THREADS, 1)
 attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
@@ -265,10 +451,13 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParam
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nblk = p.T / 128;
-    const int pi = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-    const int qblk0 = pi, qblk1 = nblk - 1 - pi;          // tile A / tile B query blocks
-    const int nkv0 = pi + 1, nkv1 = nblk - pi;            // causal key-block counts
+    // adjacent query blocks share a CTA: both warpgroups then have (almost) the same number of key blocks, so neither
+    // idles while the other finishes; CTAs differ in length instead and are launched longest-first
+    const int pi = (gridDim.x - 1) - blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+    const int qblk0 = 2 * pi, qblk1 = 2 * pi + 1;         // tile A / tile B query blocks
+    const int nkv0 = qblk0 + 1, nkv1 = qblk1 + 1;         // causal key-block counts
     const int nmax = nkv1;
+    (void)nblk;
     const int row0 = b * p.T;
 
     if (tid == 0) {
@@ -284,7 +473,10 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParam
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-
+    // Register redistribution: the helper warpgroup gives most of its registers to the two softmax warpgroups,
+    // which can then keep a whole 128-column score row in registers (single TMEM pass, early release of S).
+    if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
     if (warp == 9) {
         // ===================================== TMA producer =====================================
         if (lane == 0) {
@@ -355,8 +547,10 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParam
                 }
             }
         }
+    }
     } else {
         // ===================================== softmax warpgroups ================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;" ::: "memory");
         const int t = warp >> 2;
         const int r = (warp & 3) * 32 + lane;
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
@@ -370,25 +564,33 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParam
             mbar_wait(&s_full[t], j & 1);
             __syncwarp();
             tc_fence_after();
-            // ---- pass 1 over the S row (32 columns at a time, next chunk in flight): row max ------------
-            uint32_t raw[2][32];
-            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-            tmem_ld_32x32(tmem_s + lane_base, raw[0]);
+            // whole S row -> registers in one round of TMEM loads, then hand S back to the tensor core at once
+            uint32_t sraw[128];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                tmem_ld_wait();
-                if (c + 1 < 4) tmem_ld_32x32(tmem_s + lane_base + (c + 1) * 32, raw[(c + 1) & 1]);
-                if (diag) {
+            for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free[t]);              // S_t(j+1) may be issued while we do the exponentials
+            if (diag) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) if (c * 32 + i > r) raw[c & 1][i] = 0xff800000u;
-                }
-#pragma unroll
-                for (int i = 0; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(raw[c & 1][i]));
+                for (int i = 0; i < 128; ++i) if (i > r) sraw[i] = 0xff800000u;
             }
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+            for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
             const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2;
             float alpha = 1.f;
             if (m_blk > m_ref + 8.f) { alpha = exp2f(m_ref - m_blk); m_ref = m_blk; }   // lazy: p stays <= 2^8 otherwise
             const bool any_rescale = __any_sync(0xffffffffu, alpha != 1.f);
+            float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 128; ++i) {
+                const float e = exp2f(fmaf(__uint_as_float(sraw[i]), p.scale_log2, -m_ref));
+                sraw[i] = __float_as_uint(e);
+                rs4[i & 3] += e;
+            }
+            l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
             if (j > 0) {                                         // PV_t(j-1) must be done before P / O are touched
                 mbar_wait(&o_done[t], (j - 1) & 1);
                 __syncwarp();
@@ -406,33 +608,13 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParam
                     tmem_st_wait();
                 }
             }
-            // ---- pass 2: exp2, row sum, P -> smem (bf16, swizzled) ---------------------------------------
-            float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-            tmem_ld_32x32(tmem_s + lane_base, raw[0]);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                tmem_ld_wait();
-                if (c + 1 < 4) {
-                    tmem_ld_32x32(tmem_s + lane_base + (c + 1) * 32, raw[(c + 1) & 1]);
-                } else {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&s_free[t]);      // the tensor core may overwrite S_t now
-                }
-                if (diag) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) if (c * 32 + i > r) raw[c & 1][i] = 0xff800000u;
-                }
                 float pv[32];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float e = exp2f(fmaf(__uint_as_float(raw[c & 1][i]), p.scale_log2, -m_ref));
-                    pv[i] = e;
-                    rs4[i & 3] += e;
-                }
+                for (int i = 0; i < 32; ++i) pv[i] = __uint_as_float(sraw[c * 32 + i]);
                 store_p_chunk(myP, r, c * 32, pv);
             }
-            l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
             fence_proxy_async_smem();
             tc_fence_before();
             __syncwarp();
@@ -505,7 +687,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // TMEM: S [0,128) dP [128,256) acc0 [256,320) acc1 [320,384)
 // =================================================================================================
 template <int MODE>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(256, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const AttnParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sFix0 = smem;                         // MODE0: K   MODE1: Q
@@ -541,10 +723,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_s = tmem, tmem_dp = tmem + 128, tmem_a0 = tmem + 256, tmem_a1 = tmem + 320;
-    // 512 threads: four threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns the 32-column chunk
-    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).  16 warps per
-    // SM instead of 4 is what hides the tcgen05.ld / MUFU / st.shared latencies here.
-    const int quarter = warp & 3, cq = warp >> 2;
+    // 256 threads: two threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns column half
+    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).
+    const int quarter = warp & 3, half = warp >> 2;
     const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
 
     auto load_stream = [&](int i, int buf) {      // called by thread 0
@@ -625,8 +806,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
         mbar_wait(bar_s, it & 1);
         __syncwarp();
         tc_fence_after();
-        {
-            const int c = cq;
+#pragma unroll
+        for (int c = half * 2; c < half * 2 + 2; ++c) {
             uint32_t rs_[32], rd_[32];
             tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
             tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
@@ -675,18 +856,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     const long long grow = (long long)(row0 + ob * 128 + r);
     auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul) {
         {
-            const int c = cq;                      // each of the four row threads writes 16 of the 64 columns
-            uint32_t raw[16];
-            tmem_ld_32x16(taddr + lane_base + c * 16, raw);
+            const int c = half;                    // each of the two row threads writes 32 of the 64 columns
+            uint32_t raw[32];
+            tmem_ld_32x32(taddr + lane_base + c * 32, raw);
             tmem_ld_wait();
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
+            for (int q = 0; q < 4; ++q) {
                 uint4 u;
                 u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
                 u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
                 u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
                 u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
-                *reinterpret_cast<uint4*>(dst + c * 16 + q * 8) = u;
+                *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
             }
         }
     };
@@ -725,10 +906,10 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     p.scale = 1.0f / sqrtf(64.0f);
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.out = (__nv_bfloat16*)out; p.lse = lse;
-    const int smem = 7 * TILE_BYTES + 64 + 1024;
+    const int smem = 7 * TILE_BYTES + 64;
     const int smem_ws = (2 + 2 * WS_NST + 4) * TILE_BYTES + 256;
     static bool configured = false;
-    static int use_ws = 0;                 // the simple 2-CTA/SM kernel is faster (profiles/README.md); TDL_ATTN_WS=1 selects the ping-pong one
+    static int use_ws = 0;                 // the simple 2-CTA/SM kernel measured faster (profiles/README.md); TDL_ATTN_WS=1 selects ping-pong
     if (!configured) {
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
@@ -736,13 +917,23 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
         if (e) use_ws = atoi(e);
         configured = true;
     }
+    static int fwd_variant = -1;
+    if (fwd_variant < 0) { const char* e = getenv("TDL_ATTN_FWD"); fwd_variant = e ? atoi(e) : 1; }
+    if (fwd_variant == 2) {
+        static bool cfg2 = false;
+        const int smem2 = 7 * TILE_BYTES + 64 + 512;
+        if (!cfg2) { TDL_CHECK(cudaFuncSetAttribute(attn_fwd_t2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2)); cfg2 = true; }
+        attn_fwd_t2_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 256, smem2, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+        TDL_LAUNCH_CHECK();
+        return 0;
+    }
     if (use_ws && (T / 128) % 2 == 0) {
         attn_fwd_ws_kernel<<<dim3((unsigned)(T / 256), (unsigned)H, (unsigned)B), WS_THREADS, smem_ws,
                              reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
         TDL_LAUNCH_CHECK();
         return 0;
     }
-    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 256, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -771,8 +962,8 @@ extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d
         configured = true;
     }
     const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
-    attn_bwd_kernel<0><<<grid, 512, smem, s>>>(tq, tdo, p);
-    attn_bwd_kernel<1><<<grid, 512, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
+    attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
