@@ -21,17 +21,19 @@
 #include <cstdlib>
 
 #ifdef TDL_ATTN_TRACE
-// poor man's tracer (bench/attn_trace.cu): one thread of one CTA stamps clock64() at phase boundaries
+// poor man's tracer (bench/attn_trace.cu, bench/attn_bwd_trace.cu): one thread of one CTA stamps clock64() at phase
+// boundaries.  The stamp index lives in a register (TRACE_DECL) so a stamp costs a clock read and two stores.
 __device__ long long g_trace[8192];
 __device__ int g_trace_n;
+#define TRACE_DECL int _trace_i = 0
 #define TRACE_AT(tag)                                                                                   \
     do {                                                                                                \
         if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == TDL_ATTN_TRACE_TID) { \
-            int _i = g_trace_n;                                                                         \
-            if (_i < 4096) { g_trace[2 * _i] = (tag); g_trace[2 * _i + 1] = clock64(); g_trace_n = _i + 1; } \
+            if (_trace_i < 4096) { g_trace[2 * _trace_i] = (tag); g_trace[2 * _trace_i + 1] = clock64(); g_trace_n = ++_trace_i; } \
         }                                                                                               \
     } while (0)
 #else
+#define TRACE_DECL do {} while (0)
 #define TRACE_AT(tag) do {} while (0)
 #endif
 
@@ -50,6 +52,9 @@ struct AttnParams {
     float* lse;                  // [B, H, T]  natural-log logsumexp of the scaled scores
     const float* delta;          // bwd: [B, H, T]
     __nv_bfloat16* dqkv;         // bwd: [B*T, 3C]
+    float* dbias;                // bwd, optional: [3C] += column sums of dqkv
+    int bwd_chunk;               // bwd (persistent): (batch, head) pairs per scheduling chunk (working set <= L2)
+    unsigned long long mg_tile, mg_chunk, mg_head;   // ceil(2^40 / d) for d = nblk * chunk, chunk, H (exact for n, d < 2^20)
 };
 
 // byte offset of the 16-byte piece `q8` (0..7) of row r inside a [rows x 64] bf16 tile with 128B swizzle
@@ -69,6 +74,11 @@ __device__ __forceinline__ void store_p_chunk(uint8_t* tile, int r, int c0, cons
     }
 }
 
+__device__ __forceinline__ void tma_store_2d_tile(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+
 // ---- descriptor helpers for [128 x 64] swizzled tiles ------------------------------------------
 // tile rows are the M/N index, 64 contiguous elements are K (K-major); k16 = which 16-wide K slice
 __device__ __forceinline__ uint64_t desc_kmajor(const uint8_t* tile, int k16) {
@@ -85,6 +95,7 @@ __device__ __forceinline__ uint64_t desc_mnmajor(const uint8_t* tile, int k16, u
 // =================================================================================================
 __global__ void __launch_bounds__(128, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
+    TRACE_DECL;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sQ = smem;
     uint8_t* sK = smem + TILE_BYTES;              // 2 buffers
@@ -854,7 +865,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
     __syncwarp();
     tc_fence_after();
     const long long grow = (long long)(row0 + ob * 128 + r);
-    auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul) {
+    auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul, float* dbias) {
         {
             const int c = half;                    // each of the two row threads writes 32 of the 64 columns
             uint32_t raw[32];
@@ -869,14 +880,423 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
                 u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
                 *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
             }
+            if (dbias != nullptr) {
+                // qkv bias gradient: column sums of the (bf16-rounded) tile.  Transposing butterfly over the warp's
+                // 32 rows: after the 5 rounds lane l holds the sum of column l of this thread's 32-column half.
+                const int lane = threadIdx.x & 31;
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j]) * mul));
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) {
+                    const bool up = (lane & off) != 0;
+#pragma unroll
+                    for (int j = 0; j < off; ++j) {
+                        const float send = up ? v[j] : v[j + off];
+                        const float keep = up ? v[j + off] : v[j];
+                        v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                    }
+                }
+                atomicAdd(dbias + c * 32 + lane, v[0]);
+            }
         }
     };
     __nv_bfloat16* base = p.dqkv + grow * (3LL * p.C) + h * D;
+    float* db = p.dbias != nullptr ? p.dbias + h * D : nullptr;
     if (MODE == 0) {
-        write_acc(tmem_a1, base + p.C, p.scale);          // dK
-        write_acc(tmem_a0, base + 2 * p.C, 1.0f);         // dV
+        write_acc(tmem_a1, base + p.C, p.scale, db ? db + p.C : nullptr);          // dK
+        write_acc(tmem_a0, base + 2 * p.C, 1.0f, db ? db + 2 * p.C : nullptr);     // dV
     } else {
-        write_acc(tmem_a0, base, p.scale);                // dQ
+        write_acc(tmem_a0, base, p.scale, db);                                     // dQ
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// =================================================================================================
+// backward: persistent, software-pipelined, P / dS kept in tensor memory (default).
+// Same math as attn_bwd_kernel, restructured around what bounded it there:
+//   * the tensor core and the CUDA cores took turns            -> warp 8 (one elected lane) issues every tcgen05.mma,
+//     warp 9 every TMA load, the 8 math warps only talk to them through mbarriers, so
+//         tensor pipe: acc(j) | dP(j+1) | S(j+2)     runs under     math: exp(j+1), dS(j+1);
+//   * shared-memory bandwidth went into writing P / dS and reading them back as A operands
+//                                                              -> S is double-buffered in TMEM and the bf16 P / dS tiles are
+//     written back INTO the S buffer they came from (tcgen05.st) and consumed from there (A-from-TMEM tcgen05.mma).
+//     MODE 0 computes the transposed tiles S^T = K Q^T, dP^T = V dO^T so that P^T / dS^T have the key index on the
+//     TMEM lanes, as dV = P^T dO and dK = dS^T Q need; the per-query statistics then run along the columns and are
+//     staged in shared memory once per query block;
+//   * at T = 1024 a (block, head) tile is only 4.5 iterations long and 4.6 us of launch / prologue / drain per CTA was
+//     43 % of the kernel                                       -> one CTA per SM walks a static, longest-first list of
+//     tiles; barriers, TMEM and the load / MMA pipelines run on across tile boundaries (global iteration counter j), so
+//     the next tile's loads and first MMAs are in flight while the math warps write the previous tile's accumulators.
+// smem (14 tiles = 224 KB): 3 fixed pairs (ring) | 3 stream stages (MODE 0: {Q,dO}; MODE 1: {K,V}) | 2 output staging
+//       tiles (leave by TMA store) | column statistics
+// TMEM: S0 [0,128)  S1 [128,256)  dP [256,384)  acc0 [384,448)  acc1 [448,512)
+//       inside S[b], the thread that owns columns [64h, 64h+64) stores P at [64h, 64h+32) and dS at [64h+32, 64h+64)
+// =================================================================================================
+constexpr int BWD_WS_THREADS = 320;
+constexpr int BWD_WS_NSTR = 3;
+constexpr int BWD_WS_NFIX = 3;
+constexpr int BWD_WS_SMEM = (2 * BWD_WS_NFIX + 2 * BWD_WS_NSTR + 2) * TILE_BYTES + 2048 + 256;
+
+struct BwdCursor {
+    int t;        // global tile id; >= total when exhausted
+    int k;        // ordinal of the tile inside this CTA
+    int it, n;    // iteration inside the tile, iterations of the tile
+    int j;        // iteration counter across tiles (drives every ring buffer and barrier parity)
+    int ob, h, b; // decoded tile: outer block, head, batch (integer divisions only when the tile changes)
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(BWD_WS_THREADS, 1)
+attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
+                   const __grid_constant__ CUtensorMap tmap_dqkv, const AttnParams p) {
+    constexpr int NSTR = BWD_WS_NSTR, NFIX = BWD_WS_NFIX;
+    TRACE_DECL;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sFix = smem;                                   // [NFIX][2] : MODE0: K,V   MODE1: Q,dO
+    uint8_t* sStr = smem + 2 * NFIX * TILE_BYTES;           // [NSTR][2] : MODE0: Q,dO  MODE1: K,V
+    uint8_t* sOut = smem + (2 * NFIX + 2 * NSTR) * TILE_BYTES;                                  // [2] finished dK,dV / dQ tiles
+    float* sStat = reinterpret_cast<float*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES);     // [2][2][128]: lse*log2e, delta (MODE 0)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES + 2048);
+    uint64_t* fix_full = bars;                     // [3]
+    uint64_t* fix_empty = bars + 3;                // [3]
+    uint64_t* str_full = bars + 6;                 // [4]
+    uint64_t* str_empty = bars + 10;               // [4]
+    uint64_t* s_full = bars + 14;                  // [2]
+    uint64_t* dp_full = bars + 16;
+    uint64_t* dp_free = bars + 17;
+    uint64_t* p_full = bars + 18;                  // [2]
+    uint64_t* acc_done = bars + 20;                // [2]
+    uint64_t* acc_free = bars + 22;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nblk = p.T / 128;
+    const int BH = p.B * p.H;
+    const int total = nblk * BH;
+    // Tile order: (batch, head) pairs in chunks of p.bwd_chunk whose Q/K/V/dO fit in L2; inside a chunk longest tiles
+    // first.  CTA c takes tiles c, c + gridDim.x, ...: the chunk size is not a multiple of the grid, so which CTA gets
+    // the long tiles rotates from chunk to chunk.
+    const int CH = p.bwd_chunk;
+    auto fdiv = [](int n, unsigned long long magic) { return (int)(((unsigned long long)(unsigned)n * magic) >> 40); };
+    auto cur_decode = [&](BwdCursor& c) {                     // runs when a cursor enters a new tile; no hardware division
+        if (c.t >= total) { c.n = 0; return; }
+        const int chunk = fdiv(c.t, p.mg_tile);               // t / (nblk * CH); CH divides B*H
+        const int tl = c.t - chunk * nblk * CH;
+        const int rank = fdiv(tl, p.mg_chunk);                // tl / CH
+        const int bh = chunk * CH + tl - rank * CH;
+        c.ob = MODE == 0 ? rank : nblk - 1 - rank;
+        c.n = MODE == 0 ? nblk - c.ob : c.ob + 1;
+        c.b = fdiv(bh, p.mg_head);                            // bh / H
+        c.h = bh - c.b * p.H;
+    };
+    auto cur_init = [&]() {
+        BwdCursor c; c.t = blockIdx.x; c.k = 0; c.it = 0; c.j = 0; c.ob = c.h = c.b = 0;
+        cur_decode(c);
+        return c;
+    };
+    auto cur_next = [&](BwdCursor& c) {
+        ++c.j;
+        if (++c.it == c.n) { c.it = 0; c.t += gridDim.x; ++c.k; cur_decode(c); }
+    };
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); tma_prefetch_desc(&tmap_dqkv);
+        for (int s = 0; s < NFIX; ++s) { mbar_init(&fix_full[s], 1); mbar_init(&fix_empty[s], 1); }
+        for (int s = 0; s < NSTR; ++s) { mbar_init(&str_full[s], 1); mbar_init(&str_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 8); mbar_init(&acc_done[s], 1); }
+        mbar_init(dp_full, 1); mbar_init(dp_free, 8); mbar_init(acc_free, 8);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem_dp = tmem + 256, tmem_a0 = tmem + 384, tmem_a1 = tmem + 448;
+
+    if (warp == 9) {
+        // ======================================= TMA producer ====================================
+        if (lane == 0) {
+            for (BwdCursor c = cur_init(); c.t < total; cur_next(c)) {
+                const int ob = c.ob, h = c.h;
+                const int row0 = c.b * p.T;
+                if (c.it == 0) {
+                    const int fb = c.k % NFIX;
+                    if (c.k >= NFIX) mbar_wait(&fix_empty[fb], ((c.k / NFIX) - 1) & 1);
+                    uint8_t* f0 = sFix + fb * 2 * TILE_BYTES;
+                    mbar_arrive_expect_tx(&fix_full[fb], 2 * TILE_BYTES);
+                    if (MODE == 0) {
+                        tma_load_2d(f0, &tmap_qkv, &fix_full[fb], p.C + h * D, row0 + ob * 128);                  // K
+                        tma_load_2d(f0 + TILE_BYTES, &tmap_qkv, &fix_full[fb], 2 * p.C + h * D, row0 + ob * 128); // V
+                    } else {
+                        tma_load_2d(f0, &tmap_qkv, &fix_full[fb], h * D, row0 + ob * 128);                        // Q
+                        tma_load_2d(f0 + TILE_BYTES, &tmap_do, &fix_full[fb], h * D, row0 + ob * 128);            // dO
+                    }
+                }
+                const int st = c.j % NSTR;
+                const int i = (MODE == 0 ? ob : 0) + c.it;
+                if (c.j >= NSTR) mbar_wait(&str_empty[st], ((c.j / NSTR) - 1) & 1);
+                uint8_t* s0 = sStr + st * 2 * TILE_BYTES;
+                mbar_arrive_expect_tx(&str_full[st], 2 * TILE_BYTES);
+                if (MODE == 0) {
+                    tma_load_2d(s0, &tmap_qkv, &str_full[st], h * D, row0 + i * 128);                  // Q_i
+                    tma_load_2d(s0 + TILE_BYTES, &tmap_do, &str_full[st], h * D, row0 + i * 128);      // dO_i
+                } else {
+                    tma_load_2d(s0, &tmap_qkv, &str_full[st], p.C + h * D, row0 + i * 128);            // K_i
+                    tma_load_2d(s0 + TILE_BYTES, &tmap_qkv, &str_full[st], 2 * p.C + h * D, row0 + i * 128);   // V_i
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 8) {
+        // ======================================= MMA issue =======================================
+        if (lane == 0) {
+            const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
+            const uint32_t idesc_ts = umma_idesc_bf16(128, 64, 0, 1);       // acc   : A from TMEM (K along columns) x MN-major B
+            // MODE 0: S^T = K Q_i^T, dP^T = V dO_i^T (keys on the lanes); MODE 1: S = Q K_i^T, dP = dO V_i^T
+            auto issue_s = [&](const BwdCursor& c) {
+                if (c.it == 0) mbar_wait(&fix_full[c.k % NFIX], (c.k / NFIX) & 1);
+                mbar_wait(&str_full[c.j % NSTR], (c.j / NSTR) & 1);
+                tc_fence_after();
+                const uint8_t* f0 = sFix + (c.k % NFIX) * 2 * TILE_BYTES;
+                const uint8_t* q0 = sStr + (c.j % NSTR) * 2 * TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16_ss(tmem + (c.j & 1) * 128, desc_kmajor(f0, k), desc_kmajor(q0, k), idesc_s, k > 0);
+                umma_commit(&s_full[c.j & 1]);
+            };
+            auto issue_dp = [&](const BwdCursor& c) {       // its fixed pair and stream stage were waited for by issue_s
+                const uint8_t* f1 = sFix + (c.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES;
+                const uint8_t* q1 = sStr + (c.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(f1, k), desc_kmajor(q1, k), idesc_s, k > 0);
+                umma_commit(dp_full);
+            };
+            BwdCursor cs = cur_init(), cd = cur_init(), ca = cur_init();
+            if (cs.t < total) { issue_s(cs); cur_next(cs); }
+            if (cd.t < total) { issue_dp(cd); cur_next(cd); }
+            if (cs.t < total) { issue_s(cs); cur_next(cs); }
+            for (; ca.t < total; cur_next(ca)) {
+                const int bb = ca.j & 1;
+                const uint8_t* q0 = sStr + (ca.j % NSTR) * 2 * TILE_BYTES;
+                const uint32_t ts = tmem + bb * 128;
+                TRACE_AT(30);
+                if (cd.t < total) {                                     // dP(j+1) goes in as soon as dP(j) has left TMEM, i.e.
+                    mbar_wait(dp_free, ca.j & 1);                       // while the math warps are still busy with block j
+                    tc_fence_after();
+                    issue_dp(cd); cur_next(cd);
+                }
+                TRACE_AT(31);
+                mbar_wait(&p_full[bb], (ca.j >> 1) & 1);                // P / dS of this iteration sit in S[bb]
+                TRACE_AT(32);
+                if (ca.it == 0 && ca.k > 0) mbar_wait(acc_free, (ca.k - 1) & 1);   // previous tile's accumulators were read out
+                tc_fence_after();
+                const uint32_t accum = ca.it > 0;
+                if (MODE == 0) {
+                    // dV[k, d] += sum_q P^T[k, q] dO[q, d] ;  dK[k, d] += sum_q dS^T[k, q] Q[q, d]
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        umma_bf16_ts(tmem_a0, ts + (k >> 2) * 64 + (k & 3) * 8, desc_mnmajor(q0 + TILE_BYTES, k, TILE_BYTES), idesc_ts, (accum || k > 0));
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        umma_bf16_ts(tmem_a1, ts + (k >> 2) * 64 + 32 + (k & 3) * 8, desc_mnmajor(q0, k, TILE_BYTES), idesc_ts, (accum || k > 0));
+                } else {
+                    // dQ[q, d] += sum_k dS[q, k] K[k, d]
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        umma_bf16_ts(tmem_a0, ts + (k >> 2) * 64 + 32 + (k & 3) * 8, desc_mnmajor(q0, k, TILE_BYTES), idesc_ts, (accum || k > 0));
+                }
+                umma_commit(&acc_done[bb]);
+                umma_commit(&str_empty[ca.j % NSTR]);                   // the stream stage can be refilled
+                if (ca.it == ca.n - 1) umma_commit(&fix_empty[ca.k % NFIX]);
+                TRACE_AT(33);
+                if (cs.t < total) {
+                    mbar_wait(&acc_done[bb], (ca.j >> 1) & 1);          // acc(j) is done with S[bb]
+                    TRACE_AT(34);
+                    issue_s(cs); cur_next(cs);
+                }
+                TRACE_AT(35);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================================== math warps =========================================
+        // two threads per tile row: warp w reads TMEM lane quarter (w & 3) and owns column half (w >> 2)
+        const int quarter = warp & 3, half = warp >> 2;
+        const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
+        const int r = quarter * 32 + lane;
+        // MODE 0: the query block's statistics run along the columns: thread tid fetches lse (tid < 128) or delta of one
+        // query of the NEXT block at the top of an iteration and parks it in shared memory at the end (latency hidden)
+        auto fetch_stat = [&](const BwdCursor& c) {
+            const long long idx = (long long)(c.b * p.H + c.h) * p.T + (long long)(c.ob + c.it) * 128 + (tid & 127);
+            return tid < 128 ? p.lse[idx] : p.delta[idx];      // raw: scaled when parked, so nothing waits on the load here
+        };
+        const float stat_mul = tid < 128 ? 1.4426950408889634f : 1.0f;
+        // ---- finished tile: accumulators -> bf16 -> swizzled staging tiles -> TMA store.  It runs AFTER the math of the
+        //      next tile's first block, so the tensor core finishes the last acc MMAs under useful work, and the
+        //      accumulators are released (acc_free) as soon as they are in registers.
+        bool pend = false;
+        int pend_ob = 0, pend_h = 0, pend_b = 0, pend_bar = 0, pend_par = 0;
+        auto write_tile = [&]() {
+            mbar_wait(&acc_done[pend_bar], pend_par);
+            __syncwarp();
+            tc_fence_after();
+            TRACE_AT(27);
+            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile's stores have read the staging
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            float* db = p.dbias != nullptr ? p.dbias + pend_h * D : nullptr;
+            auto stage_acc = [&](uint32_t taddr, uint8_t* tile, float mul, float* dbias) {
+                uint32_t raw[32];                  // each of the two row threads handles 32 of the 64 columns
+                tmem_ld_32x32(taddr + lane_base + half * 32, raw);
+                tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint4 u;
+                    u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
+                    u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
+                    u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
+                    u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
+                    *reinterpret_cast<uint4*>(tile + swz(r, half * 4 + q)) = u;
+                }
+                if (dbias != nullptr) {                // qkv bias gradient: column sums of the bf16-rounded tile
+                    float v[32];
+#pragma unroll
+                    for (int j2 = 0; j2 < 32; ++j2) v[j2] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j2]) * mul));
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) {
+                        const bool up = (lane & off) != 0;
+#pragma unroll
+                        for (int j2 = 0; j2 < off; ++j2) {
+                            const float send = up ? v[j2] : v[j2 + off];
+                            const float keep = up ? v[j2 + off] : v[j2];
+                            v[j2] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                        }
+                    }
+                    atomicAdd(dbias + half * 32 + lane, v[0]);
+                }
+            };
+            if (MODE == 0) {
+                stage_acc(tmem_a1, sOut, p.scale, db ? db + p.C : nullptr);                    // dK
+                stage_acc(tmem_a0, sOut + TILE_BYTES, 1.0f, db ? db + 2 * p.C : nullptr);      // dV
+            } else {
+                stage_acc(tmem_a0, sOut, p.scale, db);                                         // dQ
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_free);              // the accumulators are in registers / shared memory
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            if (tid == 0) {
+                const int grow = pend_b * p.T + pend_ob * 128;
+                if (MODE == 0) {
+                    tma_store_2d_tile(&tmap_dqkv, sOut, p.C + pend_h * D, grow);
+                    tma_store_2d_tile(&tmap_dqkv, sOut + TILE_BYTES, 2 * p.C + pend_h * D, grow);
+                } else {
+                    tma_store_2d_tile(&tmap_dqkv, sOut, pend_h * D, grow);
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            TRACE_AT(28);
+            pend = false;
+        };
+        BwdCursor c = cur_init(), cn = cur_init();
+        if (cn.t < total) cur_next(cn);
+        if (MODE == 0 && c.t < total) {
+            sStat[tid] = fetch_stat(c) * stat_mul;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
+        float lse2 = 0.f, dlt = 0.f;
+        for (; c.t < total; cur_next(c)) {
+            const int ob = c.ob, h = c.h, b = c.b;
+            if (MODE == 1 && c.it == 0) {                      // this thread's query row is fixed for the whole tile
+                const long long idx = (long long)(b * p.H + h) * p.T + ob * 128 + r;
+                lse2 = p.lse[idx] * 1.4426950408889634f;
+                dlt = p.delta[idx];
+            }
+            const int bb = c.j & 1;
+            const bool diag = MODE == 0 ? (c.it == 0) : (c.it == c.n - 1);
+            const uint32_t ts = tmem + bb * 128 + lane_base + half * 64;
+            const float4* st_l = reinterpret_cast<const float4*>(sStat + bb * 256 + half * 64);
+            const float4* st_d = reinterpret_cast<const float4*>(sStat + bb * 256 + 128 + half * 64);
+            float stat_next = 0.f;
+            if (MODE == 0 && cn.t < total) stat_next = fetch_stat(cn);
+            // dP(j) was queued while block j-1 was still being processed, so both inputs are (nearly) there: exp (MUFU)
+            // and the dS arithmetic (FMA pipe) of different elements interleave instead of running as two phases.
+            uint32_t rs_[64];
+            TRACE_AT(20);
+            mbar_wait(&s_full[bb], (c.j >> 1) & 1);
+            tc_fence_after();
+            TRACE_AT(21);
+            tmem_ld_32x32(ts, *reinterpret_cast<uint32_t(*)[32]>(&rs_[0]));
+            tmem_ld_32x32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&rs_[32]));
+            mbar_wait(dp_full, c.j & 1);
+            tc_fence_after();
+            TRACE_AT(22);
+#pragma unroll
+            for (int cc2 = 0; cc2 < 2; ++cc2) {
+                uint32_t rd_[32];
+                tmem_ld_32x32(tmem_dp + lane_base + half * 64 + cc2 * 32, rd_);
+                tmem_ld_wait();
+                TRACE_AT(23);
+                if (cc2 == 1) {                                 // dP(j) is in registers: the tensor core may overwrite it
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(dp_free);
+                }
+                uint32_t pkp[16], pkd[16];
+#pragma unroll
+                for (int k4 = 0; k4 < 8; ++k4) {
+                    float l[4], d[4];
+                    if (MODE == 0) {
+                        const float4 l4 = st_l[cc2 * 8 + k4], d4 = st_d[cc2 * 8 + k4];
+                        l[0] = l4.x; l[1] = l4.y; l[2] = l4.z; l[3] = l4.w;
+                        d[0] = d4.x; d[1] = d4.y; d[2] = d4.z; d[3] = d4.w;
+                    } else {
+                        l[0] = l[1] = l[2] = l[3] = lse2;
+                        d[0] = d[1] = d[2] = d[3] = dlt;
+                    }
+                    float e4[4], s4[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int k = cc2 * 32 + k4 * 4 + u;   // column inside this thread's 64
+                        uint32_t sv = rs_[k];
+                        if (diag) {                             // causal mask only in the diagonal block (warp-uniform branch)
+                            const int cc = half * 64 + k;       // MODE 0: row = key, column = query; MODE 1: the transpose
+                            if (MODE == 0 ? (cc < r) : (cc > r)) sv = 0xff800000u;   // -inf -> P = 0
+                        }
+                        e4[u] = exp2f(fmaf(__uint_as_float(sv), p.scale_log2, -l[u]));
+                        s4[u] = e4[u] * (__uint_as_float(rd_[k4 * 4 + u]) - d[u]);
+                    }
+                    pkp[k4 * 2 + 0] = pack_bf16x2(e4[0], e4[1]); pkp[k4 * 2 + 1] = pack_bf16x2(e4[2], e4[3]);
+                    pkd[k4 * 2 + 0] = pack_bf16x2(s4[0], s4[1]); pkd[k4 * 2 + 1] = pack_bf16x2(s4[2], s4[3]);
+                }
+                // P (MODE 0) -> S[bb] columns [64h, 64h+32), dS -> [64h+32, 64h+64); bf16 pairs along the K index
+                if (MODE == 0) tmem_st_32x16(ts + cc2 * 16, pkp);
+                tmem_st_32x16(ts + 32 + cc2 * 16, pkd);
+                TRACE_AT(24);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[bb]);
+            TRACE_AT(25);
+            if (pend) write_tile();                            // previous tile's accumulators (its last MMAs ran under this block)
+            // stage the next block's statistics (other buffer); everyone is done reading this block's after the barrier
+            if (MODE == 0) {
+                sStat[(bb ^ 1) * 256 + tid] = stat_next * stat_mul;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+            }
+            TRACE_AT(26);
+            if (cn.t < total) cur_next(cn);
+
+            if (c.it == c.n - 1) { pend = true; pend_ob = ob; pend_h = h; pend_b = b; pend_bar = bb; pend_par = (c.j >> 1) & 1; }
+        }
+        if (pend) write_tile();
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // staging tiles are read before the CTA exits
     }
     tc_fence_before();
     __syncthreads();
@@ -938,8 +1358,10 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     return 0;
 }
 
-extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
-                                 void* dqkv, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream) {
+// dbias (optional, fp32 [3C]): += column sums of dqkv, i.e. the qkv projection's bias gradient, taken from the
+// accumulator tiles as they are written instead of re-reading dqkv.
+extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                                       void* dqkv, float* dbias, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream) {
     if (int rc = check_attn_shapes(B, T, H, Dh)) return rc;
     const int C = (int)(H * 64);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
@@ -953,17 +1375,43 @@ extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d
     p.B = (int)B; p.T = (int)T; p.H = (int)H; p.C = C;
     p.scale = 1.0f / sqrtf(64.0f);
     p.scale_log2 = p.scale * 1.4426950408889634f;
-    p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = (__nv_bfloat16*)dqkv;
+    p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = (__nv_bfloat16*)dqkv; p.dbias = dbias;
     const int smem = 10 * TILE_BYTES + 64;
+    const int smem_ws = BWD_WS_SMEM;
     static bool configured = false;
+    static int use_ws = 1;                       // TDL_ATTN_BWD_WS=0 selects the non-pipelined kernels
     if (!configured) {
+        if (const char* e = getenv("TDL_ATTN_BWD_WS")) use_ws = atoi(e);
         TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ws_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
+        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ws_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
         configured = true;
     }
     const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
-    attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
-    attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
+    if (use_ws) {
+        const long long tiles = (T / 128) * B * H;
+        long long ch = (96 * 1024) / T;                      // 4 tensors x T x 64 x 2 B per pair: keep a chunk under ~48 MB
+        ch = ch < 1 ? 1 : (ch > B * H ? B * H : ch);
+        while ((B * H) % ch) --ch;                           // chunks are all the same size
+        p.bwd_chunk = (int)ch;
+        TDL_REQUIRE(tiles < (1 << 20) && H < (1 << 20), "attention backward: too many tiles for the persistent schedule");
+        auto magic = [](long long d) { return (unsigned long long)(((1ull << 40) + d - 1) / d); };
+        p.mg_tile = magic((T / 128) * ch); p.mg_chunk = magic(ch); p.mg_head = magic(H);
+        const unsigned ctas = (unsigned)(tiles < tdl_num_sms() ? tiles : tdl_num_sms());      // persistent: one CTA per SM
+        CUtensorMap tdq;
+        if (int rc = tdl_make_tmap_2d_bf16(&tdq, dqkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
+        attn_bwd_ws_kernel<0><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, p);
+        attn_bwd_ws_kernel<1><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, p);
+    } else {
+        attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
+        attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
+    }
     TDL_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                                 void* dqkv, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream) {
+    return tdl_attention_bwd_dbias(qkv, out, d_out, lse, delta, dqkv, nullptr, B, T, H, Dh, stream);
 }

@@ -272,16 +272,17 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p32, __n
 
 // ------------------------------------------------------------------------------------ cross entropy
 // one CTA per row; logits bf16 [M, Vp] overwritten with dlogits; only columns < V are real.
-__global__ void __launch_bounds__(512) xent_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
+// Pass 1: online (max, sum); pass 2 re-reads the row (mostly from L2) and writes the gradient.
+__global__ void __launch_bounds__(1024) xent_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
         float* __restrict__ row_loss, float* __restrict__ loss_sum, int V, int Vp, float grad_scale) {
-    __shared__ float shm[16], shs[16];
+    __shared__ float shm[32], shs[32];
     const int row = blockIdx.x;
     __nv_bfloat16* lr = logits + (long long)row * Vp;
     const int nvec = Vp / 8;
     float mx = -INFINITY, sum = 0.f;
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
         float f[8];
-        bf16x8_to_f32(*reinterpret_cast<const uint4*>(lr + i * 8), f);
+        bf16x8_to_f32(ld_nc_v4(lr + i * 8), f);
         float lm = -INFINITY;
 #pragma unroll
         for (int j = 0; j < 8; ++j) if (i * 8 + j < V) lm = fmaxf(lm, f[j]);
@@ -301,8 +302,7 @@ __global__ void __launch_bounds__(512) xent_kernel(__nv_bfloat16* __restrict__ l
     const long long tgt = targets[row];
     const float inv = 1.0f / bs;
     if (threadIdx.x == 0) {
-        const float lt = __bfloat162float(lr[tgt]);
-        const float loss = logf(bs) + bm - lt;
+        const float loss = logf(bs) + bm - __bfloat162float(lr[tgt]);
         if (row_loss != nullptr) row_loss[row] = loss;
         if (loss_sum != nullptr) atomicAdd(loss_sum, loss);
     }
@@ -554,11 +554,17 @@ extern "C" int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype
     return 0;
 }
 
+static int xent_threads() {          // TDL_XENT_THREADS=1024: fewer rows in flight (more of the re-read hits L2)
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("TDL_XENT_THREADS"); v = e ? atoi(e) : 512; if (v != 256 && v != 1024) v = 512; }
+    return v;
+}
+
 extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row_loss, float* loss_sum, int64_t M,
                                 int64_t V, int64_t Vp, float grad_scale, void* stream) {
     TDL_REQUIRE(Vp % 8 == 0 && V <= Vp, "padded vocab must be a multiple of 8 and >= vocab");
-    xent_kernel<<<(unsigned)M, 512, 0, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets, row_loss, loss_sum,
-                                                         (int)V, (int)Vp, grad_scale);
+    xent_kernel<<<(unsigned)M, xent_threads(), 0, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets, row_loss,
+                                                                    loss_sum, (int)V, (int)Vp, grad_scale);
     TDL_LAUNCH_CHECK();
     return 0;
 }

@@ -20,6 +20,12 @@
 #include "common.cuh"
 #include <cstdlib>
 
+extern "C" int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream);   // elementwise.cu
+
+__device__ __forceinline__ void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 namespace {
 
 constexpr int BLOCK_M = 128;
@@ -37,6 +43,7 @@ struct GemmParams {
     void* C; long long ldc;
     const void* bias;
     const void* aux_in; void* aux_out; long long ld_aux;
+    float* colsum;                 // optional [N] fp32: += column sums of the bf16 output (staged 2-CTA epilogue only)
     // K8 (all-gather -> GEMM): A is row-sharded over `a_shards` peer buffers of `a_shard_rows` rows each, every
     // shard has its own tensor map; m-blocks are visited starting at `m_block_offset` (own shard first).
     int a_shards, a_shard_rows, m_block_offset;
@@ -372,7 +379,8 @@ template <int BLOCK_N, int STAGES_, bool AUX> struct Cfg2 {
     // epilogue staging: one output panel per column half (+ one aux panel per half when the epilogue reads or
     // writes a second tensor); the output leaves through TMA stores, aux_in arrives through TMA loads
     static constexpr int STAGING_BYTES = (AUX ? 4 : 2) * PANEL_BYTES;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 + 256;
+    static constexpr int COLSUM_BYTES = 8 * 16 * 4;                       // per epilogue warp: 16 column sums
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + COLSUM_BYTES + 1024 + 256;
 };
 
 struct EpiMaps { CUtensorMap c, aux; };
@@ -391,7 +399,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 __device__ __forceinline__ uint32_t panel_off(uint32_t r, uint32_t q8) { return r * 128u + ((q8 ^ (r & 7u)) << 4); }
 
 
-template <int BLOCK_N, int STAGES_, bool AUX>
+template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
                               const __grid_constant__ EpiMaps emaps, const __grid_constant__ GemmParams p) {
@@ -402,7 +410,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
     uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;                 // [half][out | aux] panels
-    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
+    float* colsum_smem = reinterpret_cast<float*>(staging + C::STAGING_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES + C::COLSUM_BYTES);
     uint64_t* full = bars;                       // used in the leader only
     uint64_t* empty = bars + C::STAGES;          // one per CTA
     uint64_t* tmem_full = bars + 2 * C::STAGES;  // one per CTA
@@ -680,12 +689,52 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                             }
                         }
                         if (aux_in) aux_phase ^= 1;
+                        if (COLSUM && p.colsum != nullptr) {
+                            // bias gradient of the consumer of this output: column sums of the finished bf16 panel
+                            // (intact until the next panel's first barrier).  Warp wq owns 16 columns: lane = piece
+                            // 2wq + (lane & 1) of rows (lane >> 1) + 16 i.  The 16 sums leave through an asynchronous
+                            // bulk reduction (smem -> global add): plain red.global here would make the following
+                            // bar.sync wait for the L2 round trip.
+                            const uint32_t wq = e & 3;
+                            const uint32_t q8 = 2u * wq + (lane & 1u);
+                            float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const uint32_t r2 = (lane >> 1) + 16u * i;
+                                if (m_idx + (int)r2 < p.M) {
+                                    const uint4 u = *reinterpret_cast<const uint4*>(out_panel + panel_off(r2, q8));
+                                    const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                                    cs[0] += f0.x; cs[1] += f0.y; cs[2] += f1.x; cs[3] += f1.y;
+                                    cs[4] += f2.x; cs[5] += f2.y; cs[6] += f3.x; cs[7] += f3.y;
+                                }
+                            }
+#pragma unroll
+                            for (int off = 2; off <= 16; off <<= 1) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], off);
+                            }
+                            float* slot = colsum_smem + e * 16;
+                            if (lane == 1) tma_store_wait_read();       // this warp's previous reduction has read the slot
+                            __syncwarp();
+                            if (lane < 2) {
+                                *reinterpret_cast<float4*>(slot + lane * 8) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+                                *reinterpret_cast<float4*>(slot + lane * 8 + 4) = make_float4(cs[4], cs[5], cs[6], cs[7]);
+                                fence_proxy_async_smem();
+                            }
+                            __syncwarp();
+                            const int gc = n_idx + pi * 64 + (int)wq * 16;
+                            if (lane == 1 && gc < p.N) {
+                                asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], 64;"
+                                             :: "l"(p.colsum + gc), "r"(smem_u32(slot)) : "memory");
+                                tma_store_commit();
+                            }
+                        }
                     }
                 }
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        if (staged && group_leader) tma_store_wait_all();
+        if (staged && (group_leader || (COLSUM && p.colsum != nullptr && lane == 1))) tma_store_wait_all();
     }
 
     tc_fence_before();
@@ -753,12 +802,12 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
     return 0;
 }
 
-template <int BLOCK_N, int STAGES_, bool AUX>
+template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
 static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const EpiMaps& em, GemmParams& p, cudaStream_t stream) {
     using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     static bool configured = false;
     if (!configured) {
-        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX>,
+        TDL_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured = true;
     }
@@ -766,7 +815,7 @@ static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const Ep
     const int work = m_blocks2 * p.n_blocks * p.split_k;
     const int max_clusters = tdl_num_sms() / 2;
     const int clusters = work < max_clusters ? work : max_clusters;
-    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, em, p);
+    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, em, p);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -775,8 +824,9 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
                        const void* B, void* Cout, void* const* c_ptrs, int c_scatter, int64_t c_shard_rows, int c_src_slot,
                        int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
                        const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux,
-                       int out_f32_atomic, int split_k, int block_n, void* stream) {
+                       int out_f32_atomic, int split_k, int block_n, float* colsum, void* stream) {
     TDL_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    TDL_REQUIRE(colsum == nullptr || (!out_f32_atomic && !c_scatter), "column sums need the bf16 output");
     TDL_REQUIRE(N % 32 == 0, "N (%lld) must be a multiple of 32", (long long)N);
     TDL_REQUIRE(ldc % 8 == 0 && (ld_aux % 8 == 0), "ldc/ld_aux must be multiples of 8 elements");
     if (block_n != 128 && block_n != 256) block_n = (N % 256 == 0 || N > 2048) ? 256 : 128;
@@ -807,6 +857,7 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     p.a_mn_major = a_mn_major; p.b_mn_major = b_mn_major;
     p.epilogue = epilogue; p.out_f32_atomic = out_f32_atomic; p.bias_f32 = bias_f32;
     p.C = Cout; p.ldc = ldc; p.bias = bias; p.aux_in = aux_in; p.aux_out = aux_out; p.ld_aux = ld_aux;
+    p.colsum = nullptr;
     TDL_REQUIRE(!(epilogue == EPI_GELU) || aux_out != nullptr, "GELU epilogue needs aux_out");
     TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU) || aux_in != nullptr, "epilogue needs aux_in");
     p.a_shards = a_shards; p.a_shard_rows = (int)a_shard_rows; p.m_block_offset = m_block_offset % p.m_blocks;
@@ -854,13 +905,24 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         } else {
             em.c = tb; em.aux = tb;                     // unused on the direct path
         }
-        return (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, p, s)
-                                     : launch_gemm_2cta<256, 6, false>(ta, tb, em, p, s);
+        const bool fuse_colsum = colsum != nullptr && staged && (reinterpret_cast<uintptr_t>(colsum) & 15) == 0;
+        if (fuse_colsum) p.colsum = colsum;             // column sums leave from the staged epilogue panels
+        if (fuse_colsum)
+            rc = needs_aux ? launch_gemm_2cta<256, 5, true, true>(ta, tb, em, p, s)
+                           : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, p, s);
+        else
+            rc = (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, p, s)
+                                       : launch_gemm_2cta<256, 6, false>(ta, tb, em, p, s);
+        if (!rc && colsum != nullptr && !fuse_colsum) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
+        return rc;
     }
     static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
     if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
-    if (block_n == 256) return exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
-    return exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s) : launch_gemm<128, 6>(ta, tb, p, s);
+    if (block_n == 256) rc = exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
+    else                rc = exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s) : launch_gemm<128, 6>(ta, tb, p, s);
+    // the 1-CTA kernel has no fused column sums: follow with the stand-alone reduction over the output
+    if (!rc && colsum != nullptr) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
+    return rc;
 }
 
 extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
@@ -869,7 +931,18 @@ extern "C" int tdl_gemm_bf16(const void* A, const void* B, void* Cout, int64_t M
                              int64_t ld_aux, int out_f32_atomic, int split_k, int block_n, void* stream) {
     const void* a1[1] = {A};
     return gemm_common(a1, 1, M, 0, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, bias_f32,
-                       epilogue, aux_in, aux_out, ld_aux, out_f32_atomic, split_k, block_n, stream);
+                       epilogue, aux_in, aux_out, ld_aux, out_f32_atomic, split_k, block_n, nullptr, stream);
+}
+
+// Same GEMM, and colsum[n] += sum_m bf16(C[m, n]) accumulated from the epilogue's staged output panels -- the
+// bias gradient of the layer that produced this GEMM's output gradient, without re-reading C from HBM.
+extern "C" int tdl_gemm_bf16_colsum(const void* A, const void* B, void* Cout, int64_t M, int64_t N, int64_t K,
+                                    int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
+                                    const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
+                                    int64_t ld_aux, int block_n, float* colsum, void* stream) {
+    const void* a1[1] = {A};
+    return gemm_common(a1, 1, M, 0, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, bias_f32,
+                       epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, colsum, stream);
 }
 
 // K8: all-gather -> GEMM.  A = concat of `W` row shards [shard_rows, K] that live in peer-mapped buffers;
@@ -882,7 +955,7 @@ extern "C" int tdl_allgather_gemm_bf16(const void* const* a_shard_ptrs, int W, i
     const int64_t M = shard_rows * W;
     const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
     return gemm_common(a_shard_ptrs, W, shard_rows, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, 0, bias,
-                       bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, stream);
+                       bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, nullptr, stream);
 }
 
 // K7: GEMM -> reduce-scatter (first half).  The partial product tile for rows owned by rank o is stored from
@@ -895,5 +968,5 @@ extern "C" int tdl_gemm_scatter_bf16(const void* A, const void* B, void* const* 
     const void* a1[1] = {A};
     const int offset = (int)(((shard_rows + BLOCK_M - 1) / BLOCK_M) * ((my_rank + 1) % W));   // start on a peer: spread the traffic
     return gemm_common(a1, 1, M, offset, B, nullptr, c_ptrs, 1, shard_rows, my_rank, M, N, K, lda, ldb, ldc, 0, b_mn_major,
-                       nullptr, 0, 0, nullptr, nullptr, ldc, 0, 1, block_n, stream);
+                       nullptr, 0, 0, nullptr, nullptr, ldc, 0, 1, block_n, nullptr, stream);
 }

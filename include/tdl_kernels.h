@@ -43,6 +43,11 @@ int tdl_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int64_t N, i
                   int64_t ldc, int a_mn_major, int b_mn_major, const void* bias, int bias_f32, int epilogue,
                   const void* aux_in, void* aux_out, int64_t ld_aux, int out_f32_atomic, int split_k, int block_n,
                   void* stream);
+/* Same GEMM with a bf16 output, plus colsum[n] += sum_m C[m, n] taken from the epilogue's staged panels: the
+ * bias gradient of the layer whose output gradient this GEMM produces, without another pass over C. */
+int tdl_gemm_bf16_colsum(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                         int64_t ldc, int a_mn_major, int b_mn_major, const void* bias, int bias_f32, int epilogue,
+                         const void* aux_in, void* aux_out, int64_t ld_aux, int block_n, float* colsum, void* stream);
 
 /* ---- K8 / K7: GEMM fused with the tensor-parallel collectives over peer-mapped memory ---------- */
 /* all-gather -> GEMM: A is W row shards [shard_rows, K] in peer buffers, read by TMA as the tiles are needed */
@@ -59,6 +64,9 @@ int tdl_reduce_slots(const void* staging, int W, int64_t slot_elems, const void*
 int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
 int tdl_attention_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
                       int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
+/* as above; dbias (fp32 [3C], may be NULL) += column sums of dqkv = the qkv projection's bias gradient */
+int tdl_attention_bwd_dbias(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
+                            float* dbias, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);
 
 /* ---- K10/K11/K14/K15 and friends ---------------------------------------------------------------- */
 int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd, int64_t M,

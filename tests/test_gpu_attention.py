@@ -30,7 +30,7 @@ def test_attention_forward(B, T, H):
     assert torch.allclose(lse.view(B, H, T), lse_ref, atol=2e-2, rtol=1e-3)
 
 
-@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 2), (1, 512, 2)])
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 2), (1, 512, 2), (2, 1024, 2), (1, 2048, 1)])
 def test_attention_backward(B, T, H):
     from trustworthy_dl.ops import nn as K
     dev = torch.device("cuda", 0)
@@ -52,3 +52,26 @@ def test_attention_backward(B, T, H):
     for name, g, r in (("dq", gq, dq), ("dk", gk, dk), ("dv", gv, dv)):
         err = (g - r).abs().max().item()
         assert err <= 4e-2 * (r.abs().max().item() + 1), f"{name} max err {err}"
+
+
+def test_attention_backward_fused_bias_grad():
+    """The qkv bias gradient accumulated from the accumulator write-out equals the column sums of dqkv."""
+    from trustworthy_dl.ops import nn as K
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(21)
+    B, T, H = 2, 384, 3
+    C = H * 64
+    qkv = torch.randn(B * T, 3 * C, device=dev).bfloat16()
+    out = torch.empty(B * T, C, device=dev, dtype=torch.bfloat16)
+    lse = torch.empty(B * H * T, device=dev)
+    K.attention_fwd(qkv, out, lse, B, T, H)
+    d_out = torch.randn(B * T, C, device=dev).bfloat16()
+    dqkv = torch.zeros(B * T, 3 * C, device=dev, dtype=torch.bfloat16)
+    delta = torch.empty(B * H * T, device=dev)
+    dbias = torch.full((3 * C,), 0.5, device=dev)             # accumulates on top of what is there
+    K.attention_bwd(qkv, out, d_out, lse, delta, dqkv, B, T, H, dbias=dbias)
+    ref = dqkv.float().sum(0) + 0.5
+    assert torch.allclose(dbias, ref, atol=2e-3, rtol=1e-4), (dbias - ref).abs().max().item()
+    dqkv2 = torch.zeros_like(dqkv)
+    K.attention_bwd(qkv, out, d_out, lse, delta, dqkv2, B, T, H)          # no bias pointer: same dqkv
+    assert torch.equal(dqkv, dqkv2)

@@ -136,3 +136,24 @@ def test_allgather_gemm_and_gemm_scatter_emulated_ranks(W):
         tp_ops.reduce_slots(staging[owner], W, out, residual=res)
         exp = ref2[owner * shard_rows:(owner + 1) * shard_rows] + res.float()
         assert torch.allclose(out.float(), exp, atol=0.15, rtol=3e-2), (out.float() - exp).abs().max().item()
+
+
+@pytest.mark.parametrize("M,N,K,dgelu", [(1024, 512, 256, True), (2048, 768, 128, False), (1000, 320, 192, False),
+                                         (256, 256, 128, False)])
+def test_gemm_fused_column_sums(M, N, K, dgelu):
+    """colsum += column sums of the bf16 output, from the staged epilogue panels (2-CTA path) or the stand-alone
+    reduction (small M -> 1-CTA path); rows beyond M must not contribute."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(M + N)
+    dy, w = _mk((M, K), dev), _mk((K, N), dev, 0.2)
+    pre = _mk((M, N), dev) if dgelu else None
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    cs = torch.full((N,), 0.25, device=dev)
+    Kk.linear_dgrad(dy, w, out, epilogue=Kk.EPI_DGELU if dgelu else Kk.EPI_NONE, aux_in=pre, colsum=cs)
+    ref = dy.float() @ w.float()
+    if dgelu:
+        ref = R.gelu_tanh_bwd(pre, ref)
+    assert torch.allclose(out.float(), ref, atol=5e-2, rtol=3e-2)
+    want = out.float().sum(0) + 0.25
+    assert torch.allclose(cs, want, atol=2e-3 * (M ** 0.5), rtol=1e-4), (cs - want).abs().max().item()

@@ -237,8 +237,8 @@ class GPT2Engine:
             # ---- MLP ----
             K.bias_grad(dx, self.grad32(p + "proj_b"))
             K.linear_wgrad(dx, self.fcg[l], self.grad32(p + "proj_w"), split_k=self._split_k(C, 4 * C))
-            K.linear_dgrad(dx, self.w16(p + "proj_w"), self.dfch, epilogue=K.EPI_DGELU, aux_in=self.fch[l])
-            K.bias_grad(self.dfch, self.grad32(p + "fc_b"))
+            K.linear_dgrad(dx, self.w16(p + "proj_w"), self.dfch, epilogue=K.EPI_DGELU, aux_in=self.fch[l],
+                           colsum=self.grad32(p + "fc_b"))          # fc bias grad from the epilogue panels
             K.linear_wgrad(self.dfch, self.ln2[l], self.grad32(p + "fc_w"), split_k=self._split_k(4 * C, C))
             K.linear_dgrad(self.dfch, self.w16(p + "fc_w"), self.dln)
             K.layernorm_bwd(self.dln, self.x2[l], self.w32(p + "ln2_w"), self.ln_mean[2 * l + 1], self.ln_rstd[2 * l + 1],
@@ -248,8 +248,8 @@ class GPT2Engine:
             K.bias_grad(dx, self.grad32(p + "o_b"))
             K.linear_wgrad(dx, self.atty[l], self.grad32(p + "o_w"), split_k=self._split_k(C, C))
             K.linear_dgrad(dx, self.w16(p + "o_w"), self.datty)
-            K.attention_bwd(self.qkv[l], self.atty[l], self.datty, self.lse[l], self.delta, self.dqkv, self.B, self.T, self.H)
-            K.bias_grad(self.dqkv, self.grad32(p + "qkv_b"))
+            K.attention_bwd(self.qkv[l], self.atty[l], self.datty, self.lse[l], self.delta, self.dqkv, self.B, self.T, self.H,
+                            dbias=self.grad32(p + "qkv_b"))         # qkv bias grad from the accumulator write-out
             K.linear_wgrad(self.dqkv, self.ln1[l], self.grad32(p + "qkv_w"), split_k=self._split_k(3 * C, C))
             K.linear_dgrad(self.dqkv, self.w16(p + "qkv_w"), self.dln)
             K.layernorm_bwd(self.dln, self.res[l], self.w32(p + "ln1_w"), self.ln_mean[2 * l], self.ln_rstd[2 * l],
@@ -327,7 +327,7 @@ class GPT2Engine:
         L = self.L
         P = 2                                     # radix-select passes for bf16
         n = 1 + L * 7 + 2 + 1                     # embedding, per-layer fwd (2 LN, 4 GEMM, attn), lnf+head, xent
-        n += 2 + 1 + L * (4 + 4 + 4 + 2 + 3) + 1  # head dgrad/wgrad, lnf bwd, per layer: 4 bias, 4 wgrad, 4 dgrad, 2 LN, 3 attn, emb
+        n += 2 + 1 + L * (2 + 4 + 4 + 2 + 3) + 1  # head dgrad/wgrad, lnf bwd, per layer: 2 bias (2 more fused), 4 wgrad, 4 dgrad, 2 LN, 3 attn, emb
         n += 1 + 2                                # pack+norm, adam tick, adamw
         if self.security:
             n += 2 + 2 * P + 1 + 5                # stats (moments, final, P x (hist, select), finalize) + exchange/coeff/reduce/exchange/finalize

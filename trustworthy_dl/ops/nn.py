@@ -16,9 +16,15 @@ EPI_NONE, EPI_GELU, EPI_RESIDUAL, EPI_DGELU = 0, 1, 2, 3
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *, lda: int, ldb: int,
          ldc: int, a_mn: bool = False, b_mn: bool = False, bias: Optional[torch.Tensor] = None, epilogue: int = EPI_NONE,
          aux_in: Optional[torch.Tensor] = None, aux_out: Optional[torch.Tensor] = None, ld_aux: int = 0,
-         atomic_f32: bool = False, split_k: int = 1, block_n: int = 0) -> None:
-    """out[M,N] (+)= A @ B^T on tcgen05 (see include/tdl_kernels.h for the layout flags)."""
+         atomic_f32: bool = False, split_k: int = 1, block_n: int = 0, colsum: Optional[torch.Tensor] = None) -> None:
+    """out[M,N] (+)= A @ B^T on tcgen05 (see include/tdl_kernels.h for the layout flags).  ``colsum`` (fp32 [N]):
+    += column sums of the bf16 output, fused into the epilogue."""
     bias_f32 = 1 if (bias is not None and bias.dtype == torch.float32) else 0
+    if colsum is not None:
+        _lib.call("tdl_gemm_bf16_colsum", ptr(a), ptr(b), ptr(out), i64(M), i64(N), i64(K), i64(lda), i64(ldb), i64(ldc),
+                  i32(a_mn), i32(b_mn), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in), ptr(aux_out),
+                  i64(ld_aux or ldc), i32(block_n), ptr(colsum), stream_ptr())
+        return
     _lib.call("tdl_gemm_bf16", ptr(a), ptr(b), ptr(out), i64(M), i64(N), i64(K), i64(lda), i64(ldb), i64(ldc),
               i32(a_mn), i32(b_mn), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in), ptr(aux_out),
               i64(ld_aux or ldc), i32(atomic_f32), i32(split_k), i32(block_n), stream_ptr())
@@ -31,11 +37,11 @@ def linear_fwd(x, w, out, bias=None, epilogue=EPI_NONE, aux_in=None, aux_out=Non
     gemm(x, w, out, M, N, K, lda=K, ldb=K, ldc=N, bias=bias, epilogue=epilogue, aux_in=aux_in, aux_out=aux_out, ld_aux=N)
 
 
-def linear_dgrad(dy, w, dx, epilogue=EPI_NONE, aux_in=None):
-    """dx [M,K] = dy [M,N] @ w [N,K]  (w consumed MN-major, no transpose copy)."""
+def linear_dgrad(dy, w, dx, epilogue=EPI_NONE, aux_in=None, colsum=None):
+    """dx [M,K] = dy [M,N] @ w [N,K]  (w consumed MN-major, no transpose copy); colsum [K] fp32 += column sums of dx."""
     M, N = dy.shape
     K = w.shape[1]
-    gemm(dy, w, dx, M, K, N, lda=N, ldb=K, ldc=K, b_mn=True, epilogue=epilogue, aux_in=aux_in, ld_aux=K)
+    gemm(dy, w, dx, M, K, N, lda=N, ldb=K, ldc=K, b_mn=True, epilogue=epilogue, aux_in=aux_in, ld_aux=K, colsum=colsum)
 
 
 def linear_wgrad(dy, x, dw32, split_k=1):
@@ -49,9 +55,10 @@ def attention_fwd(qkv, out, lse, B, T, H):
     _lib.call("tdl_attention_fwd", ptr(qkv), ptr(out), ptr(lse), i64(B), i64(T), i64(H), i64(64), stream_ptr())
 
 
-def attention_bwd(qkv, out, d_out, lse, delta, dqkv, B, T, H):
-    _lib.call("tdl_attention_bwd", ptr(qkv), ptr(out), ptr(d_out), ptr(lse), ptr(delta), ptr(dqkv), i64(B), i64(T),
-              i64(H), i64(64), stream_ptr())
+def attention_bwd(qkv, out, d_out, lse, delta, dqkv, B, T, H, dbias=None):
+    """dbias (fp32 [3C], optional) += column sums of dqkv (the qkv bias gradient), fused into the accumulator write-out."""
+    _lib.call("tdl_attention_bwd_dbias", ptr(qkv), ptr(out), ptr(d_out), ptr(lse), ptr(delta), ptr(dqkv), ptr(dbias),
+              i64(B), i64(T), i64(H), i64(64), stream_ptr())
 
 
 def layernorm_fwd(x, w, b, y, mean, rstd, eps=1e-5):

@@ -48,8 +48,16 @@ def is_gloo() -> bool:
     return dist.is_initialized() and dist.get_backend() == "gloo"
 
 
+def _wire_device(device: torch.device) -> torch.device:
+    """Device a message travels on: host memory under gloo, always a GPU under NCCL (which has no CPU transport)."""
+    if is_gloo():
+        return torch.device("cpu")
+    device = torch.device(device)
+    return device if device.type == "cuda" else torch.device("cuda", torch.cuda.current_device())
+
+
 def _comm_device(t: torch.Tensor) -> torch.device:
-    return torch.device("cpu") if is_gloo() else t.device
+    return _wire_device(t.device)
 
 
 def _header(t: torch.Tensor) -> torch.Tensor:
@@ -75,7 +83,7 @@ def send_tensor(t: torch.Tensor, dst: int, tag: int = 0) -> None:
 
 
 def recv_tensor(src: int, device: torch.device, tag: int = 0) -> torch.Tensor:
-    dev = torch.device("cpu") if is_gloo() else device
+    dev = _wire_device(device)
     hdr = torch.empty(8, dtype=torch.int64, device=dev)
     dist.recv(hdr, src, tag=tag)
     h = hdr.cpu().tolist()

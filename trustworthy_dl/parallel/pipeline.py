@@ -362,15 +362,18 @@ class PipelineStrategy:
             flat = torch.cat([p.detach().reshape(-1).float() for p in st.state_dict().values()
                               if p.is_floating_point()] or [torch.zeros(1)])
             cs = float(flat.double().sum().item())
-            comm.send_tensor(torch.cat([flat.cpu(), torch.tensor([cs], dtype=torch.float32)]), dst, tag=2)
+            # GPU->GPU over NVLink under NCCL (the wire device is the stage's own device); host memory under gloo
+            comm.send_tensor(torch.cat([flat, torch.tensor([cs], dtype=torch.float32, device=flat.device)]), dst, tag=2)
             opt = self.t.optimizers.pop(sid, None)
             self.t.schedulers.pop(sid, None)
             st.to("cpu")
             for p in st.parameters():
                 p.grad = None
         elif self.rank == dst:
-            buf = comm.recv_tensor(src, torch.device("cpu"), tag=2)
+            buf = comm.recv_tensor(src, self.device, tag=2)
             flat = buf[:-1]
+            if abs(float(flat.double().sum().item()) - float(buf[-1].item())) > 1e-3 * max(1.0, abs(float(buf[-1].item()))):
+                raise RuntimeError(f"stage {sid}: parameter checksum mismatch after migration {src}->{dst}")
             off = 0
             sd = st.state_dict()
             for k, v in sd.items():
