@@ -1,6 +1,6 @@
 // Phase-level trace of the persistent attention backward kernel (MODE 0 then MODE 1): unity build with TDL_ATTN_TRACE.
 // nvcc -gencode arch=compute_100a,code=sm_100a -O3 --use_fast_math -I csrc -DTDL_ATTN_TRACE_TID=33 bench/attn_bwd_trace.cu -o bench/bin/attn_bwd_trace -lcuda
-// TID 0..255 = a math thread, 256 = the MMA-issue thread
+// TID < BWD_WS_MATH = a math thread, BWD_WS_MATH (512 with 4 threads per row) = the MMA-issue thread
 #ifndef TDL_ATTN_TRACE_TID
 #define TDL_ATTN_TRACE_TID 33
 #endif
@@ -35,8 +35,8 @@ int main() {
     std::vector<long long> tr(2 * n);
     cudaMemcpyFromSymbol(tr.data(), g_trace, sizeof(long long) * 2 * n);
     printf("thread %d of CTA 0: %d stamps (both kernels back to back; tag: cycles since previous stamp)\n", TDL_ATTN_TRACE_TID, n);
-    printf("math tags: 20 loop top | 21 S ready | 22 dP ready | 23 dP chunk in regs | 24 chunk computed+stored | 25 p_full arrived | 26 stats barrier | 27 acc ready | 28 acc written\n");
-    printf("mma tags : 30 loop top | 31 dP(j+1) issued | 32 p_full seen | 33 acc(j) issued | 34 acc(j) done | 35 S(j+2) issued\n");
+    printf("math tags: 20 loop top | 21 S ready | 22 exp done | 23 dP ready | 24 dS computed+stored | 25 p_full arrived | 26 stats barrier | 27 acc ready | 28 acc written\n");
+    printf("mma tags : 30 loop top | 32 p_full seen | 33 acc(j)+dP(j+1) issued | 34 acc(j) done | 35 S(j+2) issued\n");
     for (int i = 1; i < n && i < 400; ++i) {
         printf(" %2lld:%5lld", tr[2 * i], tr[2 * i + 1] - tr[2 * i - 1]);
         if (tr[2 * i] == 26 || tr[2 * i] == 28 || tr[2 * i] == 35) printf("\n");

@@ -148,16 +148,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
 
     // S(j+1) = Q K_{j+1}^T is queued on the tensor pipe right behind P_j V_j (the S accumulator is already in
     // registers by then), so the next block's scores are ready when the softmax warps come back for them.
-    auto issue_s = [&](int jj) {                     // thread 0 only
+    // MMA issue: warp 0 waits as a whole, one elected lane issues with precomputed descriptor low words (a lone thread
+    // that rebuilds descriptors under `if (tid == 0)` spends ~70 clk per tcgen05.mma, which sat on the critical path).
+    const uint32_t q_lo = umma_desc_lo(smem_u32(sQ), 16);
+    auto issue_s = [&](int jj) {                     // warp 0, converged
         const int b2 = jj & 1;
         mbar_wait(&bar_kv[b2], (jj >> 1) & 1);
         tc_fence_after();
+        const uint32_t k_lo = umma_desc_lo(smem_u32(sK + b2 * TILE_BYTES), 16);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-            umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + b2 * TILE_BYTES, k), idesc_s, k > 0);
-        umma_commit(bar_s);
+            for (int k = 0; k < D / 16; ++k) umma_bf16_ss_lo(tmem_s, q_lo + 2 * k, k_lo + 2 * k, idesc_s, k > 0);
+            umma_commit(bar_s);
+        }
+        __syncwarp();
     };
-    if (tid == 0) { mbar_wait(bar_q, 0); issue_s(0); }
+    if (warp == 0) { mbar_wait(bar_q, 0); issue_s(0); }
     for (int j = 0; j < n_kv; ++j) {
         const int buf = j & 1;
         if (tid == 0 && j + 1 < n_kv) {              // prefetch next K/V into the other buffer
@@ -218,13 +224,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         tc_fence_before();
         __syncthreads();
         TRACE_AT(7);
-        if (tid == 0) {
+        if (warp == 0) {
             tc_fence_after();
+            const uint32_t p_lo = umma_desc_lo(smem_u32(sP), 16);
+            const uint32_t v_lo = umma_desc_lo(smem_u32(sV + buf * TILE_BYTES), TILE_BYTES);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-                umma_bf16_ss(tmem_o, desc_kmajor(sP + (k >> 2) * TILE_BYTES, k & 3),
-                             desc_mnmajor(sV + buf * TILE_BYTES, k, TILE_BYTES), idesc_o, k > 0);
-            umma_commit(bar_o);
+                for (int k = 0; k < BK / 16; ++k)    // A: two K-major 64-column sub-tiles; B: V MN-major, 2048 B per K slice
+                    umma_bf16_ss_lo(tmem_o, p_lo + (k >> 2) * (TILE_BYTES >> 4) + 2 * (k & 3), v_lo + 128 * k, idesc_o, k > 0);
+                umma_commit(bar_o);
+            }
+            __syncwarp();
             if (j + 1 < n_kv) issue_s(j + 1);
         }
         TRACE_AT(8);
@@ -930,14 +940,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_const
 //     43 % of the kernel                                       -> one CTA per SM walks a static, longest-first list of
 //     tiles; barriers, TMEM and the load / MMA pipelines run on across tile boundaries (global iteration counter j), so
 //     the next tile's loads and first MMAs are in flight while the math warps write the previous tile's accumulators.
-// smem (14 tiles = 224 KB): 3 fixed pairs (ring) | 3 stream stages (MODE 0: {Q,dO}; MODE 1: {K,V}) | 2 output staging
+// smem (14 tiles = 224 KB): 2 fixed pairs (ring) | 4 stream stages (MODE 0: {Q,dO}; MODE 1: {K,V}) | 2 output staging
 //       tiles (leave by TMA store) | column statistics
 // TMEM: S0 [0,128)  S1 [128,256)  dP [256,384)  acc0 [384,448)  acc1 [448,512)
 //       inside S[b], the thread that owns columns [64h, 64h+64) stores P at [64h, 64h+32) and dS at [64h+32, 64h+64)
 // =================================================================================================
-constexpr int BWD_WS_THREADS = 320;
-constexpr int BWD_WS_NSTR = 3;
-constexpr int BWD_WS_NFIX = 3;
+constexpr int BWD_WS_NCG = 4;                       // threads per tile row (column groups): 4 -> 16 math warps
+constexpr int BWD_WS_MATH = BWD_WS_NCG * 128;        // math threads
+constexpr int BWD_WS_THREADS = BWD_WS_MATH + 64;     // + MMA-issue warp + TMA warp
+constexpr int BWD_WS_NSTR = 4;       // a stage is refilled when acc(j) retires and needed again by S(j+4): > 1 block of slack
+constexpr int BWD_WS_NFIX = 2;
 constexpr int BWD_WS_SMEM = (2 * BWD_WS_NFIX + 2 * BWD_WS_NSTR + 2) * TILE_BYTES + 2048 + 256;
 
 struct BwdCursor {
@@ -948,11 +960,23 @@ struct BwdCursor {
     int ob, h, b; // decoded tile: outer block, head, batch (integer divisions only when the tile changes)
 };
 
+// width chosen by the register array (32 / 16 columns in, 16 / 8 packed columns out)
+__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32(taddr, r); }
+__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x16(taddr, r); }
+__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[32]) { tmem_st_32x32(taddr, r); }
+__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[16]) { tmem_st_32x16(taddr, r); }
+__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[8]) { tmem_st_32x8(taddr, r); }
+
+__device__ __forceinline__ void named_bar_math(int id) {          // barrier among the math warps only
+    asm volatile("bar.sync %0, %1;" :: "r"(id), "n"(BWD_WS_MATH) : "memory");
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(BWD_WS_THREADS, 1)
 attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
                    const __grid_constant__ CUtensorMap tmap_dqkv, const AttnParams p) {
     constexpr int NSTR = BWD_WS_NSTR, NFIX = BWD_WS_NFIX;
+    constexpr int CW = 128 / BWD_WS_NCG;           // S / dP columns per math thread
     TRACE_DECL;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sFix = smem;                                   // [NFIX][2] : MODE0: K,V   MODE1: Q,dO
@@ -960,8 +984,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     uint8_t* sOut = smem + (2 * NFIX + 2 * NSTR) * TILE_BYTES;                                  // [2] finished dK,dV / dQ tiles
     float* sStat = reinterpret_cast<float*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES);     // [2][2][128]: lse*log2e, delta (MODE 0)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES + 2048);
-    uint64_t* fix_full = bars;                     // [3]
-    uint64_t* fix_empty = bars + 3;                // [3]
+    uint64_t* fix_full = bars;                     // [<= 3]
+    uint64_t* fix_empty = bars + 3;                // [<= 3]
     uint64_t* str_full = bars + 6;                 // [4]
     uint64_t* str_empty = bars + 10;               // [4]
     uint64_t* s_full = bars + 14;                  // [2]
@@ -1007,8 +1031,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); tma_prefetch_desc(&tmap_dqkv);
         for (int s = 0; s < NFIX; ++s) { mbar_init(&fix_full[s], 1); mbar_init(&fix_empty[s], 1); }
         for (int s = 0; s < NSTR; ++s) { mbar_init(&str_full[s], 1); mbar_init(&str_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 8); mbar_init(&acc_done[s], 1); }
-        mbar_init(dp_full, 1); mbar_init(dp_free, 8); mbar_init(acc_free, 8);
+        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], BWD_WS_MATH / 32); mbar_init(&acc_done[s], 1); }
+        mbar_init(dp_full, 1); mbar_init(dp_free, BWD_WS_MATH / 32); mbar_init(acc_free, BWD_WS_MATH / 32);
         fence_barrier_init();
     }
     if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -1018,7 +1042,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_dp = tmem + 256, tmem_a0 = tmem + 384, tmem_a1 = tmem + 448;
 
-    if (warp == 9) {
+    if (warp == BWD_WS_MATH / 32 + 1) {
         // ======================================= TMA producer ====================================
         if (lane == 0) {
             for (BwdCursor c = cur_init(); c.t < total; cur_next(c)) {
@@ -1052,29 +1076,38 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             }
         }
         __syncwarp();
-    } else if (warp == 8) {
+    } else if (warp == BWD_WS_MATH / 32) {
         // ======================================= MMA issue =======================================
-        if (lane == 0) {
+        // the whole warp walks the schedule and waits; one elected lane issues
+        {
             const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
             const uint32_t idesc_ts = umma_idesc_bf16(128, 64, 0, 1);       // acc   : A from TMEM (K along columns) x MN-major B
+            // K-slice k (16 values = 8 packed columns) of P lives in the S columns of the thread group that owns them
+            auto a_col = [](int k) { return (uint32_t)((k * 16 / CW) * CW + ((k * 16) % CW) / 2); };
             // MODE 0: S^T = K Q_i^T, dP^T = V dO_i^T (keys on the lanes); MODE 1: S = Q K_i^T, dP = dO V_i^T
             auto issue_s = [&](const BwdCursor& c) {
                 if (c.it == 0) mbar_wait(&fix_full[c.k % NFIX], (c.k / NFIX) & 1);
                 mbar_wait(&str_full[c.j % NSTR], (c.j / NSTR) & 1);
                 tc_fence_after();
-                const uint8_t* f0 = sFix + (c.k % NFIX) * 2 * TILE_BYTES;
-                const uint8_t* q0 = sStr + (c.j % NSTR) * 2 * TILE_BYTES;
+                const uint32_t a_lo = umma_desc_lo(smem_u32(sFix + (c.k % NFIX) * 2 * TILE_BYTES), 16);
+                const uint32_t b_lo = umma_desc_lo(smem_u32(sStr + (c.j % NSTR) * 2 * TILE_BYTES), 16);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem + (c.j & 1) * 128, desc_kmajor(f0, k), desc_kmajor(q0, k), idesc_s, k > 0);
-                umma_commit(&s_full[c.j & 1]);
+                    for (int k = 0; k < D / 16; ++k)      // K-major operands: 32 bytes (2 descriptor units) per K slice
+                        umma_bf16_ss_lo(tmem + (c.j & 1) * 128, a_lo + 2 * k, b_lo + 2 * k, idesc_s, k > 0);
+                    umma_commit(&s_full[c.j & 1]);
+                }
+                __syncwarp();
             };
             auto issue_dp = [&](const BwdCursor& c) {       // its fixed pair and stream stage were waited for by issue_s
-                const uint8_t* f1 = sFix + (c.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES;
-                const uint8_t* q1 = sStr + (c.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES;
+                const uint32_t a_lo = umma_desc_lo(smem_u32(sFix + (c.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES), 16);
+                const uint32_t b_lo = umma_desc_lo(smem_u32(sStr + (c.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES), 16);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(f1, k), desc_kmajor(q1, k), idesc_s, k > 0);
-                umma_commit(dp_full);
+                    for (int k = 0; k < D / 16; ++k) umma_bf16_ss_lo(tmem_dp, a_lo + 2 * k, b_lo + 2 * k, idesc_s, k > 0);
+                    umma_commit(dp_full);
+                }
+                __syncwarp();
             };
             BwdCursor cs = cur_init(), cd = cur_init(), ca = cur_init();
             if (cs.t < total) { issue_s(cs); cur_next(cs); }
@@ -1085,34 +1118,43 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                 const uint8_t* q0 = sStr + (ca.j % NSTR) * 2 * TILE_BYTES;
                 const uint32_t ts = tmem + bb * 128;
                 TRACE_AT(30);
-                if (cd.t < total) {                                     // dP(j+1) goes in as soon as dP(j) has left TMEM, i.e.
-                    mbar_wait(dp_free, ca.j & 1);                       // while the math warps are still busy with block j
-                    tc_fence_after();
-                    issue_dp(cd); cur_next(cd);
-                }
-                TRACE_AT(31);
                 mbar_wait(&p_full[bb], (ca.j >> 1) & 1);                // P / dS of this iteration sit in S[bb]
-                TRACE_AT(32);
                 if (ca.it == 0 && ca.k > 0) mbar_wait(acc_free, (ca.k - 1) & 1);   // previous tile's accumulators were read out
+                const bool next_dp = cd.t < total;
+                if (next_dp) mbar_wait(dp_free, ca.j & 1);              // dP(j) has left TMEM (arrived before p_full)
                 tc_fence_after();
+                TRACE_AT(32);
+                // Back-to-back MMAs into the SAME accumulator are paced by the accumulate latency (~95 clk measured for
+                // N = 64), not by throughput, so the independent chains of this step -- dV, dK and the next block's dP --
+                // are issued round-robin.
                 const uint32_t accum = ca.it > 0;
-                if (MODE == 0) {
-                    // dV[k, d] += sum_q P^T[k, q] dO[q, d] ;  dK[k, d] += sum_q dS^T[k, q] Q[q, d]
+                // MN-major B tiles: 2048 bytes (128 descriptor units) per K slice; K-major dP operands: 32 bytes (2 units)
+                const uint32_t bq_lo = umma_desc_lo(smem_u32(q0), TILE_BYTES);                  // MODE 0: Q_i    MODE 1: K_i
+                const uint32_t bo_lo = umma_desc_lo(smem_u32(q0 + TILE_BYTES), TILE_BYTES);     // MODE 0: dO_i
+                const uint32_t pa_lo = umma_desc_lo(smem_u32(sFix + (cd.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES), 16);
+                const uint32_t pb_lo = umma_desc_lo(smem_u32(sStr + (cd.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES), 16);
+                if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        umma_bf16_ts(tmem_a0, ts + (k >> 2) * 64 + (k & 3) * 8, desc_mnmajor(q0 + TILE_BYTES, k, TILE_BYTES), idesc_ts, (accum || k > 0));
-#pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        umma_bf16_ts(tmem_a1, ts + (k >> 2) * 64 + 32 + (k & 3) * 8, desc_mnmajor(q0, k, TILE_BYTES), idesc_ts, (accum || k > 0));
-                } else {
-                    // dQ[q, d] += sum_k dS[q, k] K[k, d]
-#pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        umma_bf16_ts(tmem_a0, ts + (k >> 2) * 64 + 32 + (k & 3) * 8, desc_mnmajor(q0, k, TILE_BYTES), idesc_ts, (accum || k > 0));
+                    for (int k = 0; k < 8; ++k) {
+                        if (MODE == 0) {
+                            // dV[k, d] += sum_q P^T[k, q] dO[q, d] ;  dK[k, d] += sum_q dS^T[k, q] Q[q, d]
+                            umma_bf16_ts_lo(tmem_a0, ts + a_col(k), bo_lo + 128 * k, idesc_ts, (accum || k > 0));
+                            umma_bf16_ts_lo(tmem_a1, ts + a_col(k) + CW / 2, bq_lo + 128 * k, idesc_ts, (accum || k > 0));
+                        } else {
+                            // dQ[q, d] += sum_k dS[q, k] K[k, d]
+                            umma_bf16_ts_lo(tmem_a0, ts + a_col(k) + CW / 2, bq_lo + 128 * k, idesc_ts, (accum || k > 0));
+                        }
+                        if (next_dp && k < D / 16) {                    // dP(j+1): its operands were waited for by issue_s(j+1)
+                            umma_bf16_ss_lo(tmem_dp, pa_lo + 2 * k, pb_lo + 2 * k, idesc_s, k > 0);
+                            if (k == D / 16 - 1) umma_commit(dp_full);
+                        }
+                    }
+                    umma_commit(&acc_done[bb]);
+                    umma_commit(&str_empty[ca.j % NSTR]);               // the stream stage can be refilled
+                    if (ca.it == ca.n - 1) umma_commit(&fix_empty[ca.k % NFIX]);
                 }
-                umma_commit(&acc_done[bb]);
-                umma_commit(&str_empty[ca.j % NSTR]);                   // the stream stage can be refilled
-                if (ca.it == ca.n - 1) umma_commit(&fix_empty[ca.k % NFIX]);
+                __syncwarp();
+                if (next_dp) cur_next(cd);
                 TRACE_AT(33);
                 if (cs.t < total) {
                     mbar_wait(&acc_done[bb], (ca.j >> 1) & 1);          // acc(j) is done with S[bb]
@@ -1125,12 +1167,14 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         __syncwarp();
     } else {
         // ===================================== math warps =========================================
-        // two threads per tile row: warp w reads TMEM lane quarter (w & 3) and owns column half (w >> 2)
-        const int quarter = warp & 3, half = warp >> 2;
+        // NCG threads per tile row: warp w reads TMEM lane quarter (w & 3) and owns the CW columns of group (w >> 2).
+        // More, narrower threads (4 x 32 columns) keep four warps per scheduler, which is what hides the tcgen05.ld /
+        // barrier latencies between the MUFU-bound stretches.
+        const int quarter = warp & 3, cg = warp >> 2;
         const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
         const int r = quarter * 32 + lane;
-        // MODE 0: the query block's statistics run along the columns: thread tid fetches lse (tid < 128) or delta of one
-        // query of the NEXT block at the top of an iteration and parks it in shared memory at the end (latency hidden)
+        // MODE 0: the query block's statistics run along the columns: thread tid fetches lse (tid < 128) or delta
+        // (tid < 256) of one query of the NEXT block at the top of an iteration and parks it in shared memory at the end
         auto fetch_stat = [&](const BwdCursor& c) {
             const long long idx = (long long)(c.b * p.H + c.h) * p.T + (long long)(c.ob + c.it) * 128 + (tid & 127);
             return tid < 128 ? p.lse[idx] : p.delta[idx];      // raw: scaled when parked, so nothing waits on the load here
@@ -1147,27 +1191,30 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             tc_fence_after();
             TRACE_AT(27);
             if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile's stores have read the staging
-            asm volatile("bar.sync 2, 256;" ::: "memory");
+            named_bar_math(2);
             float* db = p.dbias != nullptr ? p.dbias + pend_h * D : nullptr;
+            constexpr int AW = D / BWD_WS_NCG;         // accumulator columns per thread (32 or 16)
             auto stage_acc = [&](uint32_t taddr, uint8_t* tile, float mul, float* dbias) {
-                uint32_t raw[32];                  // each of the two row threads handles 32 of the 64 columns
-                tmem_ld_32x32(taddr + lane_base + half * 32, raw);
+                uint32_t raw[AW];
+                tmem_ld_n(taddr + lane_base + cg * AW, raw);
                 tmem_ld_wait();
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < AW / 8; ++q) {
                     uint4 u;
                     u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
                     u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
                     u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
                     u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
-                    *reinterpret_cast<uint4*>(tile + swz(r, half * 4 + q)) = u;
+                    *reinterpret_cast<uint4*>(tile + swz(r, cg * (AW / 8) + q)) = u;
                 }
-                if (dbias != nullptr) {                // qkv bias gradient: column sums of the bf16-rounded tile
-                    float v[32];
+                if (dbias != nullptr) {
+                    // qkv bias gradient: column sums of the bf16-rounded tile.  Transposing butterfly over the warp's 32
+                    // rows: each round halves the values a lane carries; lane l ends with the sum of column l % AW.
+                    float v[AW];
 #pragma unroll
-                    for (int j2 = 0; j2 < 32; ++j2) v[j2] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j2]) * mul));
+                    for (int j2 = 0; j2 < AW; ++j2) v[j2] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j2]) * mul));
 #pragma unroll
-                    for (int off = 16; off >= 1; off >>= 1) {
+                    for (int off = AW / 2; off >= 1; off >>= 1) {
                         const bool up = (lane & off) != 0;
 #pragma unroll
                         for (int j2 = 0; j2 < off; ++j2) {
@@ -1176,7 +1223,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                             v[j2] = keep + __shfl_xor_sync(0xffffffffu, send, off);
                         }
                     }
-                    atomicAdd(dbias + half * 32 + lane, v[0]);
+                    if constexpr (AW == 16) v[0] += __shfl_xor_sync(0xffffffffu, v[0], 16);
+                    if (lane < AW) atomicAdd(dbias + cg * AW + lane, v[0]);
                 }
             };
             if (MODE == 0) {
@@ -1189,7 +1237,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_free);              // the accumulators are in registers / shared memory
             fence_proxy_async_smem();
-            asm volatile("bar.sync 2, 256;" ::: "memory");
+            named_bar_math(2);
             if (tid == 0) {
                 const int grow = pend_b * p.T + pend_ob * 128;
                 if (MODE == 0) {
@@ -1206,8 +1254,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         BwdCursor c = cur_init(), cn = cur_init();
         if (cn.t < total) cur_next(cn);
         if (MODE == 0 && c.t < total) {
-            sStat[tid] = fetch_stat(c) * stat_mul;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (tid < 256) sStat[tid] = fetch_stat(c) * stat_mul;
+            named_bar_math(1);
         }
         float lse2 = 0.f, dlt = 0.f;
         for (; c.t < total; cur_next(c)) {
@@ -1219,66 +1267,75 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             }
             const int bb = c.j & 1;
             const bool diag = MODE == 0 ? (c.it == 0) : (c.it == c.n - 1);
-            const uint32_t ts = tmem + bb * 128 + lane_base + half * 64;
-            const float4* st_l = reinterpret_cast<const float4*>(sStat + bb * 256 + half * 64);
-            const float4* st_d = reinterpret_cast<const float4*>(sStat + bb * 256 + 128 + half * 64);
+            const uint32_t ts = tmem + bb * 128 + lane_base + cg * CW;
+            const float4* st_l = reinterpret_cast<const float4*>(sStat + bb * 256 + cg * CW);
+            const float4* st_d = reinterpret_cast<const float4*>(sStat + bb * 256 + 128 + cg * CW);
             float stat_next = 0.f;
-            if (MODE == 0 && cn.t < total) stat_next = fetch_stat(cn);
-            // dP(j) was queued while block j-1 was still being processed, so both inputs are (nearly) there: exp (MUFU)
-            // and the dS arithmetic (FMA pipe) of different elements interleave instead of running as two phases.
-            uint32_t rs_[64];
+            if (MODE == 0 && tid < 256 && cn.t < total) stat_next = fetch_stat(cn);
+            // exp first (needs only S(j), which has been ready for a while), dS when dP(j) lands: dP(j) is issued together
+            // with acc(j-1), i.e. it completes while this block's exponentials are being computed.
+            float e[CW];
             TRACE_AT(20);
             mbar_wait(&s_full[bb], (c.j >> 1) & 1);
             tc_fence_after();
             TRACE_AT(21);
-            tmem_ld_32x32(ts, *reinterpret_cast<uint32_t(*)[32]>(&rs_[0]));
-            tmem_ld_32x32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&rs_[32]));
+            {
+                uint32_t rs_[CW];
+#pragma unroll
+                for (int q = 0; q < CW / 32; ++q) tmem_ld_32x32(ts + q * 32, *reinterpret_cast<uint32_t(*)[32]>(&rs_[q * 32]));
+                tmem_ld_wait();
+                if (diag) {                                    // causal mask only in the diagonal block (warp-uniform branch)
+#pragma unroll
+                    for (int k = 0; k < CW; ++k) {
+                        const int cc = cg * CW + k;            // MODE 0: row = key, column = query; MODE 1: the transpose
+                        if (MODE == 0 ? (cc < r) : (cc > r)) rs_[k] = 0xff800000u;   // -inf -> P = 0
+                    }
+                }
+#pragma unroll
+                for (int k4 = 0; k4 < CW / 4; ++k4) {
+                    float4 l4 = make_float4(lse2, lse2, lse2, lse2);
+                    if (MODE == 0) l4 = st_l[k4];
+                    e[k4 * 4 + 0] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 0]), p.scale_log2, -l4.x));
+                    e[k4 * 4 + 1] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 1]), p.scale_log2, -l4.y));
+                    e[k4 * 4 + 2] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 2]), p.scale_log2, -l4.z));
+                    e[k4 * 4 + 3] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 3]), p.scale_log2, -l4.w));
+                }
+            }
+            TRACE_AT(22);
+            if (MODE == 0) {                                   // P (bf16 pairs along the K index) -> first half of this thread's S columns
+                uint32_t pk[CW / 2];
+#pragma unroll
+                for (int k = 0; k < CW / 2; ++k) pk[k] = pack_bf16x2(e[2 * k], e[2 * k + 1]);
+                tmem_st_n(ts, pk);
+            }
             mbar_wait(dp_full, c.j & 1);
             tc_fence_after();
-            TRACE_AT(22);
+            TRACE_AT(23);
+            {
+                uint32_t rd_[CW];
 #pragma unroll
-            for (int cc2 = 0; cc2 < 2; ++cc2) {
-                uint32_t rd_[32];
-                tmem_ld_32x32(tmem_dp + lane_base + half * 64 + cc2 * 32, rd_);
+                for (int q = 0; q < CW / 32; ++q) tmem_ld_32x32(tmem_dp + lane_base + cg * CW + q * 32, *reinterpret_cast<uint32_t(*)[32]>(&rd_[q * 32]));
                 tmem_ld_wait();
-                TRACE_AT(23);
-                if (cc2 == 1) {                                 // dP(j) is in registers: the tensor core may overwrite it
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(dp_free);
-                }
-                uint32_t pkp[16], pkd[16];
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(dp_free);           // dP(j) is in registers: the tensor core may overwrite it
 #pragma unroll
-                for (int k4 = 0; k4 < 8; ++k4) {
-                    float l[4], d[4];
-                    if (MODE == 0) {
-                        const float4 l4 = st_l[cc2 * 8 + k4], d4 = st_d[cc2 * 8 + k4];
-                        l[0] = l4.x; l[1] = l4.y; l[2] = l4.z; l[3] = l4.w;
-                        d[0] = d4.x; d[1] = d4.y; d[2] = d4.z; d[3] = d4.w;
-                    } else {
-                        l[0] = l[1] = l[2] = l[3] = lse2;
-                        d[0] = d[1] = d[2] = d[3] = dlt;
-                    }
-                    float e4[4], s4[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int k = cc2 * 32 + k4 * 4 + u;   // column inside this thread's 64
-                        uint32_t sv = rs_[k];
-                        if (diag) {                             // causal mask only in the diagonal block (warp-uniform branch)
-                            const int cc = half * 64 + k;       // MODE 0: row = key, column = query; MODE 1: the transpose
-                            if (MODE == 0 ? (cc < r) : (cc > r)) sv = 0xff800000u;   // -inf -> P = 0
-                        }
-                        e4[u] = exp2f(fmaf(__uint_as_float(sv), p.scale_log2, -l[u]));
-                        s4[u] = e4[u] * (__uint_as_float(rd_[k4 * 4 + u]) - d[u]);
-                    }
-                    pkp[k4 * 2 + 0] = pack_bf16x2(e4[0], e4[1]); pkp[k4 * 2 + 1] = pack_bf16x2(e4[2], e4[3]);
-                    pkd[k4 * 2 + 0] = pack_bf16x2(s4[0], s4[1]); pkd[k4 * 2 + 1] = pack_bf16x2(s4[2], s4[3]);
+                for (int k4 = 0; k4 < CW / 4; ++k4) {
+                    float4 d4 = make_float4(dlt, dlt, dlt, dlt);
+                    if (MODE == 0) d4 = st_d[k4];
+                    e[k4 * 4 + 0] *= (__uint_as_float(rd_[k4 * 4 + 0]) - d4.x);
+                    e[k4 * 4 + 1] *= (__uint_as_float(rd_[k4 * 4 + 1]) - d4.y);
+                    e[k4 * 4 + 2] *= (__uint_as_float(rd_[k4 * 4 + 2]) - d4.z);
+                    e[k4 * 4 + 3] *= (__uint_as_float(rd_[k4 * 4 + 3]) - d4.w);
                 }
-                // P (MODE 0) -> S[bb] columns [64h, 64h+32), dS -> [64h+32, 64h+64); bf16 pairs along the K index
-                if (MODE == 0) tmem_st_32x16(ts + cc2 * 16, pkp);
-                tmem_st_32x16(ts + 32 + cc2 * 16, pkd);
-                TRACE_AT(24);
             }
+            {                                                  // dS -> second half of this thread's S columns
+                uint32_t pk[CW / 2];
+#pragma unroll
+                for (int k = 0; k < CW / 2; ++k) pk[k] = pack_bf16x2(e[2 * k], e[2 * k + 1]);
+                tmem_st_n(ts + CW / 2, pk);
+            }
+            TRACE_AT(24);
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
@@ -1287,8 +1344,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             if (pend) write_tile();                            // previous tile's accumulators (its last MMAs ran under this block)
             // stage the next block's statistics (other buffer); everyone is done reading this block's after the barrier
             if (MODE == 0) {
-                sStat[(bb ^ 1) * 256 + tid] = stat_next * stat_mul;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (tid < 256) sStat[(bb ^ 1) * 256 + tid] = stat_next * stat_mul;
+                named_bar_math(1);
             }
             TRACE_AT(26);
             if (cn.t < total) cur_next(cn);
