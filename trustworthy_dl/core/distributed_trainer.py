@@ -110,6 +110,7 @@ class TrainingConfig:
     deferred_detection: bool = True
     checkpoint_dir: str = "checkpoints"
     migration_model: str = "reference"         # reference (1 GiB/s + 2 s) | nvlink
+    detector_require_evidence: bool = True     # an anomaly verdict needs >= 1 statistic beyond z_evidence (False = reference rule)
     initial_trust: float = 1.0
     steps_per_epoch: Optional[int] = None
     seq_len: Optional[int] = None
@@ -152,7 +153,7 @@ class DistributedTrainer:
         self.trust_manager.resize(config.num_nodes)
         self.node_monitor = NodeMonitor()
         self.gradient_verifier = GradientVerifier(clip_norm=config.clip_norm)
-        self.attack_detector = AttackDetector()
+        self.attack_detector = AttackDetector(require_evidence=config.detector_require_evidence)
         self.parameter_monitor = ParameterMonitor()
         self.metrics_collector = MetricsCollector()
         self.attacker = attacker

@@ -106,11 +106,14 @@ class StatRing:
 
 def decide_from_baseline(current: np.ndarray, base_mean: np.ndarray, base_std: np.ndarray,
                          names: Sequence[str], z_evidence: float = 3.0, z_decision: float = 2.5,
-                         l2_cut: float = 5.0, std_cut: float = 4.0):
+                         l2_cut: float = 5.0, std_cut: float = 4.0, require_evidence: bool = False):
     """Pure decision function shared by the host detector and the tests of the device kernel.
 
     Returns ``(is_attack, attack_type, confidence, evidence, overall)``; mirrors reference
-    ``_detect_statistical_anomaly`` + ``_classify_attack_type`` (:292-363)."""
+    ``_detect_statistical_anomaly`` + ``_classify_attack_type`` (:292-363).  ``require_evidence`` (extension, off = the
+    reference's rule) additionally asks for at least one statistic beyond ``z_evidence``: a run whose statistics all
+    drift a little (early training) can push the MEAN z over the decision threshold without any single outlier, which
+    the reference reports as an attack of type ``None``."""
     valid = base_std > 0
     with np.errstate(divide="ignore", invalid="ignore"):
         z = np.abs((current - base_mean) / np.where(valid, base_std, 1.0))
@@ -120,7 +123,7 @@ def decide_from_baseline(current: np.ndarray, base_mean: np.ndarray, base_std: n
     for i in np.nonzero(valid & (z > z_evidence))[0]:
         evidence[names[i]] = {"z_score": float(z[i]), "current_value": float(current[i]),
                               "baseline_mean": float(base_mean[i]), "baseline_std": float(base_std[i])}
-    is_attack = bool(overall > z_decision)
+    is_attack = bool(overall > z_decision) and (bool(evidence) or not require_evidence)
     if not evidence:
         atype = None
     elif "norm_l2" in evidence and evidence["norm_l2"]["z_score"] > l2_cut:
@@ -145,7 +148,7 @@ class AttackDetector:
                  min_history: int = 10, z_evidence: float = 3.0, z_decision: float = 2.5,
                  l2_cut: float = 5.0, std_cut: float = 4.0, byzantine_threshold: float = 0.5,
                  backdoor_kl_threshold: float = 2.0, ml_min_history: int = 50,
-                 byzantine_mode: str = "pairwise",
+                 byzantine_mode: str = "pairwise", require_evidence: bool = False,
                  stats_fn: Optional[Callable[[torch.Tensor], Sequence[float]]] = None,
                  clock: Callable[[], float] = time.time):
         self.detection_threshold = float(detection_threshold)
@@ -157,6 +160,7 @@ class AttackDetector:
         self.backdoor_kl_threshold = float(backdoor_kl_threshold)
         self.ml_min_history = int(ml_min_history)
         self.byzantine_mode = byzantine_mode
+        self.require_evidence = bool(require_evidence)
         self.clock = clock
         if stats_fn is None:
             from ..ops.stats import tensor_statistics
@@ -209,7 +213,7 @@ class AttackDetector:
         baselines[node_id] = self._baseline_dict(hist, names, with_minmax)
         is_attack, atype, conf, evidence, overall = decide_from_baseline(
             vec, hist.mean(0), hist.std(0), names, self.z_evidence, self.z_decision,
-            self.l2_cut, self.std_cut)
+            self.l2_cut, self.std_cut, self.require_evidence)
         return AttackDetectionResult(is_attack, atype, conf, evidence, self.clock(), node_id, overall)
 
     def _no_attack(self, node_id: int) -> AttackDetectionResult:
