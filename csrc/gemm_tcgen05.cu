@@ -43,6 +43,7 @@ struct GemmParams {
     void* C; long long ldc;
     const void* bias;
     const void* aux_in; void* aux_out; long long ld_aux;
+    int raster_group;              // 2-CTA kernel: m-blocks per rasterisation group (<= 1: row-major tile order)
     float* colsum;                 // optional [N] fp32: += column sums of the bf16 output (staged 2-CTA epilogue only)
     // K8 (all-gather -> GEMM): A is row-sharded over `a_shards` peer buffers of `a_shard_rows` rows each, every
     // shard has its own tensor map; m-blocks are visited starting at `m_block_offset` (own shard first).
@@ -399,6 +400,19 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 __device__ __forceinline__ uint32_t panel_off(uint32_t r, uint32_t q8) { return r * 128u + ((q8 ^ (r & 7u)) << 4); }
 
 
+// Tile order of the persistent 2-CTA kernel.  Row-major (n fastest) streams the whole B operand once per m-block, which is
+// fine while B fits in L2 (layer weights) but not for the LM head (N = 50304: B = 103 MB against 3.3 GB of output
+// passing through L2).  Grouped order walks `group` m-blocks x all n-blocks with m fastest: the A slab of the group
+// stays in L2 and B is streamed once per group instead of once per m-block.
+__device__ __forceinline__ void tile_mn(int t, int n_blocks, int m_blocks, int group, int& m, int& n) {
+    if (group <= 1) { m = t / n_blocks; n = t - m * n_blocks; return; }
+    const int per = group * n_blocks;
+    const int g = t / per, r = t - g * per;
+    const int gm = min(group, m_blocks - g * group);
+    n = r / gm;
+    m = g * group + (r - n * gm);
+}
+
 template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -457,10 +471,12 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
             int stage = 0; uint32_t phase = 0;
             for (int w = cluster_id; w < total_work; w += n_clusters) {
                 const int split = w / tiles_mn, t = w % tiles_mn;
-                int m2 = t / p.n_blocks + m2_offset;
+                int m2, nb;
+                tile_mn(t, p.n_blocks, m_blocks2, p.raster_group, m2, nb);
+                m2 += m2_offset;
                 if (m2 >= m_blocks2) m2 -= m_blocks2;
                 const int m_idx = m2 * 2 * BLOCK_M + (int)cta * BLOCK_M;
-                const int n_idx = (t % p.n_blocks) * BLOCK_N + (int)cta * (BLOCK_N / 2);
+                const int n_idx = nb * BLOCK_N + (int)cta * (BLOCK_N / 2);
                 const CUtensorMap* ta = &tmap_a;
                 int m_local = m_idx;
                 if (p.a_shards > 1) {
@@ -550,10 +566,12 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
         int acc = 0; uint32_t acc_phase = 0;
         for (int w = cluster_id; w < total_work; w += n_clusters) {
             const int t = w % tiles_mn;
-            int m2 = t / p.n_blocks + m2_offset;
+            int m2, nb;
+            tile_mn(t, p.n_blocks, m_blocks2, p.raster_group, m2, nb);
+            m2 += m2_offset;
             if (m2 >= m_blocks2) m2 -= m_blocks2;
             const int m_idx = m2 * 2 * BLOCK_M + (int)cta * BLOCK_M;
-            const int n_idx = (t % p.n_blocks) * BLOCK_N + half * (BLOCK_N / 2);
+            const int n_idx = nb * BLOCK_N + half * (BLOCK_N / 2);
             const int row = m_idx + quarter * 32 + lane;
             const bool row_ok = row < p.M;
             if (!staged) {
@@ -858,6 +876,7 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     p.epilogue = epilogue; p.out_f32_atomic = out_f32_atomic; p.bias_f32 = bias_f32;
     p.C = Cout; p.ldc = ldc; p.bias = bias; p.aux_in = aux_in; p.aux_out = aux_out; p.ld_aux = ld_aux;
     p.colsum = nullptr;
+    p.raster_group = 1;
     TDL_REQUIRE(!(epilogue == EPI_GELU) || aux_out != nullptr, "GELU epilogue needs aux_out");
     TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU) || aux_in != nullptr, "epilogue needs aux_in");
     p.a_shards = a_shards; p.a_shard_rows = (int)a_shard_rows; p.m_block_offset = m_block_offset % p.m_blocks;
@@ -893,6 +912,9 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (two_cta) {
+        static int raster = -1;                 // TDL_GEMM_RASTER=<m-blocks per group> (0/1 = row-major everywhere)
+        if (raster < 0) { const char* e = getenv("TDL_GEMM_RASTER"); raster = e ? atoi(e) : 16; }
+        if (p.n_blocks >= 32 && p.split_k == 1 && p.m_block_offset == 0) p.raster_group = raster;
         EpiMaps em;
         const bool staged = !out_f32_atomic && !c_scatter;
         const bool needs_aux = epilogue != EPI_NONE;

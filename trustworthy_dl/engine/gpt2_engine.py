@@ -30,6 +30,7 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
+from ..utils.timing import nvtx_range
 from ..models.gpt2 import GPT2Config
 from ..ops import _lib, nn as K
 from ..ops.stats import tensor_statistics_device
@@ -271,9 +272,12 @@ class GPT2Engine:
     def _step_body(self) -> None:
         self.loss_sum.zero_()
         self.g32.zero_()
-        self._forward()
-        self._backward()
-        self._security_and_update()
+        with nvtx_range("engine.forward"):
+            self._forward()
+        with nvtx_range("engine.backward"):
+            self._backward()
+        with nvtx_range("engine.security+allreduce+adamw"):
+            self._security_and_update()
 
     # ------------------------------------------------------------------ public step
     def run_step_device(self) -> None:

@@ -22,6 +22,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
+from ..utils.timing import nvtx_range
 from ..core.partition import StageMap
 from . import comm
 from .trust_allreduce import TrustAllReduce
@@ -117,7 +118,8 @@ class DataParallelStrategy:
             t.attacker.poison_gradients(self.rank, [self.reducer.buffer], step)
         ts = time.perf_counter()
         weights = torch.from_numpy(t.trust_manager.aggregation_weights()).float()
-        stats, coeff = self.reducer.reduce_(weights)
+        with nvtx_range("dp.trust_allreduce"):
+            stats, coeff = self.reducer.reduce_(weights)
         stats = stats.detach().cpu().double().numpy()
         # ---- replicated security decisions -----------------------------------------
         vec = torch.cat([out_stats if out_stats is not None else torch.zeros(12, dtype=torch.float64),

@@ -33,6 +33,7 @@ from ..core.partition import StageMap
 from ..ops.reference_impl import NUM_STATS
 from ..ops.stats import tensor_statistics
 from . import comm
+from ..utils.timing import nvtx_range
 
 logger = logging.getLogger(__name__)
 
@@ -204,7 +205,8 @@ class PipelineStrategy:
                     x_in = acts[(s - 1, m)][1].detach()
                 else:
                     tc = time.perf_counter()
-                    x_in = comm.recv_tensor(self._owner(s - 1), self.device, tag=0)
+                    with nvtx_range(f"pp.recv_act s{s} m{m}"):
+                        x_in = comm.recv_tensor(self._owner(s - 1), self.device, tag=0)
                     comm_s += time.perf_counter() - tc
                 if s > 0:
                     # receiver-side verification of the previous stage's output
@@ -213,7 +215,7 @@ class PipelineStrategy:
                         have_stats[s - 1] = 1.0
                     if x_in.is_floating_point():
                         x_in.requires_grad_(True)
-                with t._autocast():
+                with nvtx_range(f"pp.fwd s{s} m{m}"), t._autocast():
                     out = self.stages[s](x_in)
                 if t.attacker is not None:
                     out = t.attacker.poison_output(self.rank, out, step)
@@ -228,15 +230,18 @@ class PipelineStrategy:
             else:
                 x_in, out = acts.pop((s, m))
                 if s == S - 1:
-                    losses[m].backward()
+                    with nvtx_range(f"pp.bwd s{s} m{m}"):
+                        losses[m].backward()
                 else:
                     if self._owner(s + 1) == self.rank:
                         g = self._grad_handoff.pop((s + 1, m))
                     else:
                         tc = time.perf_counter()
-                        g = comm.recv_tensor(self._owner(s + 1), self.device, tag=1)
+                        with nvtx_range(f"pp.recv_grad s{s} m{m}"):
+                            g = comm.recv_tensor(self._owner(s + 1), self.device, tag=1)
                         comm_s += time.perf_counter() - tc
-                    out.backward(g)
+                    with nvtx_range(f"pp.bwd s{s} m{m}"):
+                        out.backward(g)
                 if s > 0 and x_in is not None and x_in.grad is not None:
                     if self._owner(s - 1) == self.rank:
                         self._grad_handoff[(s, m)] = x_in.grad
