@@ -15,6 +15,7 @@ from collections import defaultdict
 def main():
     src_csv, dis, key = sys.argv[1:4]
     source = sys.argv[4] if len(sys.argv) > 4 else None
+    nth = int(sys.argv[5]) if len(sys.argv) > 5 else 0        # which matching launch in the report
     # --- line number per SASS instruction (in order) from nvdisasm
     lines = []
     cur = None
@@ -42,8 +43,11 @@ def main():
         if k["hdr"] is None:
             k["hdr"] = r; continue
         k["rows"].append(r)
-    want = re.sub(r"ILi(\d)E", r"<(int)\1>", key)
-    k = [x for x in kern if want.split("<")[0] in x["name"] and want.split("<")[1][:6] in x["name"]][0]
+    # `key` is a substring of the mangled name in the disassembly; `match` (optional 7th argument, default: the
+    # function name part of key) is a substring of the demangled name in the ncu report
+    match = sys.argv[6] if len(sys.argv) > 6 else re.split(r"ILi|I[a-z]", key)[0]
+    cands = [x for x in kern if match in x["name"]]
+    k = cands[min(nth, len(cands) - 1)]
     h = k["hdr"]; iS = h.index("# Samples"); iI = h.index("Instructions Executed")
     R = k["rows"]
     print(f"{k['name'][:70]}: {len(R)} SASS rows, {len(lines)} disassembled", file=sys.stderr)

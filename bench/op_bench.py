@@ -101,6 +101,19 @@ def main() -> int:
         us1 = timed(lambda: K.linear_dgrad(dyp, wp, out, epilogue=K.EPI_DGELU, aux_in=pre, colsum=cs), args.iters, flush)
         report("d_proj GEMM (dGELU+colsum)", us1, (M * C + 2 * M * 4 * C) * 2, f"{fl / us1 / 1e6:.0f} TFLOP/s; fused bias grad costs {us1 - us0:+.1f} us")
         del dyp, wp, pre, out
+        xin = torch.randn(M, C, device=dev, dtype=bf)
+        wfc = torch.randn(4 * C, C, device=dev, dtype=bf) * 0.02
+        bfc = torch.zeros(4 * C, device=dev)
+        pre = torch.empty(M, 4 * C, device=dev, dtype=bf); act = torch.empty(M, 4 * C, device=dev, dtype=bf)
+        us2 = timed(lambda: K.linear_fwd(xin, wfc, act, bias=bfc, epilogue=K.EPI_GELU, aux_out=pre), args.iters, flush)
+        report("f_fc GEMM (bias+GELU, 2 outputs)", us2, (M * C + 2 * M * 4 * C) * 2, f"{fl / us2 / 1e6:.0f} TFLOP/s")
+        res = torch.randn(M, C, device=dev, dtype=bf); wo = torch.randn(C, C, device=dev, dtype=bf) * 0.02
+        outo = torch.empty(M, C, device=dev, dtype=bf); bo = torch.zeros(C, device=dev)
+        us3 = timed(lambda: K.linear_fwd(xin, wo, outo, bias=bo, epilogue=K.EPI_RESIDUAL, aux_in=res), args.iters, flush)
+        report("f_o GEMM (bias+residual)", us3, 3 * M * C * 2, f"{2.0 * M * C * C / us3 / 1e6:.0f} TFLOP/s")
+        us4 = timed(lambda: K.linear_fwd(xin, wo, outo, bias=bo), args.iters, flush)
+        report("f_o GEMM (bias only)", us4, 2 * M * C * 2, f"{2.0 * M * C * C / us4 / 1e6:.0f} TFLOP/s")
+        del xin, wfc, pre, act, res, outo
     if "attn" in ops:
         B = args.batch
         qkv = torch.randn(M, 3 * C, device=dev, dtype=bf)

@@ -94,21 +94,27 @@ __device__ __forceinline__ void st_na_v4(void* p, const uint4& v) {
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// tanh-approximated GELU (GPT-2's gelu_new) and its derivative, written for the epilogue's instruction budget:
+//   u = x (k + k c x^2)                     gelu  = h + h tanh(u),  h = x / 2                          (6 ops incl. MUFU.TANH)
+//   a = (1 + tanh u) / 2,  w = 2 x du/dx    gelu' = a + a (1 - a) w   [since 1 - tanh^2 = 4 a (1 - a)]   (9 ops)
 __device__ __forceinline__ float gelu_tanh_f(float x) {
-    const float k = 0.7978845608028654f;
-    float u = k * (x + 0.044715f * x * x * x);
+    const float k = 0.7978845608028654f, kc = 0.7978845608028654f * 0.044715f;
+    const float x2 = x * x;
+    const float u = x * fmaf(x2, kc, k);
     float t;
     asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
-    return 0.5f * x * (1.0f + t);
+    const float h = 0.5f * x;
+    return fmaf(h, t, h);
 }
 __device__ __forceinline__ float gelu_tanh_grad_f(float x) {
-    const float k = 0.7978845608028654f;
-    float x2 = x * x;
-    float u = k * (x + 0.044715f * x * x2);
+    const float k = 0.7978845608028654f, kc = 0.7978845608028654f * 0.044715f;
+    const float x2 = x * x;
+    const float u = x * fmaf(x2, kc, k);
     float t;
     asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
-    float du = k * (1.0f + 3.0f * 0.044715f * x2);
-    return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
+    const float w = x * fmaf(x2, 6.0f * kc, 2.0f * k);       // 2 x du/dx
+    const float a = fmaf(0.5f, t, 0.5f);
+    return fmaf(a, fmaf(-a, w, w), a);
 }
 
 // ---------------------------------------------------------------------------------------------

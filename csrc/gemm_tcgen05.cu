@@ -110,7 +110,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
         }
         // activation is applied to the value that was stored (bf16-rounded), as backward will see it
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
+        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);      // from the fp32 pre-activation (its bf16 copy went to aux_out)
     } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -381,7 +381,8 @@ template <int BLOCK_N, int STAGES_, bool AUX> struct Cfg2 {
     // writes a second tensor); the output leaves through TMA stores, aux_in arrives through TMA loads
     static constexpr int STAGING_BYTES = (AUX ? 4 : 2) * PANEL_BYTES;
     static constexpr int COLSUM_BYTES = 8 * 16 * 4;                       // per epilogue warp: 16 column sums
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + COLSUM_BYTES + 1024 + 256;
+    static constexpr int BIAS_BYTES = 2 * (BLOCK_N / 2) * 4;              // per column half: this tile's bias as fp32
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + COLSUM_BYTES + BIAS_BYTES + 1024 + 256;
 };
 
 struct EpiMaps { CUtensorMap c, aux; };
@@ -425,7 +426,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
     uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;                 // [half][out | aux] panels
     float* colsum_smem = reinterpret_cast<float*>(staging + C::STAGING_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES + C::COLSUM_BYTES);
+    float* bias_smem = reinterpret_cast<float*>(staging + C::STAGING_BYTES + C::COLSUM_BYTES);     // [2][BLOCK_N / 2]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES + C::COLSUM_BYTES + C::BIAS_BYTES);
     uint64_t* full = bars;                       // used in the leader only
     uint64_t* empty = bars + C::STAGES;          // one per CTA
     uint64_t* tmem_full = bars + 2 * C::STAGES;  // one per CTA
@@ -609,6 +611,17 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                     mbar_arrive_expect_tx(&aux_bar[half], PANEL_BYTES);
                     tma_load_2d(aux_panel, &emaps.aux, &aux_bar[half], n_idx, m_idx);
                 }
+                // this half's 128 bias values -> shared memory (one per thread), read back as broadcasts after the first
+                // panel barrier: a global load right before each chunk's bias add stalled the two epilogue warps of a
+                // scheduler for the L2 latency.  Safe to overwrite: every warp passed the previous tile's last barrier.
+                float* bias_s = bias_smem + half * (BLOCK_N / 2);
+                if (p.bias != nullptr) {
+                    const int bc = n_idx + (int)lrow;
+                    float bvl = 0.f;
+                    if (bc < p.N) bvl = p.bias_f32 ? __ldg(reinterpret_cast<const float*>(p.bias) + bc)
+                                                   : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[bc]);
+                    bias_s[lrow] = bvl;
+                }
                 mbar_wait(&tmem_full[acc], acc_phase);
                 __syncwarp();
                 tc_fence_after();
@@ -633,35 +646,28 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[c & 1][j]);
-                    if (p.bias != nullptr && col0 < p.N) {
-                        if (p.bias_f32) {
-                            const float4* bp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                const float4 tb4 = __ldg(bp + q);
-                                v[q * 4 + 0] += tb4.x; v[q * 4 + 1] += tb4.y; v[q * 4 + 2] += tb4.z; v[q * 4 + 3] += tb4.w;
-                            }
-                        } else {
-                            const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0);
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const uint4 u = __ldg(bp + q);
-                                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
-                                v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
-                                v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
-                            }
-                        }
-                    }
                     if (cc == 0) {
                         // the panel buffers are about to be rewritten: the previous TMA stores must have read them
                         if (group_leader) tma_store_wait_read();
                         if (aux_in) mbar_wait(&aux_bar[half], aux_phase);
                         named_bar_sync(bar_id, 128);
                     }
+                    uint4 ua[4];
+                    if (aux_in) {                                       // issued ahead of the bias adds that hide their latency
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) ua[q] = *reinterpret_cast<const uint4*>(aux_panel + panel_off(lrow, cc * 4 + q));
+                    }
+                    if (p.bias != nullptr) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 tb4 = *reinterpret_cast<const float4*>(bias_s + c * 32 + q * 4);
+                            v[q * 4 + 0] += tb4.x; v[q * 4 + 1] += tb4.y; v[q * 4 + 2] += tb4.z; v[q * 4 + 3] += tb4.w;
+                        }
+                    }
                     if (aux_in) {
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            const uint4 u = *reinterpret_cast<const uint4*>(aux_panel + panel_off(lrow, cc * 4 + q));
+                            const uint4 u = ua[q];
                             const float2 f[4] = {unpack_bf16x2(u.x), unpack_bf16x2(u.y), unpack_bf16x2(u.z), unpack_bf16x2(u.w)};
 #pragma unroll
                             for (int e2 = 0; e2 < 4; ++e2) {
@@ -682,7 +688,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                             *reinterpret_cast<uint4*>(aux_panel + panel_off(lrow, cc * 4 + q)) = u;
                         }
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(__bfloat162float(__float2bfloat16_rn(v[j])));
+                        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);      // from the fp32 pre-activation (its bf16 copy went to aux_out)
                     }
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
