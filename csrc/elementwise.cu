@@ -163,6 +163,123 @@ __global__ void __launch_bounds__(256, 2) layernorm_bwd_kernel(const __nv_bfloat
     for (int i = threadIdx.x; i < C; i += blockDim.x) { atomicAdd(&dw[i], sh_dw[i]); atomicAdd(&db[i], sh_db[i]); }
 }
 
+// Four warps per row (8 or 16 columns per lane): the dgamma / dbeta / column-sum partials shrink to 24 registers per
+// thread, which leaves room to have the three input rows (dy, x, dres) in flight together and to keep 4 blocks (32
+// warps) per SM.  Row sums cross the four warps through shared memory and one named barrier per row.
+// dxsum (optional, fp32 [C]) += column sums of the bf16 dx that is written: the bias gradient of the layer below,
+// which used to cost a separate pass over dx.
+template <int IT>
+__global__ void __launch_bounds__(256, IT == 1 ? 3 : 2) layernorm_bwd4_kernel(const __nv_bfloat16* __restrict__ dy,
+        const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ mean,
+        const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx,
+        float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dxsum, int M, int C) {
+    extern __shared__ float sh[];             // [3][C] block accumulators (dw, db, dxsum)
+    __shared__ float part[2][2][4][2];        // [row group][parity][warp][s1, s2]
+    for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh[i] = 0.f;
+    __syncthreads();
+    const int grp = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5, lane = threadIdx.x & 31;
+    float aw[IT][8], ab[IT][8], ao[IT][8], ww[IT][8];
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+        const int col = i * 1024 + t * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { aw[i][j] = 0.f; ab[i][j] = 0.f; ao[i][j] = 0.f; ww[i][j] = 0.f; }
+        if (col < C) {
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + col)), w1 = __ldg(reinterpret_cast<const float4*>(w + col + 4));
+            ww[i][0] = w0.x; ww[i][1] = w0.y; ww[i][2] = w0.z; ww[i][3] = w0.w;
+            ww[i][4] = w1.x; ww[i][5] = w1.y; ww[i][6] = w1.z; ww[i][7] = w1.w;
+        }
+    }
+    const float inv_c = 1.0f / C;
+    int par = 0;
+    for (int row = blockIdx.x * 2 + grp; row < M; row += gridDim.x * 2) {
+        const long long off = (long long)row * C;
+        uint4 rdy[IT], rx[IT], rr[IT];
+#pragma unroll
+        for (int i = 0; i < IT; ++i) {
+            const int col = i * 1024 + t * 8;
+            if (col < C) {
+                rdy[i] = ld_nc_v4(dy + off + col);
+                rx[i] = ld_nc_v4(x + off + col);
+                if (dres != nullptr) rr[i] = ld_nc_v4(dres + off + col);
+            }
+        }
+        const float mu = mean[row], rs = rstd[row];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < IT; ++i) {
+            const int col = i * 1024 + t * 8;
+            if (col < C) {
+                float dyv[8], xv[8];
+                bf16x8_to_f32(rdy[i], dyv);
+                bf16x8_to_f32(rx[i], xv);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float xh = (xv[j] - mu) * rs, g = dyv[j] * ww[i][j];
+                    s1 += g;
+                    s2 += g * xh;
+                    aw[i][j] += dyv[j] * xh;
+                    ab[i][j] += dyv[j];
+                }
+            }
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (lane == 0) { part[grp][par][wq][0] = s1; part[grp][par][wq][1] = s2; }
+        asm volatile("bar.sync %0, 128;" :: "r"(1 + grp) : "memory");
+        s1 = (part[grp][par][0][0] + part[grp][par][1][0] + part[grp][par][2][0] + part[grp][par][3][0]) * inv_c;
+        s2 = (part[grp][par][0][1] + part[grp][par][1][1] + part[grp][par][2][1] + part[grp][par][3][1]) * inv_c;
+        par ^= 1;                                  // the other slot is free: everyone passed this row's barrier
+#pragma unroll
+        for (int i = 0; i < IT; ++i) {
+            const int col = i * 1024 + t * 8;
+            if (col < C) {
+                float dyv[8], xv[8], o[8];
+                bf16x8_to_f32(rdy[i], dyv);
+                bf16x8_to_f32(rx[i], xv);
+                if (dres != nullptr) bf16x8_to_f32(rr[i], o);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) o[j] = 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float xh = (xv[j] - mu) * rs;
+                    o[j] += (dyv[j] * ww[i][j] - s1 - xh * s2) * rs;
+                }
+                const uint4 packed = f32_to_bf16x8(o);
+                *reinterpret_cast<uint4*>(dx + off + col) = packed;
+                if (dxsum != nullptr) {
+                    float ob[8];
+                    bf16x8_to_f32(packed, ob);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) ao[i][j] += ob[j];
+                }
+            }
+        }
+    }
+    // block combine (two row groups) in shared memory, then one vector reduction per 4 columns
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+        const int col = i * 1024 + t * 8;
+        if (col < C) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                atomicAdd(&sh[col + j], aw[i][j]);
+                atomicAdd(&sh[C + col + j], ab[i][j]);
+                if (dxsum != nullptr) atomicAdd(&sh[2 * C + col + j], ao[i][j]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x * 4; i < C; i += blockDim.x * 4) {
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(dw + i), "f"(sh[i]), "f"(sh[i + 1]), "f"(sh[i + 2]), "f"(sh[i + 3]) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(db + i), "f"(sh[C + i]), "f"(sh[C + i + 1]), "f"(sh[C + i + 2]), "f"(sh[C + i + 3]) : "memory");
+        if (dxsum != nullptr)
+            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(dxsum + i), "f"(sh[2 * C + i]), "f"(sh[2 * C + i + 1]), "f"(sh[2 * C + i + 2]), "f"(sh[2 * C + i + 3]) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------------------------ bias grad
 // db[n] += sum_m dy[m, n];  block = 32 column-groups x 8 row lanes, 256 columns per block
 __global__ void __launch_bounds__(256) bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, float* __restrict__ db,
@@ -491,9 +608,27 @@ extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, 
     return 0;
 }
 
-extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
-                                 const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream) {
+extern "C" int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream);
+
+// dxsum (optional, fp32 [C], 16-byte aligned like dw / db): += column sums of the bf16 dx (bias gradient of the layer below)
+extern "C" int tdl_layernorm_bwd_colsum(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
+                                        const void* dres, void* dx, float* dw, float* db, float* dxsum, int64_t M, int64_t C,
+                                        void* stream) {
     TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported", (long long)C);
+    static int variant = -1;                   // TDL_LN_BWD=1: one warp per row (previous kernel)
+    if (variant < 0) { const char* e = getenv("TDL_LN_BWD"); variant = e ? atoi(e) : 4; }
+    const bool aligned = ((reinterpret_cast<uintptr_t>(dw) | reinterpret_cast<uintptr_t>(db) | reinterpret_cast<uintptr_t>(dxsum)) & 15) == 0;
+    if (variant == 4 && C % 4 == 0 && aligned) {
+        const int grid = (int)std::min<long long>((M + 1) / 2, (long long)tdl_num_sms() * (C <= 1024 ? 3 : 2));   // one resident wave
+        const size_t smem = 3 * C * sizeof(float);
+#define LN_BWD4(I) layernorm_bwd4_kernel<I><<<grid, 256, smem, STREAM(stream)>>>( \
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, \
+        dw, db, dxsum, (int)M, (int)C)
+        if (C <= 1024) LN_BWD4(1); else LN_BWD4(2);
+#undef LN_BWD4
+        TDL_LAUNCH_CHECK();
+        return 0;
+    }
     const int grid = (int)std::min<long long>((M + 7) / 8, (long long)tdl_num_sms() * 2);   // one resident wave: fewer dgamma/dbeta atomics
 #define LN_BWD(I) layernorm_bwd_kernel<I><<<grid, 256, 2 * C * sizeof(float), STREAM(stream)>>>( \
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, \
@@ -504,7 +639,13 @@ extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, 
     }
 #undef LN_BWD
     TDL_LAUNCH_CHECK();
+    if (dxsum != nullptr) return tdl_bias_grad(dx, dxsum, M, C, C, stream);
     return 0;
+}
+
+extern "C" int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
+                                 const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream) {
+    return tdl_layernorm_bwd_colsum(dy, x, w, mean, rstd, dres, dx, dw, db, nullptr, M, C, stream);
 }
 
 extern "C" int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream) {

@@ -73,6 +73,9 @@ int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, fl
                       int64_t C, float eps, void* stream);
 int tdl_layernorm_bwd(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
                       const void* dres, void* dx, float* dw, float* db, int64_t M, int64_t C, void* stream);
+/* as above; dxsum (fp32 [C], may be NULL) += column sums of the bf16 dx = bias gradient of the layer below */
+int tdl_layernorm_bwd_colsum(const void* dy, const void* x, const float* w, const float* mean, const float* rstd,
+                             const void* dres, void* dx, float* dw, float* db, float* dxsum, int64_t M, int64_t C, void* stream);
 int tdl_bias_grad(const void* dy, float* db, int64_t M, int64_t N, int64_t ld, void* stream);
 int tdl_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t BT, int64_t T, int64_t C, void* stream);
 int tdl_embedding_bwd(const int64_t* idx, const void* dx, float* dwte, float* dwpe, int64_t BT, int64_t T, int64_t C, void* stream);

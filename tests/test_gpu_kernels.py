@@ -68,6 +68,13 @@ def test_layernorm_fwd_bwd(dev, M, C):
     assert torch.allclose(dx.float(), dxr + dres.float(), atol=3e-2, rtol=3e-2)
     assert torch.allclose(dw, dwr, atol=1e-2 * math.sqrt(M), rtol=1e-2)
     assert torch.allclose(db, dbr, atol=1e-2 * math.sqrt(M), rtol=1e-2)
+    # fused column sums of the written dx (bias gradient of the layer below); accumulates; no dres
+    dx2 = torch.empty_like(x); dw2 = torch.zeros(C, device=dev); db2 = torch.zeros(C, device=dev)
+    cs = torch.full((C,), 0.5, device=dev)
+    K.layernorm_bwd(dy, x, w, mean, rstd, None, dx2, dw2, db2, dxsum=cs)
+    assert torch.allclose(dx2.float(), dxr, atol=3e-2, rtol=3e-2)
+    assert torch.allclose(cs, dx2.float().sum(0) + 0.5, atol=2e-3 * math.sqrt(M), rtol=1e-4), (cs - dx2.float().sum(0) - 0.5).abs().max().item()
+    assert torch.allclose(dw2, dw, atol=1e-3 * math.sqrt(M), rtol=1e-3) and torch.allclose(db2, db, atol=1e-3 * math.sqrt(M), rtol=1e-3)
 
 
 def test_bias_grad_and_embedding(dev):

@@ -231,22 +231,22 @@ class GPT2Engine:
         K.linear_dgrad(dlogits, self.w16("wte"), self.dln)
         K.linear_wgrad(dlogits, self.lnf, self.grad32("wte"), split_k=1)
         dx, dx_next = self.dx_a, self.dx_b
+        # every LayerNorm backward also emits the column sums of the dx it writes = the bias gradient of the linear layer
+        # below it (MLP down-projection under ln_f / ln_1, attention output projection under ln_2)
         K.layernorm_bwd(self.dln, self.res[L], self.w32("lnf_w"), self.ln_mean[2 * L], self.ln_rstd[2 * L], None, dx,
-                        self.grad32("lnf_w"), self.grad32("lnf_b"))
+                        self.grad32("lnf_w"), self.grad32("lnf_b"), dxsum=self.grad32(f"h{L - 1}.proj_b"))
         for l in reversed(range(L)):
             p = f"h{l}."
             # ---- MLP ----
-            K.bias_grad(dx, self.grad32(p + "proj_b"))
             K.linear_wgrad(dx, self.fcg[l], self.grad32(p + "proj_w"), split_k=self._split_k(C, 4 * C))
             K.linear_dgrad(dx, self.w16(p + "proj_w"), self.dfch, epilogue=K.EPI_DGELU, aux_in=self.fch[l],
                            colsum=self.grad32(p + "fc_b"))          # fc bias grad from the epilogue panels
             K.linear_wgrad(self.dfch, self.ln2[l], self.grad32(p + "fc_w"), split_k=self._split_k(4 * C, C))
             K.linear_dgrad(self.dfch, self.w16(p + "fc_w"), self.dln)
             K.layernorm_bwd(self.dln, self.x2[l], self.w32(p + "ln2_w"), self.ln_mean[2 * l + 1], self.ln_rstd[2 * l + 1],
-                            dx, dx_next, self.grad32(p + "ln2_w"), self.grad32(p + "ln2_b"))
+                            dx, dx_next, self.grad32(p + "ln2_w"), self.grad32(p + "ln2_b"), dxsum=self.grad32(p + "o_b"))
             dx, dx_next = dx_next, dx
             # ---- attention ----
-            K.bias_grad(dx, self.grad32(p + "o_b"))
             K.linear_wgrad(dx, self.atty[l], self.grad32(p + "o_w"), split_k=self._split_k(C, C))
             K.linear_dgrad(dx, self.w16(p + "o_w"), self.datty)
             K.attention_bwd(self.qkv[l], self.atty[l], self.datty, self.lse[l], self.delta, self.dqkv, self.B, self.T, self.H,
@@ -254,7 +254,8 @@ class GPT2Engine:
             K.linear_wgrad(self.dqkv, self.ln1[l], self.grad32(p + "qkv_w"), split_k=self._split_k(3 * C, C))
             K.linear_dgrad(self.dqkv, self.w16(p + "qkv_w"), self.dln)
             K.layernorm_bwd(self.dln, self.res[l], self.w32(p + "ln1_w"), self.ln_mean[2 * l], self.ln_rstd[2 * l],
-                            dx, dx_next, self.grad32(p + "ln1_w"), self.grad32(p + "ln1_b"))
+                            dx, dx_next, self.grad32(p + "ln1_w"), self.grad32(p + "ln1_b"),
+                            dxsum=self.grad32(f"h{l - 1}.proj_b") if l > 0 else None)
             dx, dx_next = dx_next, dx
         K.embedding_bwd(self.idx, dx, self.grad32("wte"), self.grad32("wpe"), self.T)
 
@@ -331,7 +332,7 @@ class GPT2Engine:
         L = self.L
         P = 2                                     # radix-select passes for bf16
         n = 1 + L * 7 + 2 + 1                     # embedding, per-layer fwd (2 LN, 4 GEMM, attn), lnf+head, xent
-        n += 2 + 1 + L * (2 + 4 + 4 + 2 + 3) + 1  # head dgrad/wgrad, lnf bwd, per layer: 2 bias (2 more fused), 4 wgrad, 4 dgrad, 2 LN, 3 attn, emb
+        n += 2 + 1 + L * (4 + 4 + 2 + 3) + 1      # head dgrad/wgrad, lnf bwd, per layer: 4 wgrad, 4 dgrad, 2 LN, 3 attn (bias grads fused), emb
         n += 1 + 2                                # pack+norm, adam tick, adamw
         if self.security:
             n += 2 + 2 * P + 1 + 5                # stats (moments, final, P x (hist, select), finalize) + exchange/coeff/reduce/exchange/finalize

@@ -66,10 +66,11 @@ def layernorm_fwd(x, w, b, y, mean, rstd, eps=1e-5):
     _lib.call("tdl_layernorm_fwd", ptr(x), ptr(w), ptr(b), ptr(y), ptr(mean), ptr(rstd), i64(M), i64(C), f32(eps), stream_ptr())
 
 
-def layernorm_bwd(dy, x, w, mean, rstd, dres, dx, dw, db):
+def layernorm_bwd(dy, x, w, mean, rstd, dres, dx, dw, db, dxsum=None):
+    """dx = dres + LN'(dy); dw/db += dgamma/dbeta; dxsum (fp32 [C], optional) += column sums of dx."""
     M, C = x.shape
-    _lib.call("tdl_layernorm_bwd", ptr(dy), ptr(x), ptr(w), ptr(mean), ptr(rstd), ptr(dres), ptr(dx), ptr(dw), ptr(db),
-              i64(M), i64(C), stream_ptr())
+    _lib.call("tdl_layernorm_bwd_colsum", ptr(dy), ptr(x), ptr(w), ptr(mean), ptr(rstd), ptr(dres), ptr(dx), ptr(dw), ptr(db),
+              ptr(dxsum), i64(M), i64(C), stream_ptr())
 
 
 def bias_grad(dy, db32):
