@@ -7,9 +7,9 @@
 // Forward (one CTA = one 128-query block of one head, 2 CTAs per SM):
 //   S = Q K^T      tcgen05.mma, K-major operands, fp32 S in TMEM (128 lanes x 128 columns)
 //   softmax        each of the 128 threads owns one query row (tcgen05.ld 32x32b), online max/sum in
-//                  registers, exp2 with the scale folded in, P written to smem as bf16 in the
-//                  128B-swizzled K-major layout the tensor core reads
-//   O += P V       tcgen05.mma with V consumed MN-major exactly as it sits in memory; partial
+//                  registers, exp2 with the scale folded in, P written back to tensor memory as bf16 pairs
+//                  (tcgen05.st) -- no shared-memory round trip
+//   O += P V       tcgen05.mma with A = P from TMEM and V consumed MN-major exactly as it sits in memory; partial
 //                  products land in TMEM and are folded into the register accumulator with the
 //                  running rescale
 // Backward = preprocess (delta = rowsum(dO*O)) + two tensor-core kernels:
@@ -100,8 +100,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     uint8_t* sQ = smem;
     uint8_t* sK = smem + TILE_BYTES;              // 2 buffers
     uint8_t* sV = smem + 3 * TILE_BYTES;          // 2 buffers
-    uint8_t* sP = smem + 5 * TILE_BYTES;          // [128 x 128] = 2 sub-tiles
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * TILE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * TILE_BYTES);
     uint64_t* bar_q = bars;
     uint64_t* bar_kv = bars + 1;                  // [2]
     uint64_t* bar_s = bars + 3;
@@ -127,7 +126,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
+    // S [0,128) fp32 | O block product [128,192) | P [192,256) as bf16 pairs: the A operand of P V straight from TMEM
+    const uint32_t tmem_s = tmem, tmem_o = tmem + 128, tmem_p = tmem + 192;
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
 
     if (tid == 0) {
@@ -210,7 +210,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
                 pv[i] = e;
                 rs4[i & 3] += e;
             }
-            store_p_chunk(sP, r, c * 32, pv);
+            uint32_t pk[16];                         // this row's 32 probabilities as 16 bf16 pairs -> TMEM
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(pv[2 * i], pv[2 * i + 1]);
+            tmem_st_32x16(tmem_p + lane_base + c * 16, pk);
         }
         const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         TRACE_AT(5);
@@ -220,18 +223,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
         for (int i = 0; i < 64; ++i) o_acc[i] *= alpha;
 
         TRACE_AT(6);
-        fence_proxy_async_smem();                    // P (generic proxy) -> visible to the tensor core
+        tmem_st_wait();                              // P is in tensor memory
         tc_fence_before();
         __syncthreads();
         TRACE_AT(7);
         if (warp == 0) {
             tc_fence_after();
-            const uint32_t p_lo = umma_desc_lo(smem_u32(sP), 16);
             const uint32_t v_lo = umma_desc_lo(smem_u32(sV + buf * TILE_BYTES), TILE_BYTES);
             if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k)    // A: two K-major 64-column sub-tiles; B: V MN-major, 2048 B per K slice
-                    umma_bf16_ss_lo(tmem_o, p_lo + (k >> 2) * (TILE_BYTES >> 4) + 2 * (k & 3), v_lo + 128 * k, idesc_o, k > 0);
+                for (int k = 0; k < BK / 16; ++k)    // A: P from TMEM, 8 packed columns per K slice; B: V MN-major, 2048 B per K slice
+                    umma_bf16_ts_lo(tmem_o, tmem_p + 8 * k, v_lo + 128 * k, idesc_o, k > 0);
                 umma_commit(bar_o);
             }
             __syncwarp();
@@ -1383,7 +1385,7 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     p.scale = 1.0f / sqrtf(64.0f);
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.out = (__nv_bfloat16*)out; p.lse = lse;
-    const int smem = 7 * TILE_BYTES + 64;
+    const int smem = 5 * TILE_BYTES + 64;                 // Q, 2 x K, 2 x V (P lives in tensor memory)
     const int smem_ws = (2 + 2 * WS_NST + 4) * TILE_BYTES + 256;
     static bool configured = false;
     static int use_ws = 0;                 // the simple 2-CTA/SM kernel measured faster (profiles/README.md); TDL_ATTN_WS=1 selects ping-pong
