@@ -976,7 +976,7 @@ __device__ __forceinline__ void named_bar_math(int id) {          // barrier amo
 template <int MODE>
 __global__ void __launch_bounds__(BWD_WS_THREADS, 1)
 attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
-                   const __grid_constant__ CUtensorMap tmap_dqkv, const AttnParams p) {
+                   const __grid_constant__ CUtensorMap tmap_dqkv, const __grid_constant__ CUtensorMap tmap_o, const AttnParams p) {
     constexpr int NSTR = BWD_WS_NSTR, NFIX = BWD_WS_NFIX;
     constexpr int CW = 128 / BWD_WS_NCG;           // S / dP columns per math thread
     TRACE_DECL;
@@ -996,7 +996,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     uint64_t* p_full = bars + 18;                  // [2]
     uint64_t* acc_done = bars + 20;                // [2]
     uint64_t* acc_free = bars + 22;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
+    uint64_t* o_full = bars + 23;                  // MODE 1: the tile's O rows landed (for delta = rowsum(dO * O))
+    uint64_t* o_free = bars + 24;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nblk = p.T / 128;
@@ -1035,6 +1037,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
         for (int s = 0; s < NSTR; ++s) { mbar_init(&str_full[s], 1); mbar_init(&str_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], BWD_WS_MATH / 32); mbar_init(&acc_done[s], 1); }
         mbar_init(dp_full, 1); mbar_init(dp_free, BWD_WS_MATH / 32); mbar_init(acc_free, BWD_WS_MATH / 32);
+        mbar_init(o_full, 1); mbar_init(o_free, BWD_WS_MATH / 32);
         fence_barrier_init();
     }
     if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -1061,6 +1064,10 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                     } else {
                         tma_load_2d(f0, &tmap_qkv, &fix_full[fb], h * D, row0 + ob * 128);                        // Q
                         tma_load_2d(f0 + TILE_BYTES, &tmap_do, &fix_full[fb], h * D, row0 + ob * 128);            // dO
+                        // O rows of the tile -> the staging tile MODE 1 does not use for output (single buffer)
+                        if (c.k >= 1) mbar_wait(o_free, (c.k - 1) & 1);
+                        mbar_arrive_expect_tx(o_full, TILE_BYTES);
+                        tma_load_2d(sOut + TILE_BYTES, &tmap_o, o_full, h * D, row0 + ob * 128);
                     }
                 }
                 const int st = c.j % NSTR;
@@ -1229,6 +1236,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                     if (lane < AW) atomicAdd(dbias + cg * AW + lane, v[0]);
                 }
             };
+            // (measured: routing these sums through shared-memory atomics + a bulk reduction costs more, +47 vs +33 us)
             if (MODE == 0) {
                 stage_acc(tmem_a1, sOut, p.scale, db ? db + p.C : nullptr);                    // dK
                 stage_acc(tmem_a0, sOut + TILE_BYTES, 1.0f, db ? db + 2 * p.C : nullptr);      // dV
@@ -1265,7 +1273,35 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             if (MODE == 1 && c.it == 0) {                      // this thread's query row is fixed for the whole tile
                 const long long idx = (long long)(b * p.H + h) * p.T + ob * 128 + r;
                 lse2 = p.lse[idx] * 1.4426950408889634f;
-                dlt = p.delta[idx];
+                // delta = rowsum(dO * O) from the two tiles in shared memory (this used to be a separate kernel and a
+                // separate pass over O and dO); written out for the dK/dV kernel, which runs after this one
+                const int fb = c.k % NFIX;
+                mbar_wait(&fix_full[fb], (c.k / NFIX) & 1);
+                mbar_wait(o_full, c.k & 1);
+                const uint8_t* tdo = sFix + fb * 2 * TILE_BYTES + TILE_BYTES;
+                const uint8_t* to = sOut + TILE_BYTES;
+                float part = 0.f;
+#pragma unroll
+                for (int q = 0; q < 8 / BWD_WS_NCG; ++q) {
+                    const uint32_t piece = cg * (8 / BWD_WS_NCG) + q;
+                    const uint4 ua = *reinterpret_cast<const uint4*>(to + swz(r, piece));
+                    const uint4 ug = *reinterpret_cast<const uint4*>(tdo + swz(r, piece));
+                    const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wg[4] = {ug.x, ug.y, ug.z, ug.w};
+#pragma unroll
+                    for (int j2 = 0; j2 < 4; ++j2) {
+                        const float2 fa = unpack_bf16x2(wa[j2]), fg = unpack_bf16x2(wg[j2]);
+                        part = fmaf(fa.x, fg.x, part);
+                        part = fmaf(fa.y, fg.y, part);
+                    }
+                }
+                sStat[cg * 128 + r] = part;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(o_free);
+                named_bar_math(1);
+                dlt = 0.f;
+#pragma unroll
+                for (int q = 0; q < BWD_WS_NCG; ++q) dlt += sStat[q * 128 + r];
+                if (cg == 0) const_cast<float*>(p.delta)[idx] = dlt;
             }
             const int bb = c.j & 1;
             const bool diag = MODE == 0 ? (c.it == 0) : (c.it == c.n - 1);
@@ -1427,9 +1463,6 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
     CUtensorMap tq, tdo;
     if (int rc = tdl_make_tmap_2d_bf16(&tq, qkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
     if (int rc = tdl_make_tmap_2d_bf16(&tdo, d_out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
-    const long long items = B * T * H * 8;
-    attn_delta_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)d_out, delta,
-                                                                    (int)B, (int)T, (int)H);
     AttnParams p{};
     p.B = (int)B; p.T = (int)T; p.H = (int)H; p.C = C;
     p.scale = 1.0f / sqrtf(64.0f);
@@ -1448,6 +1481,11 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
         configured = true;
     }
     const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
+    if (!use_ws) {                               // the pipelined dQ kernel computes delta itself
+        const long long items = B * T * H * 8;
+        attn_delta_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)d_out,
+                                                                        delta, (int)B, (int)T, (int)H);
+    }
     if (use_ws) {
         const long long tiles = (T / 128) * B * H;
         long long ch = (96 * 1024) / T;                      // 4 tensors x T x 64 x 2 B per pair: keep a chunk under ~48 MB
@@ -1460,8 +1498,11 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
         const unsigned ctas = (unsigned)(tiles < tdl_num_sms() ? tiles : tdl_num_sms());      // persistent: one CTA per SM
         CUtensorMap tdq;
         if (int rc = tdl_make_tmap_2d_bf16(&tdq, dqkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
-        attn_bwd_ws_kernel<0><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, p);
-        attn_bwd_ws_kernel<1><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, p);
+        CUtensorMap to;
+        if (int rc = tdl_make_tmap_2d_bf16(&to, out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
+        // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
+        attn_bwd_ws_kernel<1><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, to, p);
+        attn_bwd_ws_kernel<0><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, to, p);
     } else {
         attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
         attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);

@@ -332,7 +332,7 @@ class GPT2Engine:
         L = self.L
         P = 2                                     # radix-select passes for bf16
         n = 1 + L * 7 + 2 + 1                     # embedding, per-layer fwd (2 LN, 4 GEMM, attn), lnf+head, xent
-        n += 2 + 1 + L * (4 + 4 + 2 + 3) + 1      # head dgrad/wgrad, lnf bwd, per layer: 4 wgrad, 4 dgrad, 2 LN, 3 attn (bias grads fused), emb
+        n += 2 + 1 + L * (4 + 4 + 2 + 2) + 1      # head dgrad/wgrad, lnf bwd, per layer: 4 wgrad, 4 dgrad, 2 LN, 2 attn (bias grads and delta fused), emb
         n += 1 + 2                                # pack+norm, adam tick, adamw
         if self.security:
             n += 2 + 2 * P + 1 + 5                # stats (moments, final, P x (hist, select), finalize) + exchange/coeff/reduce/exchange/finalize
