@@ -129,6 +129,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     // S [0,128) fp32 | O block product [128,192) | P [192,256) as bf16 pairs: the A operand of P V straight from TMEM
     const uint32_t tmem_s = tmem, tmem_o = tmem + 128, tmem_p = tmem + 192;
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    pdl_enter();                                     // global memory is touched only below
 
     if (tid == 0) {
         mbar_arrive_expect_tx(bar_q, TILE_BYTES);
@@ -1046,6 +1047,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_dp = tmem + 256, tmem_a0 = tmem + 384, tmem_a1 = tmem + 448;
+    pdl_enter();                                     // global memory is touched only below
 
     if (warp == BWD_WS_MATH / 32 + 1) {
         // ======================================= TMA producer ====================================
@@ -1448,7 +1450,8 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
         TDL_LAUNCH_CHECK();
         return 0;
     }
-    attn_fwd_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+    TDL_CHECK(tdl_launch_pdl(attn_fwd_kernel, dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), dim3(128), smem,
+                             reinterpret_cast<cudaStream_t>(stream), tm, p));
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -1501,8 +1504,8 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
         CUtensorMap to;
         if (int rc = tdl_make_tmap_2d_bf16(&to, out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
         // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
-        attn_bwd_ws_kernel<1><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, to, p);
-        attn_bwd_ws_kernel<0><<<ctas, BWD_WS_THREADS, smem_ws, s>>>(tq, tdo, tdq, to, p);
+        TDL_CHECK(tdl_launch_pdl(attn_bwd_ws_kernel<1>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
+        TDL_CHECK(tdl_launch_pdl(attn_bwd_ws_kernel<0>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
     } else {
         attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
         attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 // ---------------------------------------------------------------------------------------------
 // error plumbing (C ABI: every entry point returns 0 on success; tdl_last_error() explains)
@@ -215,6 +216,31 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
         :: "r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Programmatic dependent launch.  Kernels call pdl_enter() before their first access to global memory that another
+// kernel produces or still reads; hosts launch them with tdl_launch_pdl().  What sits above pdl_enter() in a kernel
+// (barrier init, TMEM allocation, index setup) then overlaps with the tail of the previous kernel in the stream instead
+// of waiting behind its last CTA, also inside a captured CUDA graph.  TDL_PDL=0 gives plain stream-ordered launches.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+static inline bool tdl_pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("TDL_PDL"); v = e ? atoi(e) : 1; }
+    return v != 0;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t tdl_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                         Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = tdl_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // One lane of a converged warp (elect.sync): the compiler then knows the guarded region runs in a single thread and
 // emits tcgen05.mma / commit without the per-instruction election loop it wraps around them under `if (lane == 0)`.
 __device__ __forceinline__ bool elect_one() {

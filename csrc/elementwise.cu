@@ -32,6 +32,7 @@ template <int ITERS>
 __global__ void __launch_bounds__(128) layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x,
         const float* __restrict__ w, const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
         float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int C, float eps) {
+    pdl_enter();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * 4 + warp;
     if (row >= M) return;
@@ -177,6 +178,7 @@ __global__ void __launch_bounds__(256, IT == 1 ? 3 : 2) layernorm_bwd4_kernel(co
     __shared__ float part[2][2][4][2];        // [row group][parity][warp][s1, s2]
     for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh[i] = 0.f;
     __syncthreads();
+    pdl_enter();
     const int grp = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5, lane = threadIdx.x & 31;
     float aw[IT][8], ab[IT][8], ao[IT][8], ww[IT][8];
 #pragma unroll
@@ -597,8 +599,8 @@ inline int grid_for(long long n, int per_block) {
 extern "C" int tdl_layernorm_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                                  int64_t M, int64_t C, float eps, void* stream) {
     TDL_REQUIRE(C % 8 == 0 && C <= 256 * LN_MAX_ITERS, "LayerNorm width %lld unsupported (need %%8==0, <= %d)", (long long)C, 256 * LN_MAX_ITERS);
-#define LN_FWD(I) layernorm_fwd_kernel<I><<<(unsigned)((M + 3) / 4), 128, 0, STREAM(stream)>>>( \
-        (const __nv_bfloat16*)x, w, b, (__nv_bfloat16*)y, mean, rstd, (int)M, (int)C, eps)
+#define LN_FWD(I) TDL_CHECK(tdl_launch_pdl(layernorm_fwd_kernel<I>, dim3((unsigned)((M + 3) / 4)), dim3(128), 0, STREAM(stream), \
+        (const __nv_bfloat16*)x, w, b, (__nv_bfloat16*)y, mean, rstd, (int)M, (int)C, eps))
     switch ((C + 255) / 256) {
         case 1: LN_FWD(1); break; case 2: LN_FWD(2); break; case 3: LN_FWD(3); break; case 4: LN_FWD(4); break;
         case 5: LN_FWD(5); break; case 6: LN_FWD(6); break; case 7: LN_FWD(7); break; default: LN_FWD(8); break;
@@ -621,9 +623,9 @@ extern "C" int tdl_layernorm_bwd_colsum(const void* dy, const void* x, const flo
     if (variant == 4 && C % 4 == 0 && aligned) {
         const int grid = (int)std::min<long long>((M + 1) / 2, (long long)tdl_num_sms() * (C <= 1024 ? 3 : 2));   // one resident wave
         const size_t smem = 3 * C * sizeof(float);
-#define LN_BWD4(I) layernorm_bwd4_kernel<I><<<grid, 256, smem, STREAM(stream)>>>( \
+#define LN_BWD4(I) TDL_CHECK(tdl_launch_pdl(layernorm_bwd4_kernel<I>, dim3(grid), dim3(256), smem, STREAM(stream), \
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, w, mean, rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, \
-        dw, db, dxsum, (int)M, (int)C)
+        dw, db, dxsum, (int)M, (int)C))
         if (C <= 1024) LN_BWD4(1); else LN_BWD4(2);
 #undef LN_BWD4
         TDL_LAUNCH_CHECK();

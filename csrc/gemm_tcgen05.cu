@@ -467,6 +467,10 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
     const int m2_offset = p.m_block_offset >> 1;
 
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, cluster handshake) may run while
+    // the previous kernel in the stream is still draining on other SMs; global memory is touched only below this point.
+    pdl_enter();
+
     if (warp == 0) {
         // ================================ TMA producer (both CTAs) ================================
         if (lane == 0) {
@@ -839,7 +843,8 @@ static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const Ep
     const int work = m_blocks2 * p.n_blocks * p.split_k;
     const int max_clusters = tdl_num_sms() / 2;
     const int clusters = work < max_clusters ? work : max_clusters;
-    gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM><<<2 * clusters, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, em, p);
+    TDL_CHECK(tdl_launch_pdl(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM>, dim3(2 * clusters), dim3(NUM_THREADS),
+                             C::SMEM_BYTES, stream, ta, tb, em, p));
     TDL_LAUNCH_CHECK();
     return 0;
 }
