@@ -392,22 +392,46 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p32, __n
 // ------------------------------------------------------------------------------------ cross entropy
 // one CTA per row; logits bf16 [M, Vp] overwritten with dlogits; only columns < V are real.
 // Pass 1: online (max, sum); pass 2 re-reads the row (mostly from L2) and writes the gradient.
+// Both passes move XENT_U vectors per thread per trip so that enough loads are in flight (one 16-byte load per
+// thread per trip left the kernel latency-bound at ~0.6 of the HBM rate).
+constexpr int XENT_U = 4;
+__device__ __forceinline__ uint4 xent_mask_tail(uint4 raw, int nv) {        // columns >= V of a vector become -inf
+    uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (2 * q >= nv) w[q] = 0xff80ff80u;
+        else if (2 * q + 1 >= nv) w[q] = (w[q] & 0xffffu) | 0xff800000u;
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
 __global__ void __launch_bounds__(1024) xent_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
         float* __restrict__ row_loss, float* __restrict__ loss_sum, int V, int Vp, float grad_scale) {
     __shared__ float shm[32], shs[32];
     const int row = blockIdx.x;
     __nv_bfloat16* lr = logits + (long long)row * Vp;
     const int nvec = Vp / 8;
+    const uint4 ninf = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);
     float mx = -INFINITY, sum = 0.f;
-    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        float f[8];
-        bf16x8_to_f32(ld_nc_v4(lr + i * 8), f);
-        float lm = -INFINITY;
+    for (int base = threadIdx.x; base < nvec; base += blockDim.x * XENT_U) {
+        uint4 raw[XENT_U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) if (i * 8 + j < V) lm = fmaxf(lm, f[j]);
-        if (lm > mx) { sum *= __expf(mx - lm); mx = lm; }
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * blockDim.x;
+            raw[u] = i < nvec ? ld_nc_v4(lr + i * 8) : ninf;
+        }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) if (i * 8 + j < V) sum += __expf(f[j] - mx);
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * blockDim.x;
+            if (i < nvec && i * 8 + 8 > V) raw[u] = xent_mask_tail(raw[u], V - i * 8);
+            float f[8];
+            bf16x8_to_f32(raw[u], f);
+            float lm = fmaxf(fmaxf(fmaxf(f[0], f[1]), fmaxf(f[2], f[3])), fmaxf(fmaxf(f[4], f[5]), fmaxf(f[6], f[7])));
+            if (lm > mx) { sum *= __expf(mx - lm); mx = lm; }
+            if (mx != -INFINITY) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sum += __expf(f[j] - mx);      // exp(-inf) = 0 for masked columns
+            }
+        }
     }
     // block combine of (max, sum)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -419,25 +443,139 @@ __global__ void __launch_bounds__(1024) xent_kernel(__nv_bfloat16* __restrict__ 
     for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bm = fmaxf(bm, shm[w2]);
     for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) bs += shm[w2] == -INFINITY ? 0.f : shs[w2] * __expf(shm[w2] - bm);
     const long long tgt = targets[row];
-    const float inv = 1.0f / bs;
+    const float inv = grad_scale / bs;
     if (threadIdx.x == 0) {
         const float loss = logf(bs) + bm - __bfloat162float(lr[tgt]);
         if (row_loss != nullptr) row_loss[row] = loss;
         if (loss_sum != nullptr) atomicAdd(loss_sum, loss);
     }
     __syncthreads();       // the target logit is read before anyone overwrites it
-    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        float f[8];
-        bf16x8_to_f32(*reinterpret_cast<const uint4*>(lr + i * 8), f);
+    const int tvec = (int)(tgt >> 3), tj = (int)(tgt & 7);
+    for (int base = threadIdx.x; base < nvec; base += blockDim.x * XENT_U) {
+        uint4 raw[XENT_U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = i * 8 + j;
-            float p = c < V ? __expf(f[j] - bm) * inv : 0.f;
-            if (c == tgt) p -= 1.f;
-            f[j] = p * grad_scale;
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * blockDim.x;
+            raw[u] = i < nvec ? *reinterpret_cast<const uint4*>(lr + i * 8) : ninf;
+        }
+#pragma unroll
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * blockDim.x;
+            if (i < nvec) {
+                if (i * 8 + 8 > V) raw[u] = xent_mask_tail(raw[u], V - i * 8);
+                float f[8];
+                bf16x8_to_f32(raw[u], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - bm) * inv;     // padding: exp(-inf) = 0
+                if (i == tvec) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (j == tj) f[j] -= grad_scale;
+                }
+                *reinterpret_cast<uint4*>(lr + i * 8) = f32_to_bf16x8(f);
+            }
+        }
+    }
+}
+
+// Cluster variant (default when the row fits): one row per cluster of 4 CTAs.  Each CTA keeps its quarter of the bf16 row
+// in shared memory (25 KB for the GPT-2 vocabulary, so 6-8 CTAs stay resident per SM), the four partial (max, sum) pairs
+// are exchanged through distributed shared memory, and the gradient is produced from the cached quarter: the logits are
+// read from HBM once and written once.  (The streaming kernel's second pass was measured to miss L2: with enough rows in
+// flight to hide latency the working set is ~100 MB.)
+constexpr int XENT_CL = 4;
+__device__ __forceinline__ uint32_t xent_cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void xent_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float xent_ld_peer(const float* local_smem, uint32_t peer) {   // the same variable in CTA `peer` of the cluster
+    uint32_t a;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(smem_u32(local_smem)), "r"(peer));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+    return v;
+}
+__global__ void __cluster_dims__(XENT_CL, 1, 1) __launch_bounds__(256)
+xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets, float* __restrict__ row_loss,
+                    float* __restrict__ loss_sum, int V, int Vp, int per, float grad_scale) {
+    extern __shared__ uint4 srow[];            // this CTA's `per` vectors of the row
+    __shared__ float shm[8], shs[8];
+    __shared__ float stat[2];                  // this CTA's (max, sum), read by the peers
+    const uint32_t rank = xent_cluster_rank();
+    const int row = blockIdx.x / XENT_CL;
+    __nv_bfloat16* lr = logits + (long long)row * Vp;
+    const int nvec = Vp / 8;
+    const int v0 = (int)rank * per, v1 = min(nvec, v0 + per);
+    float mx = -INFINITY, sum = 0.f;
+    for (int base = v0 + threadIdx.x; base < v1; base += 256 * XENT_U) {
+        uint4 raw[XENT_U];
+#pragma unroll
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * 256;
+            if (i < v1) raw[u] = ld_nc_v4(lr + i * 8);
+        }
+#pragma unroll
+        for (int u = 0; u < XENT_U; ++u) {
+            const int i = base + u * 256;
+            if (i < v1) {
+                if (i * 8 + 8 > V) raw[u] = xent_mask_tail(raw[u], V - i * 8);
+                srow[i - v0] = raw[u];
+                float f[8];
+                bf16x8_to_f32(raw[u], f);
+                const float lm = fmaxf(fmaxf(fmaxf(f[0], f[1]), fmaxf(f[2], f[3])), fmaxf(fmaxf(f[4], f[5]), fmaxf(f[6], f[7])));
+                if (lm > mx) { sum *= __expf(mx - lm); mx = lm; }
+                if (mx != -INFINITY) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sum += __expf(f[j] - mx);
+                }
+            }
+        }
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float wm = warp_max(mx);
+    sum = warp_sum(mx == -INFINITY ? 0.f : sum * __expf(mx - wm));
+    if (lane == 0) { shm[warp] = wm; shs[warp] = sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = -INFINITY, s2 = 0.f;
+        for (int w2 = 0; w2 < 8; ++w2) m = fmaxf(m, shm[w2]);
+        for (int w2 = 0; w2 < 8; ++w2) s2 += shm[w2] == -INFINITY ? 0.f : shs[w2] * __expf(shm[w2] - m);
+        stat[0] = m; stat[1] = s2;
+    }
+    xent_cluster_sync();                       // all four (max, sum) pairs are published (also orders this CTA's srow writes)
+    float pm[XENT_CL], ps[XENT_CL];
+#pragma unroll
+    for (int q = 0; q < XENT_CL; ++q) { pm[q] = xent_ld_peer(&stat[0], q); ps[q] = xent_ld_peer(&stat[1], q); }
+    float bm = -INFINITY, bs = 0.f;
+#pragma unroll
+    for (int q = 0; q < XENT_CL; ++q) bm = fmaxf(bm, pm[q]);
+#pragma unroll
+    for (int q = 0; q < XENT_CL; ++q) bs += pm[q] == -INFINITY ? 0.f : ps[q] * __expf(pm[q] - bm);
+    const long long tgt = targets[row];
+    const int tvec = (int)(tgt >> 3), tj = (int)(tgt & 7);
+    const float inv = grad_scale / bs;
+    if (threadIdx.x == 0 && tvec >= v0 && tvec < v1) {         // the CTA that holds the target logit reports the loss
+        const float lt = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(srow)[tgt - (long long)v0 * 8]);
+        const float loss = logf(bs) + bm - lt;
+        if (row_loss != nullptr) row_loss[row] = loss;
+        if (loss_sum != nullptr) atomicAdd(loss_sum, loss);
+    }
+    for (int i = v0 + threadIdx.x; i < v1; i += 256) {
+        float f[8];
+        bf16x8_to_f32(srow[i - v0], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - bm) * inv;          // padding: exp(-inf) = 0
+        if (i == tvec) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (j == tj) f[j] -= grad_scale;
         }
         *reinterpret_cast<uint4*>(lr + i * 8) = f32_to_bf16x8(f);
     }
+    xent_cluster_sync();                       // nobody exits while a peer may still read its stat[]
 }
 
 // ------------------------------------------------------------------------------------ K1 pack + norm
@@ -699,15 +837,30 @@ extern "C" int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype
 
 static int xent_threads() {          // TDL_XENT_THREADS=1024: fewer rows in flight (more of the re-read hits L2)
     static int v = -1;
-    if (v < 0) { const char* e = getenv("TDL_XENT_THREADS"); v = e ? atoi(e) : 512; if (v != 256 && v != 1024) v = 512; }
+    if (v < 0) { const char* e = getenv("TDL_XENT_THREADS"); v = e ? atoi(e) : 256; if (v != 512 && v != 1024) v = 256; }
     return v;
 }
 
 extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row_loss, float* loss_sum, int64_t M,
                                 int64_t V, int64_t Vp, float grad_scale, void* stream) {
     TDL_REQUIRE(Vp % 8 == 0 && V <= Vp, "padded vocab must be a multiple of 8 and >= vocab");
-    xent_kernel<<<(unsigned)M, xent_threads(), 0, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets, row_loss,
-                                                                    loss_sum, (int)V, (int)Vp, grad_scale);
+    static int variant = -1;                   // TDL_XENT=0: streaming kernel (two reads of the logits)
+    if (variant < 0) { const char* e = getenv("TDL_XENT"); variant = e ? atoi(e) : 1; }
+    const int nvec = (int)(Vp / 8);
+    const int per = (nvec + XENT_CL - 1) / XENT_CL;
+    const size_t smem = (size_t)per * 16;
+    if (variant == 1 && smem <= 64 * 1024 && M * XENT_CL < (1ll << 31)) {
+        static bool configured = false;
+        if (!configured) {
+            TDL_CHECK(cudaFuncSetAttribute(xent_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            configured = true;
+        }
+        xent_cluster_kernel<<<(unsigned)(M * XENT_CL), 256, smem, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets,
+                                                                                  row_loss, loss_sum, (int)V, (int)Vp, per, grad_scale);
+    } else {
+        xent_kernel<<<(unsigned)M, xent_threads(), 0, STREAM(stream)>>>((__nv_bfloat16*)logits, (const long long*)targets, row_loss,
+                                                                        loss_sum, (int)V, (int)Vp, grad_scale);
+    }
     TDL_LAUNCH_CHECK();
     return 0;
 }
