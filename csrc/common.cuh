@@ -147,11 +147,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Spin with a watchdog: a pipeline bug becomes a trapped kernel (an error the host sees) instead of
 // a hung GPU.  ~4e9 cycles is seconds, far beyond any legitimate wait.
+// try_wait with a suspend-time hint: the warp is parked by the hardware until the phase completes or the hint
+// expires, instead of burning issue slots that the math warps on the same scheduler need (in the attention backward
+// a quarter of all executed instructions were barrier polls of the TMA / MMA-issue warps).
+__device__ __forceinline__ bool mbar_try_wait_parked(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u) : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity)) {
+    while (!mbar_try_wait_parked(bar, parity)) {
         if ((++spins & 0x3FFu) == 0 && clock64() - t0 > 4000000000ll) {
             printf("tdl: mbarrier wait timed out (block %d,%d,%d thread %d parity %u)\n", blockIdx.x, blockIdx.y, blockIdx.z,
                    threadIdx.x, parity);
