@@ -90,11 +90,25 @@ __global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs
 #pragma unroll
     for (int i = 0; i < W; ++i) ddot[i] = 0.0;
     int run = 0;
+    // U vectors per thread per trip: W * U peer loads are in flight before anything is consumed.  Loaded NVLink latency is
+    // tens of microseconds (a plain peer copy needs ~100 KB in flight per SM to reach 730 GB/s), so one vector per trip
+    // leaves the links mostly idle.
+    constexpr int U = W <= 2 ? 8 : (W <= 4 ? 4 : 2);
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long v = vec_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; v < vec_end; v += stride) {
-        uint4 raw[W];
+    for (long long v0 = vec_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < vec_end; v0 += stride * U) {
+        uint4 rawu[U][W];
 #pragma unroll
-        for (int i = 0; i < W; ++i) raw[i] = ld_peer_v4(reinterpret_cast<const uint4*>(in.p[i]) + v);   // all loads in flight first
+        for (int u = 0; u < U; ++u) {
+            const long long v = v0 + u * stride;
+#pragma unroll
+            for (int i = 0; i < W; ++i)
+                rawu[u][i] = v < vec_end ? ld_peer_v4(reinterpret_cast<const uint4*>(in.p[i]) + v) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+        const long long v = v0 + u * stride;
+        if (v < vec_end) {
+        uint4 (&raw)[W] = rawu[u];
         float g[W][VN];
 #pragma unroll
         for (int i = 0; i < W; ++i) unpack_vec<T>(raw[i], g[i]);
@@ -118,6 +132,8 @@ __global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs
 #pragma unroll
             for (int i = 0; i < W; ++i) { ddot[i] += dot[i]; dot[i] = 0.f; }
             dmed2 += med2; med2 = 0.f; run = 0;
+        }
+        }
         }
     }
 #pragma unroll
@@ -288,7 +304,9 @@ extern "C" int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int
     const long long nvec = vec_end - vec_begin;
     if (nvec <= 0) return 0;
     long long blocks = (nvec + 255) / 256;
-    const long long cap = (long long)tdl_num_sms() * 4;
+    static int per_sm = -1;                      // TDL_TR_BLOCKS: resident blocks per SM for the reduction
+    if (per_sm < 0) { const char* e = getenv("TDL_TR_BLOCKS"); per_sm = e ? atoi(e) : 4; if (per_sm < 1) per_sm = 1; }
+    const long long cap = (long long)tdl_num_sms() * per_sm;
     const int grid = (int)(blocks > cap ? cap : blocks);
 #define LAUNCH(T, WW) trust_reduce_kernel<T, WW><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial)
 #define BY_W(T) switch (W) { case 1: LAUNCH(T, 1); break; case 2: LAUNCH(T, 2); break; case 3: LAUNCH(T, 3); break; \
