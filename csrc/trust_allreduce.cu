@@ -182,8 +182,16 @@ __global__ void exchange_kernel(PeerPtrs pads, int rank, int W, int which, const
         asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(&peer->flags[which][rank]), "r"(epoch) : "memory");
         const ExchPad* mine = reinterpret_cast<const ExchPad*>(pads.p[rank]);
         unsigned int seen;
+        // A peer that never raises its flag (crashed or wedged process) must not hang this GPU for good: after ~2 minutes of
+        // cycles the kernel traps with the missing rank named, which the host sees as a launch failure (liveness signal).
+        const long long t0 = clock64();
+        unsigned int spins = 0;
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(&mine->flags[which][t]) : "memory");
+            if ((int)(seen - epoch) < 0 && (++spins & 0xFFFu) == 0 && clock64() - t0 > 200000000000ll) {
+                printf("tdl: exchange %d: rank %d never reached epoch %u (seen %u) -- peer lost?\n", which, t, epoch, seen);
+                __trap();
+            }
         } while ((int)(seen - epoch) < 0);
     }
     __syncthreads();
