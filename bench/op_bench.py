@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Device-timed micro-benchmarks of the non-GEMM hot ops at GPT-2-medium step shapes (B=32, T=1024), L2 flushed
 between iterations.  One line per op: time, bytes moved (algorithmic), achieved GB/s and fraction of the measured HBM
-copy bandwidth in MEASURED_PEAKS.json.
+copy bandwidth in MEASURED_PEAKS.json.  The flush leaves up to one L2 (126 MB) of dirty lines that are written back
+while the timed kernel runs, so kernels that move only ~100-300 MB (LayerNorm, bias gradients) read low here; use the
+numbers to compare variants of one op, and the `ncu` launch lists for absolute times of the small kernels.
 
   python bench/op_bench.py [--ops xent,ln_bwd,ln_fwd,bias_grad,dproj,attn] [--iters 10]
 """
