@@ -102,6 +102,8 @@ def main() -> int:
         report("d_proj GEMM (dGELU)", us0, (M * C + 2 * M * 4 * C) * 2, f"{fl / us0 / 1e6:.0f} TFLOP/s")
         us1 = timed(lambda: K.linear_dgrad(dyp, wp, out, epilogue=K.EPI_DGELU, aux_in=pre, colsum=cs), args.iters, flush)
         report("d_proj GEMM (dGELU+colsum)", us1, (M * C + 2 * M * 4 * C) * 2, f"{fl / us1 / 1e6:.0f} TFLOP/s; fused bias grad costs {us1 - us0:+.1f} us")
+        usm = timed(lambda: K.linear_dgrad(dyp, wp, out, epilogue=K.EPI_MUL, aux_in=pre, colsum=cs), args.iters, flush)
+        report("d_proj GEMM (*saved gelu'+colsum)", usm, (M * C + 2 * M * 4 * C) * 2, f"{fl / usm / 1e6:.0f} TFLOP/s")
         del dyp, wp, pre, out
         xin = torch.randn(M, C, device=dev, dtype=bf)
         wfc = torch.randn(4 * C, C, device=dev, dtype=bf) * 0.02
@@ -109,6 +111,8 @@ def main() -> int:
         pre = torch.empty(M, 4 * C, device=dev, dtype=bf); act = torch.empty(M, 4 * C, device=dev, dtype=bf)
         us2 = timed(lambda: K.linear_fwd(xin, wfc, act, bias=bfc, epilogue=K.EPI_GELU, aux_out=pre), args.iters, flush)
         report("f_fc GEMM (bias+GELU, 2 outputs)", us2, (M * C + 2 * M * 4 * C) * 2, f"{fl / us2 / 1e6:.0f} TFLOP/s")
+        us2b = timed(lambda: K.linear_fwd(xin, wfc, act, bias=bfc, epilogue=K.EPI_GELU_DG, aux_out=pre), args.iters, flush)
+        report("f_fc GEMM (bias+GELU, saves gelu')", us2b, (M * C + 2 * M * 4 * C) * 2, f"{fl / us2b / 1e6:.0f} TFLOP/s")
         res = torch.randn(M, C, device=dev, dtype=bf); wo = torch.randn(C, C, device=dev, dtype=bf) * 0.02
         outo = torch.empty(M, C, device=dev, dtype=bf); bo = torch.zeros(C, device=dev)
         us3 = timed(lambda: K.linear_fwd(xin, wo, outo, bias=bo, epilogue=K.EPI_RESIDUAL, aux_in=res), args.iters, flush)

@@ -118,6 +118,21 @@ __device__ __forceinline__ float gelu_tanh_grad_f(float x) {
     return fmaf(a, fmaf(-a, w, w), a);
 }
 
+// both at once (one tanh): the forward epilogue can store gelu'(x) instead of x, which turns the backward epilogue into a
+// plain multiply
+__device__ __forceinline__ void gelu_tanh_both_f(float x, float& g, float& dg) {
+    const float k = 0.7978845608028654f, kc = 0.7978845608028654f * 0.044715f;
+    const float x2 = x * x;
+    const float u = x * fmaf(x2, kc, k);
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+    const float h = 0.5f * x;
+    g = fmaf(h, t, h);
+    const float w = x * fmaf(x2, 6.0f * kc, 2.0f * k);
+    const float a = fmaf(0.5f, t, 0.5f);
+    dg = fmaf(a, fmaf(-a, w, w), a);
+}
+
 // ---------------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------------

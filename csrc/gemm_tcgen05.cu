@@ -33,7 +33,9 @@ constexpr int BLOCK_K = 64;                 // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 320;            // TMA warp + MMA warp + 8 epilogue warps
 
-enum Epilogue { EPI_NONE = 0, EPI_GELU = 1, EPI_RESIDUAL = 2, EPI_DGELU = 3 };
+enum Epilogue { EPI_NONE = 0, EPI_GELU = 1, EPI_RESIDUAL = 2, EPI_DGELU = 3,
+                EPI_GELU_DG = 4,     // out = gelu(pre), aux_out = gelu'(pre)   (forward of a layer whose backward uses EPI_MUL)
+                EPI_MUL = 5 };       // out = acc * aux_in
 
 struct GemmParams {
     int M, N, K;
@@ -99,19 +101,22 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
                          :: "l"(out + q * 4), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3]) : "memory");
         return;
     }
-    if (p.epilogue == EPI_GELU) {
+    if (p.epilogue == EPI_GELU || p.epilogue == EPI_GELU_DG) {
         __nv_bfloat16* pre = reinterpret_cast<__nv_bfloat16*>(p.aux_out) + static_cast<long long>(row) * p.ld_aux + col0;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 4; ++q) {            // aux_out gets the pre-activation, or gelu' of it; v becomes gelu(pre)
+            float sv[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (p.epilogue == EPI_GELU_DG) { float g2; gelu_tanh_both_f(v[q * 8 + j], g2, sv[j]); v[q * 8 + j] = g2; }
+                else { sv[j] = v[q * 8 + j]; v[q * 8 + j] = gelu_tanh_f(v[q * 8 + j]); }
+            }
             uint4 u;
-            u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-            u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+            u.x = pack_bf16x2(sv[0], sv[1]); u.y = pack_bf16x2(sv[2], sv[3]);
+            u.z = pack_bf16x2(sv[4], sv[5]); u.w = pack_bf16x2(sv[6], sv[7]);
             *reinterpret_cast<uint4*>(pre + q * 8) = u;
         }
-        // activation is applied to the value that was stored (bf16-rounded), as backward will see it
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);      // from the fp32 pre-activation (its bf16 copy went to aux_out)
-    } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU) {
+    } else if (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU || p.epilogue == EPI_MUL) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const uint4 u = aux[q];
@@ -120,6 +125,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
             for (int e = 0; e < 4; ++e) {
                 if (p.epilogue == EPI_RESIDUAL) {
                     v[q * 8 + 2 * e] += f[e].x; v[q * 8 + 2 * e + 1] += f[e].y;
+                } else if (p.epilogue == EPI_MUL) {
+                    v[q * 8 + 2 * e] *= f[e].x; v[q * 8 + 2 * e + 1] *= f[e].y;
                 } else {
                     v[q * 8 + 2 * e] *= gelu_tanh_grad_f(f[e].x); v[q * 8 + 2 * e + 1] *= gelu_tanh_grad_f(f[e].y);
                 }
@@ -144,7 +151,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 }
 
 __device__ __forceinline__ void load_aux(const GemmParams& p, int row, int col0, bool ok, uint4 (&aux)[4]) {
-    if (ok && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU)) {
+    if (ok && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU || p.epilogue == EPI_MUL)) {
         const uint4* a = reinterpret_cast<const uint4*>(
             reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + static_cast<long long>(row) * p.ld_aux + col0);
 #pragma unroll
@@ -561,8 +568,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
         const int half = e >> 2;
         constexpr int NC = BLOCK_N / 64;
         const bool staged = !p.out_f32_atomic && !p.c_scatter;          // coalesced path: smem panels + TMA
-        const bool aux_in = AUX && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU);
-        const bool aux_out = AUX && p.epilogue == EPI_GELU;
+        const bool aux_in = AUX && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU || p.epilogue == EPI_MUL);
+        const bool aux_out = AUX && (p.epilogue == EPI_GELU || p.epilogue == EPI_GELU_DG);
         uint8_t* out_panel = staging + half * (AUX ? 2 : 1) * PANEL_BYTES;
         uint8_t* aux_panel = out_panel + PANEL_BYTES;                   // only dereferenced when AUX
         const bool group_leader = (e & 3) == 0 && lane == 0;            // one thread per column half issues TMA
@@ -677,6 +684,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                             for (int e2 = 0; e2 < 4; ++e2) {
                                 if (p.epilogue == EPI_RESIDUAL) {
                                     v[q * 8 + 2 * e2] += f[e2].x; v[q * 8 + 2 * e2 + 1] += f[e2].y;
+                                } else if (p.epilogue == EPI_MUL) {
+                                    v[q * 8 + 2 * e2] *= f[e2].x; v[q * 8 + 2 * e2 + 1] *= f[e2].y;
                                 } else {
                                     v[q * 8 + 2 * e2] *= gelu_tanh_grad_f(f[e2].x); v[q * 8 + 2 * e2 + 1] *= gelu_tanh_grad_f(f[e2].y);
                                 }
@@ -684,15 +693,29 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                         }
                     }
                     if (aux_out) {
+                        if (p.epilogue == EPI_GELU_DG) {
+                            // gelu and gelu' share the tanh; gelu' goes to the aux panel 8 values at a time
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            uint4 u;
-                            u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-                            u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-                            *reinterpret_cast<uint4*>(aux_panel + panel_off(lrow, cc * 4 + q)) = u;
+                            for (int q = 0; q < 4; ++q) {
+                                float dg[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { float g2; gelu_tanh_both_f(v[q * 8 + j], g2, dg[j]); v[q * 8 + j] = g2; }
+                                uint4 u;
+                                u.x = pack_bf16x2(dg[0], dg[1]); u.y = pack_bf16x2(dg[2], dg[3]);
+                                u.z = pack_bf16x2(dg[4], dg[5]); u.w = pack_bf16x2(dg[6], dg[7]);
+                                *reinterpret_cast<uint4*>(aux_panel + panel_off(lrow, cc * 4 + q)) = u;
+                            }
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                uint4 u;
+                                u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+                                u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                                *reinterpret_cast<uint4*>(aux_panel + panel_off(lrow, cc * 4 + q)) = u;
+                            }
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);  // from the fp32 pre-activation (its bf16 copy went to aux_out)
                         }
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_tanh_f(v[j]);      // from the fp32 pre-activation (its bf16 copy went to aux_out)
                     }
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
@@ -888,8 +911,9 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     p.C = Cout; p.ldc = ldc; p.bias = bias; p.aux_in = aux_in; p.aux_out = aux_out; p.ld_aux = ld_aux;
     p.colsum = nullptr;
     p.raster_group = 1;
-    TDL_REQUIRE(!(epilogue == EPI_GELU) || aux_out != nullptr, "GELU epilogue needs aux_out");
-    TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU) || aux_in != nullptr, "epilogue needs aux_in");
+    TDL_REQUIRE(epilogue >= EPI_NONE && epilogue <= EPI_MUL, "unknown epilogue %d", epilogue);
+    TDL_REQUIRE(!(epilogue == EPI_GELU || epilogue == EPI_GELU_DG) || aux_out != nullptr, "GELU epilogue needs aux_out");
+    TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU || epilogue == EPI_MUL) || aux_in != nullptr, "epilogue needs aux_in");
     p.a_shards = a_shards; p.a_shard_rows = (int)a_shard_rows; p.m_block_offset = m_block_offset % p.m_blocks;
     p.c_scatter = c_scatter; p.c_shard_rows = (int)c_shard_rows; p.c_src_slot = c_src_slot;
     if (a_shards > 1) {
@@ -932,7 +956,7 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         if (staged) {
             rc = tdl_make_tmap_2d_bf16(&em.c, Cout, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 128);
             if (rc) return rc;
-            const void* auxp = epilogue == EPI_GELU ? aux_out : aux_in;
+            const void* auxp = (epilogue == EPI_GELU || epilogue == EPI_GELU_DG) ? aux_out : aux_in;
             rc = tdl_make_tmap_2d_bf16(&em.aux, needs_aux ? auxp : Cout, (uint64_t)N, (uint64_t)M, (uint64_t)(needs_aux ? ld_aux : ldc), 64, 128);
             if (rc) return rc;
         } else {

@@ -37,7 +37,8 @@ int tdl_tensor_stats_noalloc(const void* x, int dtype, int64_t n, double* out12,
 
 /* ---- K6: tcgen05 GEMM with fused epilogues (cuBLAS calls under distributed_trainer.py:160-161) - */
 /* C[M,N] (+)= A * B^T.  a/b_mn_major: 0 = operand stored [rows, K] (K contiguous), 1 = stored [K, rows].
- * epilogue: 0 none, 1 GELU (pre-activation saved to aux_out), 2 +residual(aux_in), 3 *GELU'(aux_in).
+ * epilogue: 0 none, 1 GELU (pre-activation saved to aux_out), 2 +residual(aux_in), 3 *GELU'(aux_in),
+ *           4 GELU with GELU'(pre-activation) saved to aux_out, 5 *aux_in (the backward partner of 4).
  * out_f32_atomic: accumulate into an fp32 C with red.global.add (split_k > 1 allowed). */
 int tdl_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
                   int64_t ldc, int a_mn_major, int b_mn_major, const void* bias, int bias_f32, int epilogue,

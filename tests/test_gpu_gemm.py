@@ -157,3 +157,29 @@ def test_gemm_fused_column_sums(M, N, K, dgelu):
     assert torch.allclose(out.float(), ref, atol=5e-2, rtol=3e-2)
     want = out.float().sum(0) + 0.25
     assert torch.allclose(cs, want, atol=2e-3 * (M ** 0.5), rtol=1e-4), (cs - want).abs().max().item()
+
+
+@pytest.mark.parametrize("M", [256, 1024])
+def test_gemm_gelu_with_saved_derivative(M):
+    """Epilogue 4 stores gelu'(pre) next to gelu(pre); epilogue 5 multiplies by it: together = the GELU backward."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(5 + M)
+    N, K = 512, 128
+    x, w = _mk((M, K), dev), _mk((N, K), dev, 0.2)
+    bias = torch.randn(N, device=dev)
+    pre = x.float() @ w.float().t() + bias
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    dg = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, w, out, bias=bias, epilogue=Kk.EPI_GELU_DG, aux_out=dg)
+    assert torch.allclose(out.float(), R.gelu_tanh(pre), atol=3e-2, rtol=2e-2)
+    dg_ref = R.gelu_tanh_bwd(pre, torch.ones_like(pre))
+    assert torch.allclose(dg.float(), dg_ref, atol=2e-2, rtol=2e-2), (dg.float() - dg_ref).abs().max().item()
+    dy = _mk((M, K), dev)
+    w2 = _mk((K, N), dev, 0.2)
+    dpre = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    cs = torch.zeros(N, device=dev)
+    Kk.linear_dgrad(dy, w2, dpre, epilogue=Kk.EPI_MUL, aux_in=dg, colsum=cs)
+    ref = (dy.float() @ w2.float()) * dg.float()
+    assert torch.allclose(dpre.float(), ref, atol=5e-2, rtol=3e-2)
+    assert torch.allclose(cs, dpre.float().sum(0), atol=2e-3 * (M ** 0.5), rtol=1e-4)

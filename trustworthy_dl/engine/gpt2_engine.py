@@ -190,7 +190,7 @@ class GPT2Engine:
         self.atty = torch.empty(L, M, C, **bf)
         self.x2 = torch.empty(L, M, C, **bf)
         self.ln2 = torch.empty(L, M, C, **bf)
-        self.fch = torch.empty(L, M, 4 * C, **bf)
+        self.fch = torch.empty(L, M, 4 * C, **bf)       # gelu'(fc pre-activation), consumed by the MLP backward
         self.fcg = torch.empty(L, M, 4 * C, **bf)
         self.ln_mean = torch.empty(2 * L + 1, M, **f32)
         self.ln_rstd = torch.empty(2 * L + 1, M, **f32)
@@ -239,7 +239,7 @@ class GPT2Engine:
             p = f"h{l}."
             # ---- MLP ----
             K.linear_wgrad(dx, self.fcg[l], self.grad32(p + "proj_w"), split_k=self._split_k(C, 4 * C))
-            K.linear_dgrad(dx, self.w16(p + "proj_w"), self.dfch, epilogue=K.EPI_DGELU, aux_in=self.fch[l],
+            K.linear_dgrad(dx, self.w16(p + "proj_w"), self.dfch, epilogue=K.EPI_MUL, aux_in=self.fch[l],
                            colsum=self.grad32(p + "fc_b"))          # fc bias grad from the epilogue panels
             K.linear_wgrad(self.dfch, self.ln2[l], self.grad32(p + "fc_w"), split_k=self._split_k(4 * C, C))
             K.linear_dgrad(self.dfch, self.w16(p + "fc_w"), self.dln)
@@ -374,7 +374,7 @@ class GPT2Engine:
             K.layernorm_fwd(self.x2[l], self.w32(p + "ln2_w"), self.w32(p + "ln2_b"), self.ln2[l],
                             self.ln_mean[2 * l + 1], self.ln_rstd[2 * l + 1], self.cfg.layer_norm_eps)
             K.linear_fwd(self.ln2[l], self.w16(p + "fc_w"), self.fcg[l], bias=self.w32(p + "fc_b"),
-                         epilogue=K.EPI_GELU, aux_out=self.fch[l])
+                         epilogue=K.EPI_GELU_DG, aux_out=self.fch[l])     # fch holds gelu'(pre): backward multiplies
             K.linear_fwd(self.fcg[l], self.w16(p + "proj_w"), self.res[l + 1], bias=self.w32(p + "proj_b"),
                          epilogue=K.EPI_RESIDUAL, aux_in=self.x2[l])
         K.layernorm_fwd(self.res[L], self.w32("lnf_w"), self.w32("lnf_b"), self.lnf, self.ln_mean[2 * L],

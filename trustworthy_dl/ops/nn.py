@@ -11,6 +11,7 @@ from . import _lib
 from ._lib import f32, i32, i64, ptr, stream_ptr
 
 EPI_NONE, EPI_GELU, EPI_RESIDUAL, EPI_DGELU = 0, 1, 2, 3
+EPI_GELU_DG, EPI_MUL = 4, 5      # forward stores gelu'(pre) in aux_out; backward is then out = acc * aux_in
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *, lda: int, ldb: int,
