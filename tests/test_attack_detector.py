@@ -109,3 +109,22 @@ def test_history_ring_is_bounded():
         d.detect_output_anomaly(torch.randn(64), 0, s)
     assert len(d.output_history[0]) == 16
     assert d.output_history[0].steps_view().tolist() == list(range(24, 40))
+
+
+def test_reference_private_helpers_exist_and_agree():
+    """The reference's private decision helpers (attack_detector.py:241-363) are available under their names."""
+    import torch
+    from trustworthy_dl.security.attack_detection import AttackDetector
+    d = AttackDetector()
+    torch.manual_seed(0)
+    for i in range(12):
+        d.detect_output_anomaly(torch.randn(2000), 0, i)
+    d._update_output_baseline(0)
+    base = d.output_baselines[0]
+    assert set(base["mean"].keys()) >= {"mean", "std", "min", "max", "percentile_5", "percentile_95"}
+    calm = d._detect_statistical_anomaly(d._calculate_tensor_statistics(torch.randn(2000)), base, 0)
+    assert not calm.is_attack
+    loud = d._detect_statistical_anomaly(d._calculate_tensor_statistics(torch.randn(2000) * 40), base, 0)
+    assert loud.is_attack and loud.attack_type == d._classify_attack_type(loud.evidence)
+    assert d._detect_gradient_anomaly(d._calculate_tensor_statistics(torch.randn(2000) * 40), base).is_attack
+    assert d._classify_attack_type({}) is None

@@ -306,6 +306,20 @@ class ExperimentRunner:
         plt.legend(); plt.grid(True, alpha=0.3); plt.ylim(0, 1)
         plt.savefig(self.output_dir / "trust_evolution.png", dpi=300, bbox_inches="tight"); plt.close()
 
+    def _simulate_trust_evolution(self, node_id: int, epochs, seed: int = 0) -> List[float]:
+        """The reference's *synthetic* trust curve (experiment_runner.py:407-425): a random walk that drifts down by 0.1 per
+        epoch for attacked nodes once the attack has started.  The charts here are drawn from the measured trust history;
+        this stays available for side-by-side plots and is never mixed into results."""
+        rng = np.random.default_rng(seed + node_id)
+        epochs = list(epochs)
+        scores = [1.0]
+        for epoch in epochs[1:]:
+            attacked = (node_id in self.config.target_nodes and self.config.attack_enabled
+                        and epoch >= self.config.attack_start_epoch)
+            change = (-0.1 + rng.normal(0, 0.05)) if attacked else rng.normal(0, 0.02)
+            scores.append(float(np.clip(scores[-1] + change, 0.0, 1.0)))
+        return scores
+
     def _plot_attack_impact(self, plt, s) -> None:
         fig, axes = plt.subplots(2, 2, figsize=(15, 10))
         inj = np.maximum(1, np.asarray(s["injected"], dtype=float))

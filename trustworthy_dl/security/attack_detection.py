@@ -216,6 +216,46 @@ class AttackDetector:
             self.l2_cut, self.std_cut, self.require_evidence)
         return AttackDetectionResult(is_attack, atype, conf, evidence, self.clock(), node_id, overall)
 
+    # ---- the reference's private helpers, kept under their names (attack_detector.py:241-363) -------------------
+    def _update_output_baseline(self, node_id: int) -> None:
+        """Rebuild the output baseline of ``node_id`` from its full history (reference :241-266)."""
+        ring = self.output_history.get(node_id)
+        if ring is not None and len(ring):
+            self.output_baselines[node_id] = self._baseline_dict(ring.view(), STAT_NAMES, True)
+
+    def _update_gradient_baseline(self, node_id: int) -> None:
+        """Rebuild the gradient baseline (norm statistics) of ``node_id`` (reference :268-290)."""
+        ring = self.gradient_history.get(node_id)
+        if ring is not None and len(ring):
+            names = GRADIENT_STAT_NAMES
+            self.gradient_baselines[node_id] = self._baseline_dict(ring.view(), names, False)
+
+    def _detect_statistical_anomaly(self, current: Dict[str, float], baseline: Dict[str, Dict], node_id: int = -1) -> AttackDetectionResult:
+        """z-score decision of a statistics dict against a baseline dict (reference :292-342)."""
+        names = [n for n in current if n in baseline]
+        cur = np.array([current[n] for n in names], dtype=np.float64)
+        mean = np.array([baseline[n]["mean"] for n in names], dtype=np.float64)
+        std = np.array([baseline[n]["std"] for n in names], dtype=np.float64)
+        is_attack, atype, conf, evidence, overall = decide_from_baseline(cur, mean, std, names, self.z_evidence, self.z_decision,
+                                                                         self.l2_cut, self.std_cut, self.require_evidence)
+        return AttackDetectionResult(is_attack, atype, conf, evidence, self.clock(), node_id, overall)
+
+    def _detect_gradient_anomaly(self, current: Dict[str, float], baseline: Dict[str, Dict], node_id: int = -1) -> AttackDetectionResult:
+        """Alias of :meth:`_detect_statistical_anomaly` (reference :344-348)."""
+        return self._detect_statistical_anomaly(current, baseline, node_id)
+
+    def _classify_attack_type(self, evidence: Dict[str, Dict]) -> Optional[AttackType]:
+        """Evidence dict -> attack type (reference :350-363)."""
+        if not evidence:
+            return None
+        if "norm_l2" in evidence and evidence["norm_l2"]["z_score"] > self.l2_cut:
+            return AttackType.GRADIENT_POISONING
+        if "std" in evidence and evidence["std"]["z_score"] > self.std_cut:
+            return AttackType.DATA_POISONING
+        if "skewness" in evidence or "kurtosis" in evidence:
+            return AttackType.ADVERSARIAL_INPUT
+        return AttackType.BYZANTINE
+
     def _no_attack(self, node_id: int) -> AttackDetectionResult:
         return AttackDetectionResult(False, None, 0.0, {}, self.clock(), node_id, 0.0)
 
