@@ -1701,8 +1701,7 @@ attn_bwd_ps_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
             TRACE_AT(27);
             if (lt == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile's stores have read the staging
             asm volatile("bar.sync 2, 256;" ::: "memory");
-            float* db = p.dbias != nullptr ? p.dbias + c.h * D : nullptr;
-            auto stage_acc = [&](uint32_t taddr, uint8_t* tile, float mul, float* dbias) {
+            auto stage_acc = [&](uint32_t taddr, uint8_t* tile, float mul) {
                 uint32_t raw[32];                               // each of the two row threads handles 32 of the 64 columns
                 tmem_ld_32x32(taddr + lane_base + half * 32, raw);
                 tmem_ld_wait();
@@ -1715,30 +1714,12 @@ attn_bwd_ps_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                     u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
                     *reinterpret_cast<uint4*>(tile + swz(r, half * 4 + q)) = u;
                 }
-                if (dbias != nullptr) {
-                    // qkv bias gradient: column sums of the bf16-rounded tile.  Transposing butterfly over the warp's 32
-                    // rows: each round halves the values a lane carries; lane l ends with the sum of column l.
-                    float v[32];
-#pragma unroll
-                    for (int j2 = 0; j2 < 32; ++j2) v[j2] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j2]) * mul));
-#pragma unroll
-                    for (int off = 16; off >= 1; off >>= 1) {
-                        const bool up = (lane & off) != 0;
-#pragma unroll
-                        for (int j2 = 0; j2 < off; ++j2) {
-                            const float send = up ? v[j2] : v[j2 + off];
-                            const float keep = up ? v[j2 + off] : v[j2];
-                            v[j2] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-                        }
-                    }
-                    atomicAdd(dbias + half * 32 + lane, v[0]);
-                }
             };
             if (MODE == 0) {
-                stage_acc(tmem_a1, sOut, p.scale, db ? db + p.C : nullptr);                    // dK
-                stage_acc(tmem_a0, sOut + TILE_BYTES, 1.0f, db ? db + 2 * p.C : nullptr);      // dV
+                stage_acc(tmem_a1, sOut, p.scale);                    // dK
+                stage_acc(tmem_a0, sOut + TILE_BYTES, 1.0f);          // dV
             } else {
-                stage_acc(tmem_a0, sOut, p.scale, db);                                         // dQ
+                stage_acc(tmem_a0, sOut, p.scale);                    // dQ
             }
             tc_fence_before();
             __syncwarp();
@@ -1754,6 +1735,32 @@ attn_bwd_ps_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_co
                     tma_store_2d_tile(&tmap_dqkv, sOut, c.h * D, grow);
                 }
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            if (p.dbias != nullptr && (MODE == 0 || lt < 128)) {
+                // qkv bias gradient = column sums of the staged bf16 tiles (they stay intact until the next tile's first
+                // barrier).  128 threads per tile: thread = 16-byte piece (t & 7) of rows (t >> 3) + 16 i; the four row
+                // groups of a warp combine by shuffle, the four warps of a tile by red.global.
+                const int t = lt & 127, which = lt >> 7;              // MODE 0: tile 0 = dK, tile 1 = dV
+                const uint8_t* tile = sOut + which * TILE_BYTES;
+                const uint32_t q8 = t & 7;
+                float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const uint4 u = *reinterpret_cast<const uint4*>(tile + swz((t >> 3) + 16 * i, q8));
+                    const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                    cs[0] += f0.x; cs[1] += f0.y; cs[2] += f1.x; cs[3] += f1.y;
+                    cs[4] += f2.x; cs[5] += f2.y; cs[6] += f3.x; cs[7] += f3.y;
+                }
+#pragma unroll
+                for (int j2 = 0; j2 < 8; ++j2) {
+                    cs[j2] += __shfl_xor_sync(0xffffffffu, cs[j2], 8);
+                    cs[j2] += __shfl_xor_sync(0xffffffffu, cs[j2], 16);
+                }
+                if (lane < 8) {
+                    float* dst = p.dbias + c.h * D + (MODE == 0 ? (1 + which) * p.C : 0) + q8 * 8;
+                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(dst), "f"(cs[0]), "f"(cs[1]), "f"(cs[2]), "f"(cs[3]) : "memory");
+                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(dst + 4), "f"(cs[4]), "f"(cs[5]), "f"(cs[6]), "f"(cs[7]) : "memory");
+                }
             }
             TRACE_AT(28);
         };
@@ -1921,6 +1928,7 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
     p.scale = 1.0f / sqrtf(64.0f);
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = (__nv_bfloat16*)dqkv; p.dbias = dbias;
+    TDL_REQUIRE((reinterpret_cast<uintptr_t>(dbias) & 15) == 0, "attention backward: dbias must be 16-byte aligned");
     const int smem = 10 * TILE_BYTES + 64;
     const int smem_ws = BWD_WS_SMEM;
     static bool configured = false;
