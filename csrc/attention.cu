@@ -12,10 +12,15 @@
 //   O += P V       tcgen05.mma with A = P from TMEM and V consumed MN-major exactly as it sits in memory; partial
 //                  products land in TMEM and are folded into the register accumulator with the
 //                  running rescale
-// Backward = preprocess (delta = rowsum(dO*O)) + two tensor-core kernels:
-//   dK/dV kernel   one CTA per key block, loops over query blocks; dV += P^T dO, dK += dS^T Q with
-//                  P / dS read from smem as MN-major A operands, accumulators stay in TMEM
-//   dQ kernel      one CTA per query block, loops over key blocks; dQ += dS K
+// Backward = two persistent tensor-core kernels (one CTA per SM walking a longest-first tile list):
+//   dQ kernel      per query block, loops over key blocks; dQ += dS K; also computes delta = rowsum(dO*O) from the tiles it
+//                  already holds and writes it out for the second kernel
+//   dK/dV kernel   per key block, loops over query blocks on the TRANSPOSED tiles S^T = K Q^T, dP^T = V dO^T, so that
+//                  dV += P^T dO and dK += dS^T Q take P^T / dS^T as A operands straight from tensor memory
+//   Roles inside a CTA: one TMA warp, one MMA-issue warp (elect.sync, precomputed descriptor words), 8 warps that only
+//   turn S into P (exp2), 8 warps that turn (P, dP) into dS and write finished tiles out through TMA stores (and add
+//   the qkv bias gradient).  S is double-buffered in TMEM; P / dS are written back into the S buffer they came from.
+//   (attn_bwd_kernel / attn_bwd_ws_kernel are the earlier generations, selectable with TDL_ATTN_BWD_WS=0 / 1.)
 // The reference reaches attention only through torch/HF eager ops.
 #include "common.cuh"
 #include <cstdlib>
