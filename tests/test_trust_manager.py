@@ -153,3 +153,20 @@ def test_trust_stays_clipped(seq):
     for dev, gc in seq:
         v = tm.update_trust_score(0, dev, gc)
         assert 0.0 <= v <= 1.0
+
+
+def test_heartbeat_monitor_marks_lagging_and_silent_ranks_offline():
+    from trustworthy_dl.core import HeartbeatMonitor, NodeStatus, TrustManager
+    tm = TrustManager(num_nodes=4)
+    hb = HeartbeatMonitor(4, max_step_lag=2, timeout_s=30.0, on_offline=tm.mark_offline)
+    assert hb.observe([1, 1, 1, 1], [10.0, 10.0, 10.1, 10.0]) == []
+    # rank 2 stops advancing: 2 steps behind is tolerated, 3 is not
+    assert hb.observe([3, 3, 1, 3], [12.0, 12.0, 10.1, 12.0]) == []
+    assert hb.observe([4, 4, float("nan"), 4], [13.0, 13.0, float("nan"), 13.0]) == [2]
+    assert tm.get_node_status(2) == NodeStatus.OFFLINE
+    # rank 0 keeps the step count but its clock is a minute old
+    assert hb.observe([5, 5, 5, 5], [14.0 - 61.0, 14.0, 14.0, 14.0]) == [0]
+    assert [(e["node_id"], e["event"]) for e in hb.events] == [(2, "offline"), (0, "offline"), (2, "online")]
+    hb2 = HeartbeatMonitor(4)
+    hb2.load_state_dict(hb.state_dict())
+    assert hb2.offline.tolist() == hb.offline.tolist()

@@ -49,7 +49,7 @@ from ..security.gradient_verification import GradientVerifier
 from ..security.parameter_monitor import ParameterMonitor
 from ..utils.metrics import MetricsCollector
 from . import checkpoint as _ckpt
-from .node_monitor import NodeMonitor
+from .node_monitor import HeartbeatMonitor, NodeMonitor
 from .partition import StageMap, build_stages, unit_cost
 from .reassignment import ReassignmentPlanner, estimate_migration_time
 from .trust_manager import NodeStatus, TrustManager
@@ -111,6 +111,7 @@ class TrainingConfig:
     checkpoint_dir: str = "checkpoints"
     migration_model: str = "reference"         # reference (1 GiB/s + 2 s) | nvlink
     detector_require_evidence: bool = True     # an anomaly verdict needs >= 1 statistic beyond z_evidence (False = reference rule)
+    heartbeat_interval: int = 10               # steps between liveness gathers across ranks (0 = off)
     initial_trust: float = 1.0
     steps_per_epoch: Optional[int] = None
     seq_len: Optional[int] = None
@@ -152,6 +153,9 @@ class DistributedTrainer:
             num_nodes=config.num_nodes, trust_threshold=config.trust_threshold, initial_trust=config.initial_trust)
         self.trust_manager.resize(config.num_nodes)
         self.node_monitor = NodeMonitor()
+        # liveness: a rank whose heartbeat lags is marked OFFLINE (the reference defines the status but never sets it)
+        self.heartbeat = HeartbeatMonitor(config.num_nodes, max_step_lag=2 * max(1, config.heartbeat_interval),
+                                          on_offline=self.trust_manager.mark_offline)
         self.gradient_verifier = GradientVerifier(clip_norm=config.clip_norm)
         self.attack_detector = AttackDetector(require_evidence=config.detector_require_evidence)
         self.parameter_monitor = ParameterMonitor()
@@ -482,11 +486,28 @@ class DistributedTrainer:
             opt.step()
             opt.zero_grad(set_to_none=True)
 
+    def _heartbeat(self) -> None:
+        """Report this process's (step, time) and apply the liveness rule to everybody's reports.  Single-process runs own
+        all logical nodes, so they all beat together; multi-process runs gather one pair per rank."""
+        every = int(self.config.heartbeat_interval)
+        if every <= 0 or self.global_step % every:
+            return
+        beat = HeartbeatMonitor.beat(self.global_step, time.time())
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        if world > 1 and world == self.config.num_nodes:
+            from ..parallel import comm
+            g = comm.all_gather_vector(torch.tensor(beat, dtype=torch.float64))
+            self.heartbeat.observe(g[:, 0].tolist(), g[:, 1].tolist())
+        else:
+            n = self.config.num_nodes
+            self.heartbeat.observe([beat[0]] * n, [beat[1]] * n)
+
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
         """One full step (the body of the reference's hot loop, :391-418)."""
         self.setup()
         self.global_step += 1
         self._last_step_info = {}
+        self._heartbeat()
         if self._backend_impl is not None:
             return self._backend_impl.train_step(batch)
         t0 = time.perf_counter()

@@ -14,7 +14,7 @@ from typing import Dict, List, Optional, Sequence
 
 import numpy as np
 
-__all__ = ["NodeMonitor"]
+__all__ = ["NodeMonitor", "HeartbeatMonitor"]
 
 
 class NodeMonitor:
@@ -95,3 +95,75 @@ class NodeMonitor:
         for k, v in self._gnorms.items():
             self._gvar.setdefault(k, np.zeros_like(v))
         self._n_grad = {int(k): int(v) for k, v in sd["n_grad"].items()}
+
+
+class HeartbeatMonitor:
+    """Host-side liveness view of the ranks (the reference defines ``NodeStatus.OFFLINE`` but has no
+    heartbeat, timeout or straggler detection, so nothing ever sets it).
+
+    Every rank reports ``(step, wall_time)`` once per step -- the multi-process strategies already gather a small decision
+    vector per step, the heartbeat rides in it -- and every rank runs the same rule on the same gathered data:
+
+    * a rank whose step counter lags the median by more than ``max_step_lag`` steps, or
+    * a rank whose report is older than ``timeout_s`` seconds relative to the newest report
+
+    is declared offline (``on_offline`` callback, by default ``TrustManager.mark_offline``); a rank that reports again
+    within bounds is returned to service through ``on_online``.  The device-side counterpart is the watchdog of the
+    exchange kernel (``csrc/trust_allreduce.cu``), which turns a peer that never arrives into a launch failure.
+    """
+
+    def __init__(self, num_nodes: int, max_step_lag: int = 2, timeout_s: float = 60.0, on_offline=None, on_online=None):
+        self.num_nodes = int(num_nodes)
+        self.max_step_lag = int(max_step_lag)
+        self.timeout_s = float(timeout_s)
+        self.on_offline = on_offline
+        self.on_online = on_online
+        self.last_step = np.full(self.num_nodes, -1, dtype=np.int64)
+        self.last_time = np.zeros(self.num_nodes, dtype=np.float64)
+        self.offline = np.zeros(self.num_nodes, dtype=bool)
+        self.events: List[Dict] = []
+
+    @staticmethod
+    def beat(step: int, now: float) -> List[float]:
+        """The two numbers a rank contributes to the per-step gather."""
+        return [float(step), float(now)]
+
+    def observe(self, steps: Sequence[float], times: Sequence[float]) -> List[int]:
+        """Feed one gathered heartbeat (index = rank; ``nan`` = no report this round).  Returns the ranks that are
+        offline after the update."""
+        steps = np.asarray(steps, dtype=np.float64)
+        times = np.asarray(times, dtype=np.float64)
+        seen = ~np.isnan(steps)
+        self.last_step[seen] = steps[seen].astype(np.int64)
+        self.last_time[seen] = times[seen]
+        known = self.last_step >= 0
+        if not known.any():
+            return []
+        med = float(np.median(self.last_step[known]))
+        newest = float(self.last_time[known].max())
+        for n in range(self.num_nodes):
+            if not known[n]:
+                continue
+            late = (med - self.last_step[n]) > self.max_step_lag or (newest - self.last_time[n]) > self.timeout_s
+            if late and not self.offline[n]:
+                self.offline[n] = True
+                self.events.append({"node_id": n, "event": "offline", "step": int(med), "lag": float(med - self.last_step[n]),
+                                    "silence_s": float(newest - self.last_time[n])})
+                if self.on_offline is not None:
+                    self.on_offline(n)
+            elif not late and self.offline[n]:
+                self.offline[n] = False
+                self.events.append({"node_id": n, "event": "online", "step": int(med)})
+                if self.on_online is not None:
+                    self.on_online(n)
+        return [int(n) for n in np.nonzero(self.offline)[0]]
+
+    def state_dict(self) -> Dict:
+        return {"last_step": self.last_step.tolist(), "last_time": self.last_time.tolist(), "offline": self.offline.tolist(),
+                "events": list(self.events)}
+
+    def load_state_dict(self, sd: Dict) -> None:
+        self.last_step = np.asarray(sd["last_step"], dtype=np.int64)
+        self.last_time = np.asarray(sd["last_time"], dtype=np.float64)
+        self.offline = np.asarray(sd["offline"], dtype=bool)
+        self.events = list(sd.get("events", []))
