@@ -606,6 +606,29 @@ __global__ void __launch_bounds__(256) pack_norm_kernel(const float* __restrict_
     }
 }
 
+// sum of squares of an already packed bucket (the eager data-parallel path writes gradients straight into the bucket)
+template <typename T>
+__global__ void __launch_bounds__(256) sumsq_kernel(const T* __restrict__ x, long long n, double* __restrict__ sumsq) {
+    __shared__ double sh[8];
+    float acc = 0.f;
+    double dacc = 0.0;
+    int run = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = to_f32<T>(x[i]);
+        acc = fmaf(v, v, acc);
+        if (++run == 64) { dacc += acc; acc = 0.f; run = 0; }
+    }
+    dacc += acc;
+    for (int o = 16; o > 0; o >>= 1) dacc += __shfl_xor_sync(0xffffffffu, dacc, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = dacc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        atomicAdd(sumsq, t);
+    }
+}
+
 // ------------------------------------------------------------------------------------ multi-tensor sq norm
 template <typename T>
 __global__ void __launch_bounds__(256) multi_sqnorm_kernel(const long long* __restrict__ ptrs, const long long* __restrict__ numels,
@@ -682,6 +705,19 @@ __global__ void __launch_bounds__(256) poison_kernel(T* __restrict__ x, long lon
             v += b * sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307f * u2);
         }
         x[i] = from_f32<T>(v);
+    }
+}
+
+// parameter-poisoning fault injection that can sit inside a captured step: does nothing while *level == 0,
+// otherwise adds level * N(0,1) to every element (a compromised owner corrupting the shard it publishes)
+__global__ void __launch_bounds__(256) poison_if_kernel(__nv_bfloat16* __restrict__ x, long long n, const float* __restrict__ level,
+                                                        unsigned long long seed) {
+    const float b = *level;
+    if (b == 0.f) return;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float u1 = (mix32(seed * 0x100000001B3ull + 2 * i) + 1.0f) * (1.0f / 4294967808.0f);
+        const float u2 = mix32(seed * 0x100000001B3ull + 2 * i + 1) * (1.0f / 4294967296.0f);
+        x[i] = __float2bfloat16(__bfloat162float(x[i]) + b * sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307f * u2));
     }
 }
 
@@ -872,6 +908,17 @@ extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double
     return 0;
 }
 
+// sumsq (device double) += sum x^2 ; the cross-rank exchange re-zeroes the accumulator after publishing it
+extern "C" int tdl_sumsq(const void* x, int dtype, int64_t n, double* sumsq, void* stream) {
+    const int grid = grid_for(n, 256 * 16);
+    if (dtype == TDL_F32) sumsq_kernel<float><<<grid, 256, 0, STREAM(stream)>>>((const float*)x, n, sumsq);
+    else if (dtype == TDL_BF16) sumsq_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)x, n, sumsq);
+    else if (dtype == TDL_F16) sumsq_kernel<__half><<<grid, 256, 0, STREAM(stream)>>>((const __half*)x, n, sumsq);
+    else return tdl_set_error("unsupported dtype %d", dtype);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int tdl_multi_sqnorm(const int64_t* ptrs_dev, const int64_t* numels_dev, int num, int dtype, float* out,
                                 void* stream) {
     if (num <= 0) return 0;
@@ -905,6 +952,12 @@ extern "C" int tdl_poison_inplace(void* x, int64_t n, int dtype, float a, float 
     else if (dtype == TDL_BF16) poison_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((__nv_bfloat16*)x, n, a, b, (unsigned long long)seed);
     else if (dtype == TDL_F16) poison_kernel<__half><<<grid, 256, 0, STREAM(stream)>>>((__half*)x, n, a, b, (unsigned long long)seed);
     else return tdl_set_error("unsupported dtype %d", dtype);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_poison_if(void* x_bf16, int64_t n, const float* level_dev, int64_t seed, void* stream) {
+    poison_if_kernel<<<grid_for(n, 256 * 8), 256, 0, STREAM(stream)>>>((__nv_bfloat16*)x_bf16, n, level_dev, (unsigned long long)seed);
     TDL_LAUNCH_CHECK();
     return 0;
 }

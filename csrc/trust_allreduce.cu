@@ -73,12 +73,27 @@ template <int W> __device__ __forceinline__ float median_w(float (&a)[W]) {
     return (W & 1) ? a[W / 2] : 0.5f * (a[W / 2 - 1] + a[W / 2]);
 }
 
+// NVLS store: one 16-byte store to the multicast address lands in every GPU bound to the multicast object
+template <typename T> __device__ __forceinline__ void st_multimem_v4(void* p, const uint4& v);
+template <> __device__ __forceinline__ void st_multimem_v4<__nv_bfloat16>(void* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+template <> __device__ __forceinline__ void st_multimem_v4<float>(void* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)),
+                 "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
+
 // stats_partial: [W] dot(g_i, med) then [1] |med|^2   (doubles, accumulated with atomics)
-template <typename T, int W>
-__global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs out, long long vec_begin, long long vec_end,
-                                                           const float* __restrict__ coeff, double* __restrict__ stats_partial) {
+// store_rank < 0: the reduced vector goes to every peer (W stores, or ONE multimem.st when `mc_out` is the bucket's
+// multicast address); store_rank >= 0: only to out.p[store_rank] (ZeRO-1: the owner alone consumes its slice).
+// TPB = 64 is the variant that runs UNDER the backward pass: 2 warps x <= 128 registers fit beside a resident GEMM or
+// attention CTA (which leave ~10 K registers and a few KB of shared memory per SM).
+template <typename T, int W, int TPB>
+__global__ void __launch_bounds__(TPB) trust_reduce_kernel(PeerPtrs in, PeerPtrs out, long long vec_begin, long long vec_end,
+                                                           const float* __restrict__ coeff, double* __restrict__ stats_partial,
+                                                           int store_rank, void* mc_out) {
     constexpr int VN = Vec<T>::N;
-    __shared__ double sh[8][W + 1];
+    __shared__ double sh[TPB / 32][W + 1];
     float c[W];
 #pragma unroll
     for (int i = 0; i < W; ++i) c[i] = coeff[i];
@@ -111,7 +126,13 @@ __global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs
         uint4 (&raw)[W] = rawu[u];
         float g[W][VN];
 #pragma unroll
-        for (int i = 0; i < W; ++i) unpack_vec<T>(raw[i], g[i]);
+        for (int i = 0; i < W; ++i) {
+            unpack_vec<T>(raw[i], g[i]);
+            // a rank that ships NaN/Inf gets coefficient 0 (non-finite norm), but 0 * NaN is still NaN: non-finite
+            // elements are read as 0 so they can reach neither the aggregate nor the median / dot statistics
+#pragma unroll
+            for (int e = 0; e < VN; ++e) g[i][e] = fabsf(g[i][e]) <= 3.3895314e38f ? g[i][e] : 0.f;
+        }
         float o[VN];
 #pragma unroll
         for (int e = 0; e < VN; ++e) {
@@ -126,8 +147,14 @@ __global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs
             o[e] = acc;
         }
         const uint4 packed = pack_vec<T>(o);
+        if (store_rank >= 0) {
+            st_peer_v4(reinterpret_cast<uint4*>(out.p[store_rank]) + v, packed);
+        } else if (mc_out != nullptr) {
+            st_multimem_v4<T>(reinterpret_cast<uint4*>(mc_out) + v, packed);
+        } else {
 #pragma unroll
-        for (int i = 0; i < W; ++i) st_peer_v4(reinterpret_cast<uint4*>(out.p[i]) + v, packed);
+            for (int i = 0; i < W; ++i) st_peer_v4(reinterpret_cast<uint4*>(out.p[i]) + v, packed);
+        }
         if (++run == 32) {
 #pragma unroll
             for (int i = 0; i < W; ++i) { ddot[i] += dot[i]; dot[i] = 0.f; }
@@ -154,8 +181,54 @@ __global__ void __launch_bounds__(256) trust_reduce_kernel(PeerPtrs in, PeerPtrs
     __syncthreads();
     if (threadIdx.x <= W) {
         double t = 0;
-        for (int w2 = 0; w2 < 8; ++w2) t += sh[w2][threadIdx.x];
+        for (int w2 = 0; w2 < TPB / 32; ++w2) t += sh[w2][threadIdx.x];
         atomicAdd(&stats_partial[threadIdx.x], t);
+    }
+}
+
+// ------------------------------------------------------------------ K4: plain sum all-reduce (no-security arm)
+// Two-shot over the same symmetric bucket.  NVLS form: multimem.ld_reduce pulls the slice already summed inside the
+// switch (fp32 accumulation), the scaled result goes back with one multimem.st.  P2P form (no multicast object): W
+// peer loads + W peer stores, i.e. K2 without the median network -- the arm the detection overhead is measured against.
+template <typename T> __device__ __forceinline__ uint4 ld_reduce_multimem_v4(const void* p);
+template <> __device__ __forceinline__ uint4 ld_reduce_multimem_v4<__nv_bfloat16>(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+template <> __device__ __forceinline__ uint4 ld_reduce_multimem_v4<float>(const void* p) {
+    float a, b, c, d;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(p) : "memory");
+    return make_uint4(__float_as_uint(a), __float_as_uint(b), __float_as_uint(c), __float_as_uint(d));
+}
+
+template <typename T, bool NVLS>
+__global__ void __launch_bounds__(256) sum_allreduce_kernel(PeerPtrs bufs, void* mc, int W, long long vec_begin, long long vec_end,
+                                                            float scale) {
+    constexpr int VN = Vec<T>::N;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = vec_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; v < vec_end; v += stride) {
+        float acc[VN];
+        if (NVLS) {
+            const uint4 u = ld_reduce_multimem_v4<T>(reinterpret_cast<const uint4*>(mc) + v);
+            unpack_vec<T>(u, acc);
+        } else {
+#pragma unroll
+            for (int e = 0; e < VN; ++e) acc[e] = 0.f;
+            for (int i = 0; i < W; ++i) {
+                float g[VN];
+                unpack_vec<T>(ld_peer_v4(reinterpret_cast<const uint4*>(bufs.p[i]) + v), g);
+#pragma unroll
+                for (int e = 0; e < VN; ++e) acc[e] += g[e];
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < VN; ++e) acc[e] *= scale;
+        const uint4 packed = pack_vec<T>(acc);
+        if (NVLS) st_multimem_v4<T>(reinterpret_cast<uint4*>(mc) + v, packed);
+        else for (int i = 0; i < W; ++i) st_peer_v4(reinterpret_cast<uint4*>(bufs.p[i]) + v, packed);
     }
 }
 
@@ -206,10 +279,14 @@ struct TrustParams {
 };
 
 // norms_sq[W] (from the exchange pad), trust[W], status[W] -> coeff[W]
+// acc_sq[W] / acc_bad[W] (optional): a step that reduces several buckets accumulates the squared norms and the
+// "rejected in some bucket" marks here; finalize then judges the step as a whole.
 __global__ void coefficients_kernel(const double* __restrict__ gathered /*[W][EXCH_MAX], col 0 = sumsq*/, int W,
                                     const float* __restrict__ trust, const int* __restrict__ status,
-                                    TrustParams tp, float* __restrict__ coeff, float* __restrict__ norms_out) {
+                                    TrustParams tp, float* __restrict__ coeff, float* __restrict__ norms_out,
+                                    double* __restrict__ acc_sq, int* __restrict__ acc_bad) {
     if (threadIdx.x != 0) return;
+    if (acc_sq != nullptr) for (int i = 0; i < W; ++i) acc_sq[i] += gathered[i * EXCH_MAX];
     float n[MAX_W], w[MAX_W];
     bool live[MAX_W];
     float sorted[MAX_W];
@@ -221,7 +298,7 @@ __global__ void coefficients_kernel(const double* __restrict__ gathered /*[W][EX
         live[i] = w[i] > 0.f && isfinite(n[i]);
         if (live[i]) sorted[k++] = n[i];
     }
-    if (k == 0) { for (int i = 0; i < W; ++i) coeff[i] = 0.f; return; }
+    if (k == 0) { for (int i = 0; i < W; ++i) { coeff[i] = 0.f; if (acc_bad != nullptr && w[i] > 0.f) acc_bad[i] = 1; } return; }
     for (int a = 1; a < k; ++a) { float v = sorted[a]; int b = a - 1; while (b >= 0 && sorted[b] > v) { sorted[b + 1] = sorted[b]; --b; } sorted[b + 1] = v; }
     const float med = sorted[(k - 1) / 2];       // lower median: robust against one exploding norm even for k = 2
     float tot = 0.f;
@@ -235,16 +312,27 @@ __global__ void coefficients_kernel(const double* __restrict__ gathered /*[W][EX
             c = w[i] * clip / tot;
         }
         coeff[i] = c;
+        if (acc_bad != nullptr && !valid[i] && w[i] > 0.f) acc_bad[i] = 1;       // live rank rejected in this bucket
     }
 }
 
 // gathered partials [W ranks][W dots + med2] -> stats[W][4] = (norm, dot, |med|^2, cos); then the trust EMA + FSM.
 // flags_out[i]: bit0 = failed verification this step (norm ratio / cosine / non-finite).
-__global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W, const float* __restrict__ norms,
+// acc_sq / acc_bad (optional, see coefficients_kernel): whole-step norms come from the accumulated squared bucket
+// norms, a rank rejected in any bucket fails verification; both are cleared for the next step.
+__global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W, const float* __restrict__ norms_in,
                                       const float* __restrict__ out_dev, TrustParams tp, float* __restrict__ stats,
                                       float* __restrict__ trust, int* __restrict__ status, int* __restrict__ flags_out,
-                                      int update_trust) {
+                                      int update_trust, double* __restrict__ acc_sq, int* __restrict__ acc_bad) {
     if (threadIdx.x != 0) return;
+    float norms[MAX_W];
+    bool bad[MAX_W];
+    for (int i = 0; i < W; ++i) {
+        norms[i] = acc_sq != nullptr ? sqrtf((float)acc_sq[i]) : norms_in[i];
+        bad[i] = acc_bad != nullptr && acc_bad[i] != 0;
+        if (acc_sq != nullptr) acc_sq[i] = 0.0;
+        if (acc_bad != nullptr) acc_bad[i] = 0;
+    }
     double med2 = 0.0, dot[MAX_W];
     for (int i = 0; i < W; ++i) dot[i] = 0.0;
     for (int r = 0; r < W; ++r) {
@@ -271,7 +359,7 @@ __global__ void finalize_trust_kernel(const double* __restrict__ gathered, int W
         const float n = norms[i];
         const float cosv = (n > 0.f && mn > 0.f) ? (float)(dot[i] / ((double)n * mn)) : 1.f;
         stats[i * 4 + 0] = n; stats[i * 4 + 1] = (float)dot[i]; stats[i * 4 + 2] = (float)med2; stats[i * 4 + 3] = cosv;
-        bool ok = isfinite(n) && isfinite(cosv);
+        bool ok = isfinite(n) && isfinite(cosv) && !bad[i];
         if (W >= 3) ok = ok && cosv >= tp.cosine_min;
         if (W >= 2 && ref > 0.f) ok = ok && n <= tp.norm_ratio_max * ref;
         int fl = ok ? 0 : 1;
@@ -304,19 +392,25 @@ extern "C" size_t tdl_exchange_pad_bytes(void) { return sizeof(ExchPad); }
 // One rank's share of the fused reduction.  in_ptrs/out_ptrs: W device pointers (peer-mapped or local).
 // The slice [vec_begin, vec_end) is in 16-byte vectors.  coeff: device [W].  stats_partial: device doubles
 // [W+1], accumulated (caller zeroes; the exchange kernel re-zeroes it after publishing).
-extern "C" int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin,
-                                int64_t vec_end, const float* coeff, double* stats_partial, void* stream) {
+// store_rank: -1 = every peer, r = only out_ptrs[r].  mc_out: multicast (NVLS) address of the bucket or NULL.
+// threads: 256 (stand-alone) or 64 (the variant meant to run under other kernels); max_blocks <= 0: 4 x #SMs.
+extern "C" int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin,
+                                   int64_t vec_end, const float* coeff, double* stats_partial, int store_rank, void* mc_out,
+                                   int threads, int max_blocks, void* stream) {
     TDL_REQUIRE(W >= 1 && W <= MAX_W, "world size %d unsupported (1..%d)", W, MAX_W);
+    TDL_REQUIRE(store_rank < W, "store_rank %d out of range", store_rank);
+    TDL_REQUIRE(threads == 256 || threads == 64, "trust_reduce: 64 or 256 threads per block");
     PeerPtrs in{}, out{};
     for (int i = 0; i < W; ++i) { in.p[i] = in_ptrs[i]; out.p[i] = out_ptrs[i]; }
     const long long nvec = vec_end - vec_begin;
     if (nvec <= 0) return 0;
-    long long blocks = (nvec + 255) / 256;
+    long long blocks = (nvec + threads - 1) / threads;
     static int per_sm = -1;                      // TDL_TR_BLOCKS: resident blocks per SM for the reduction
     if (per_sm < 0) { const char* e = getenv("TDL_TR_BLOCKS"); per_sm = e ? atoi(e) : 4; if (per_sm < 1) per_sm = 1; }
-    const long long cap = (long long)tdl_num_sms() * per_sm;
+    const long long cap = max_blocks > 0 ? max_blocks : (long long)tdl_num_sms() * per_sm;
     const int grid = (int)(blocks > cap ? cap : blocks);
-#define LAUNCH(T, WW) trust_reduce_kernel<T, WW><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial)
+#define LAUNCH(T, WW) do { if (threads == 256) trust_reduce_kernel<T, WW, 256><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); \
+                           else trust_reduce_kernel<T, WW, 64><<<grid, 64, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); } while (0)
 #define BY_W(T) switch (W) { case 1: LAUNCH(T, 1); break; case 2: LAUNCH(T, 2); break; case 3: LAUNCH(T, 3); break; \
     case 4: LAUNCH(T, 4); break; case 5: LAUNCH(T, 5); break; case 6: LAUNCH(T, 6); break; case 7: LAUNCH(T, 7); break; \
     case 8: LAUNCH(T, 8); break; }
@@ -325,6 +419,35 @@ extern "C" int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int
     else return tdl_set_error("trust_reduce: dtype %d unsupported", dtype);
 #undef BY_W
 #undef LAUNCH
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin,
+                                int64_t vec_end, const float* coeff, double* stats_partial, void* stream) {
+    return tdl_trust_reduce_ex(in_ptrs, out_ptrs, W, dtype, vec_begin, vec_end, coeff, stats_partial, -1, nullptr, 256, 0, stream);
+}
+
+// K4: plain (sum x scale) all-reduce of slice [vec_begin, vec_end) of a symmetric bucket: through the switch when
+// `mc_ptr` (the multicast address) is given, over P2P loads/stores otherwise.  The caller brackets it with tdl_exchange
+// barriers exactly like tdl_trust_reduce.
+extern "C" int tdl_sum_allreduce(void* const* buf_ptrs, void* mc_ptr, int W, int dtype, int64_t vec_begin, int64_t vec_end,
+                                 float scale, int max_blocks, void* stream) {
+    TDL_REQUIRE(W >= 1 && W <= MAX_W, "world size %d unsupported (1..%d)", W, MAX_W);
+    PeerPtrs b{};
+    for (int i = 0; i < W; ++i) b.p[i] = buf_ptrs[i];
+    const long long nvec = vec_end - vec_begin;
+    if (nvec <= 0) return 0;
+    long long blocks = (nvec + 255) / 256;
+    const long long cap = max_blocks > 0 ? max_blocks : (long long)tdl_num_sms() * 4;
+    const int grid = (int)(blocks > cap ? cap : blocks);
+    if (dtype == TDL_BF16) {
+        if (mc_ptr) sum_allreduce_kernel<__nv_bfloat16, true><<<grid, 256, 0, STREAM(stream)>>>(b, mc_ptr, W, vec_begin, vec_end, scale);
+        else        sum_allreduce_kernel<__nv_bfloat16, false><<<grid, 256, 0, STREAM(stream)>>>(b, mc_ptr, W, vec_begin, vec_end, scale);
+    } else if (dtype == TDL_F32) {
+        if (mc_ptr) sum_allreduce_kernel<float, true><<<grid, 256, 0, STREAM(stream)>>>(b, mc_ptr, W, vec_begin, vec_end, scale);
+        else        sum_allreduce_kernel<float, false><<<grid, 256, 0, STREAM(stream)>>>(b, mc_ptr, W, vec_begin, vec_end, scale);
+    } else return tdl_set_error("sum_allreduce: dtype %d unsupported", dtype);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -339,6 +462,40 @@ extern "C" int tdl_exchange(void* const* pad_ptrs, int rank, int W, int which, c
     return 0;
 }
 
+// copies what the peers published in gather area `which` (count 8-byte words per rank) into out[W][count]
+__global__ void exchange_read_kernel(const ExchPad* pad, int W, int which, int count, unsigned long long* __restrict__ out) {
+    const int t = threadIdx.x;
+    if (t < W * count) out[t] = reinterpret_cast<const unsigned long long*>(&pad->gather[which][t / count][0])[t % count];
+}
+
+// K9 verdict on the device: shard i is intact iff the checksum this rank folded while pulling it equals the one its
+// owner published (both mod 2^32 per word).  flags[i] |= 1 on mismatch.
+__global__ void integrity_compare_kernel(const unsigned long long* __restrict__ seen, const unsigned long long* __restrict__ pub,
+                                         int W, int* __restrict__ flags) {
+    const int i = threadIdx.x;
+    if (i < W) {
+        const bool same = (seen[2 * i] & 0xFFFFFFFFull) == (pub[2 * i] & 0xFFFFFFFFull) &&
+                          (seen[2 * i + 1] & 0xFFFFFFFFull) == (pub[2 * i + 1] & 0xFFFFFFFFull);
+        if (!same) flags[i] |= 1;
+    }
+}
+
+extern "C" int tdl_exchange_read(const void* my_pad, int W, int which, int count, void* out_u64, void* stream) {
+    TDL_REQUIRE(W >= 1 && W <= MAX_W && count >= 1 && count <= EXCH_MAX && (which == 0 || which == 1), "bad exchange_read arguments");
+    exchange_read_kernel<<<1, 128, 0, STREAM(stream)>>>(reinterpret_cast<const ExchPad*>(my_pad), W, which, count,
+                                                        reinterpret_cast<unsigned long long*>(out_u64));
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_integrity_compare(const void* seen_u64, const void* published_u64, int W, int* flags, void* stream) {
+    TDL_REQUIRE(W >= 1 && W <= MAX_W, "world size %d unsupported", W);
+    integrity_compare_kernel<<<1, 32, 0, STREAM(stream)>>>(reinterpret_cast<const unsigned long long*>(seen_u64),
+                                                           reinterpret_cast<const unsigned long long*>(published_u64), W, flags);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
 static TrustParams make_tp(const float* f) {
     TrustParams tp;
     tp.alpha = f[0]; tp.threshold = f[1]; tp.compromised_below = f[2]; tp.recovering_above = f[3]; tp.retrust_above = f[4];
@@ -349,10 +506,27 @@ static TrustParams make_tp(const float* f) {
 
 // params12 (host floats): alpha, threshold, compromised_below, recovering_above, retrust_above, penalty,
 //                         clip_ratio, norm_ratio_max, cosine_min, w_dev, w_gc, base_score
+extern "C" int tdl_trust_coefficients_acc(const void* my_pad, int W, const float* trust, const int* status,
+                                          const float* params12, float* coeff, float* norms_out, double* acc_sq,
+                                          int* acc_bad, void* stream) {
+    const ExchPad* pad = reinterpret_cast<const ExchPad*>(my_pad);
+    coefficients_kernel<<<1, 32, 0, STREAM(stream)>>>(&pad->gather[0][0][0], W, trust, status, make_tp(params12), coeff, norms_out,
+                                                      acc_sq, acc_bad);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int tdl_trust_coefficients(const void* my_pad, int W, const float* trust, const int* status,
                                       const float* params12, float* coeff, float* norms_out, void* stream) {
+    return tdl_trust_coefficients_acc(my_pad, W, trust, status, params12, coeff, norms_out, nullptr, nullptr, stream);
+}
+
+extern "C" int tdl_trust_finalize_acc(const void* my_pad, int W, const float* norms, const float* out_dev,
+                                      const float* params12, float* stats, float* trust, int* status, int* flags_out,
+                                      int update_trust, double* acc_sq, int* acc_bad, void* stream) {
     const ExchPad* pad = reinterpret_cast<const ExchPad*>(my_pad);
-    coefficients_kernel<<<1, 32, 0, STREAM(stream)>>>(&pad->gather[0][0][0], W, trust, status, make_tp(params12), coeff, norms_out);
+    finalize_trust_kernel<<<1, 32, 0, STREAM(stream)>>>(&pad->gather[1][0][0], W, norms, out_dev, make_tp(params12), stats, trust,
+                                                        status, flags_out, update_trust, acc_sq, acc_bad);
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -360,9 +534,6 @@ extern "C" int tdl_trust_coefficients(const void* my_pad, int W, const float* tr
 extern "C" int tdl_trust_finalize(const void* my_pad, int W, const float* norms, const float* out_dev,
                                   const float* params12, float* stats, float* trust, int* status, int* flags_out,
                                   int update_trust, void* stream) {
-    const ExchPad* pad = reinterpret_cast<const ExchPad*>(my_pad);
-    finalize_trust_kernel<<<1, 32, 0, STREAM(stream)>>>(&pad->gather[1][0][0], W, norms, out_dev, make_tp(params12), stats, trust,
-                                                        status, flags_out, update_trust);
-    TDL_LAUNCH_CHECK();
-    return 0;
+    return tdl_trust_finalize_acc(my_pad, W, norms, out_dev, params12, stats, trust, status, flags_out, update_trust, nullptr,
+                                  nullptr, stream);
 }

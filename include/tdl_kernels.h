@@ -96,16 +96,41 @@ int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, co
 size_t tdl_exchange_pad_bytes(void);
 int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
                      const float* coeff, double* stats_partial, void* stream);
+/* as tdl_trust_reduce; store_rank >= 0: only out_ptrs[store_rank] receives the result (ZeRO-1 owner slice); mc_out: NVLS
+ * multicast address of the bucket (one multimem.st instead of W peer stores) or NULL; threads 256, or 64 for the variant
+ * small enough to run beside a resident GEMM CTA (gradient aggregation overlapped with backward); max_blocks <= 0: default */
+int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
+                        const float* coeff, double* stats_partial, int store_rank, void* mc_out, int threads, int max_blocks,
+                        void* stream);
+/* K4: plain (sum x scale) all-reduce of a slice of a symmetric bucket: multimem.ld_reduce + multimem.st through the
+ * switch when mc_ptr != NULL, P2P loads/stores otherwise (the no-security arm the detection overhead is measured against) */
+int tdl_sum_allreduce(void* const* buf_ptrs, void* mc_ptr, int W, int dtype, int64_t vec_begin, int64_t vec_end, float scale,
+                      int max_blocks, void* stream);
+int tdl_sumsq(const void* x, int dtype, int64_t n, double* sumsq, void* stream);
 int tdl_exchange(void* const* pad_ptrs, int rank, int W, int which, const double* vals, int count,
                  unsigned int* epoch_counter, int zero_vals, void* stream);
 int tdl_trust_coefficients(const void* my_pad, int W, const float* trust, const int* status, const float* params12,
                            float* coeff, float* norms_out, void* stream);
+/* bucketed steps: acc_sq[W] (double) / acc_bad[W] (int) accumulate squared bucket norms and per-bucket rejections over
+ * the coefficient calls of a step; finalize consumes and clears them (NULL: single-bucket behaviour) */
+int tdl_trust_coefficients_acc(const void* my_pad, int W, const float* trust, const int* status, const float* params12,
+                               float* coeff, float* norms_out, double* acc_sq, int* acc_bad, void* stream);
+int tdl_trust_finalize_acc(const void* my_pad, int W, const float* norms, const float* out_dev, const float* params12,
+                           float* stats, float* trust, int* status, int* flags_out, int update_trust, double* acc_sq,
+                           int* acc_bad, void* stream);
 int tdl_trust_finalize(const void* my_pad, int W, const float* norms, const float* out_dev, const float* params12,
                        float* stats, float* trust, int* status, int* flags_out, int update_trust, void* stream);
 
 /* ---- K9: parameter all-gather with fused checksum + drift ("Param Monitor", README.md:22) -------- */
 int tdl_param_gather(const void* const* shard_ptrs, int W, int dtype, void* dst, void* prev, int64_t shard_elems,
                      void* sums_u64, double* drift, void* stream);
+
+/* device-side verdict of the gather: what the owners published (read back from the exchange pad) against the
+ * checksums folded while pulling; flags[i] |= 1 when shard i does not match */
+int tdl_exchange_read(const void* my_pad, int W, int which, int count, void* out_u64, void* stream);
+int tdl_integrity_compare(const void* seen_u64, const void* published_u64, int W, int* flags, void* stream);
+/* graph-capturable parameter-poisoning hook: adds *level_dev * N(0,1) to a bf16 shard while *level_dev != 0 */
+int tdl_poison_if(void* x_bf16, int64_t n, const float* level_dev, int64_t seed, void* stream);
 
 /* ---- K13: conv epilogue (ResNet/VGG stages left unimplemented at distributed_trainer.py:137-144) */
 int tdl_conv_epilogue_fwd(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t N,

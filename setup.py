@@ -27,7 +27,11 @@ setup(
     package_data={"trustworthy_dl": ["_C/*.so"]},
     python_requires=">=3.9",
     install_requires=["torch>=2.4", "numpy", "scipy", "scikit-learn", "pandas", "pyyaml"],
-    extras_require={"dev": ["pytest", "hypothesis", "pytest-timeout"], "plots": ["matplotlib"]},
+    # extras of reference setup_py.py:43-59 (dev / docs / experiments) plus the optional chart backend
+    extras_require={"dev": ["pytest", "hypothesis", "pytest-timeout", "black", "isort", "mypy", "flake8"],
+                    "docs": ["sphinx", "sphinx-rtd-theme"],
+                    "experiments": ["wandb", "tensorboard", "jupyter"],
+                    "plots": ["matplotlib"]},
     entry_points={"console_scripts": [
         "trustworthy-dl-train=trustworthy_dl.cli:main",
         "trustworthy-dl-experiment=trustworthy_dl.experiments.runner:main",

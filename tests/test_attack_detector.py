@@ -51,6 +51,31 @@ def test_decisions_match_reference(ref_detector, poison):
         assert ours.last_result[0].confidence > 0.5
 
 
+@pytest.mark.parametrize("poison", ["x1.5", "x2", "x3", "x5", "x10", "x100", "flip", "noise", "shift", "x0.2"])
+def test_injected_poisoning_same_verdict_with_and_without_evidence_rule(ref_detector, poison):
+    """The trainer's default (``detector_require_evidence=True``, an extension) must not change any verdict on
+    injected poisoning: every scenario gets the verdict of the unmodified reference rule, step by step."""
+    torch.manual_seed(0)
+    strict, plain, ref = AttackDetector(require_evidence=True), AttackDetector(require_evidence=False), ref_detector.AttackDetector()
+    for step in range(30):
+        x = torch.randn(4, 64, 128)
+        assert strict.detect_output_anomaly(x, 0, step) == plain.detect_output_anomaly(x, 0, step) \
+            == ref.detect_output_anomaly(x, 0, step)
+    x = torch.randn(4, 64, 128)
+    if poison.startswith("x"):
+        x = x * float(poison[1:])
+    elif poison == "flip":
+        x = -x
+    elif poison == "shift":
+        x = x + 0.75
+    else:
+        x = x + 0.5 * torch.randn_like(x)
+    a, b, c = (d.detect_output_anomaly(x, 0, 30) for d in (strict, plain, ref))
+    assert a == b == c
+    if a:
+        assert strict.last_result[0].attack_type == plain.last_result[0].attack_type
+
+
 def test_first_nine_calls_never_flag_and_none_is_attack():
     d = AttackDetector()
     assert d.detect_output_anomaly(None, 0, 0) is True

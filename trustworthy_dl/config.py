@@ -49,7 +49,8 @@ def training_config_from_dict(d: Dict[str, Any], **overrides) -> TrainingConfig:
     opt = {"checkpoint_interval": tr, "steps_per_epoch": tr, "seq_len": tr, "optimizer": tr, "weight_decay": tr,
            "dtype": tr, "clip_norm": tr, "micro_batches": ds, "tp_size": ds, "pp_size": ds, "dp_size": ds,
            "max_reassignment_attempts": sec, "device": ds, "lr_schedule": tr, "checkpoint_dir": tr, "seed": tr,
-           "engine": tr, "migration_model": ds}
+           "engine": tr, "migration_model": ds, "zero": ds,
+           "detector_require_evidence": sec, "heartbeat_interval": ds}
     for name, section in opt.items():
         if name in section:
             kw[name] = section[name]

@@ -118,6 +118,8 @@ class TrainingConfig:
     log_interval: int = 10
     seed: int = 0
     engine: str = "auto"                       # auto | eager | fused (GPT2Engine on sm_100a)
+    zero: int = 0                              # 1 = ZeRO-1 on the fused data-parallel path: sharded optimizer step +
+                                               #     integrity-checked parameter all-gather (K9) every step
 
     @classmethod
     def from_kwargs(cls, **kw) -> "TrainingConfig":

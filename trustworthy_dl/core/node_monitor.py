@@ -123,6 +123,15 @@ class HeartbeatMonitor:
         self.offline = np.zeros(self.num_nodes, dtype=bool)
         self.events: List[Dict] = []
 
+    def resize(self, num_nodes: int) -> None:
+        """Track ``num_nodes`` ranks, keeping what is known about the ones that stay."""
+        n, old = int(num_nodes), self.num_nodes
+        keep = min(n, old)
+        last_step = np.full(n, -1, dtype=np.int64); last_step[:keep] = self.last_step[:keep]
+        last_time = np.zeros(n, dtype=np.float64); last_time[:keep] = self.last_time[:keep]
+        offline = np.zeros(n, dtype=bool); offline[:keep] = self.offline[:keep]
+        self.num_nodes, self.last_step, self.last_time, self.offline = n, last_step, last_time, offline
+
     @staticmethod
     def beat(step: int, now: float) -> List[float]:
         """The two numbers a rank contributes to the per-step gather."""
@@ -133,6 +142,8 @@ class HeartbeatMonitor:
         offline after the update."""
         steps = np.asarray(steps, dtype=np.float64)
         times = np.asarray(times, dtype=np.float64)
+        if steps.size != self.num_nodes:
+            self.resize(steps.size)          # strategies adopt the launch's world size after construction
         seen = ~np.isnan(steps)
         self.last_step[seen] = steps[seen].astype(np.int64)
         self.last_time[seen] = times[seen]

@@ -15,7 +15,7 @@ from .trust_manager import TrustManager
 
 __all__ = ["ReassignmentPlanner", "estimate_migration_time", "NVLINK_PEER_BYTES_PER_S"]
 
-NVLINK_PEER_BYTES_PER_S = 770e9           # measured peer copy, B200_PROFILING.md
+NVLINK_PEER_BYTES_PER_S = 770e9           # one-direction peer copy measured with bench/p2p_probe.py on this pool (0.9 TB/s is the link rate)
 REFERENCE_BYTES_PER_S = float(1024 ** 3)    # reference assumption (:360)
 
 

@@ -6,8 +6,9 @@ method of ``TrustManager`` (:44-398).  The design is different on purpose:
 
 * State is held in flat numpy vectors (``value / last_updated / count / decay / recovery /
   status / metrics[n, 6]``), not a dict of dataclasses.  The same layout is mirrored on the
-  GPU by :class:`trustworthy_dl.core.trust_device.DeviceTrustState`, whose float32 trust
-  vector is what the fused trust-weighted all-reduce kernel reads.
+  GPU by the ``trust`` / ``status`` vectors of :class:`trustworthy_dl.parallel.symm.SymmetricTrustReducer`:
+  the float32 trust vector the fused trust-weighted all-reduce reads and ``finalize_trust_kernel``
+  (csrc/trust_allreduce.cu) updates.
 * The clock is injectable.  The reference multiplies the old trust by
   ``exp(-decay_rate * wall_clock_dt)`` (:113-114) which makes decisions timing dependent; the
   default clock here is a logical clock that only advances when the trainer says so.
@@ -46,7 +47,7 @@ class NodeStatus(Enum):
     OFFLINE = "offline"
 
 
-#: integer codes shared with the device-side trust kernel (csrc/trust_update.cu)
+#: integer codes shared with the device-side trust kernel (finalize_trust_kernel in csrc/trust_allreduce.cu)
 STATUS_CODES: Dict[NodeStatus, int] = {
     NodeStatus.TRUSTED: 0, NodeStatus.SUSPICIOUS: 1, NodeStatus.COMPROMISED: 2,
     NodeStatus.RECOVERING: 3, NodeStatus.OFFLINE: 4,

@@ -177,6 +177,9 @@ def trust_weighted_reduce(bucket_per_rank: Sequence[torch.Tensor], weights: torc
     W = g.shape[0]
     if norms is None:
         norms = g.norm(dim=1)
+    # non-finite elements are read as 0 (as in the kernel): a rank shipping NaN/Inf has coefficient 0 through its
+    # non-finite norm, but 0 * NaN would still poison the aggregate and the median
+    g = torch.nan_to_num(g, nan=0.0, posinf=0.0, neginf=0.0)
     med = median_of_ranks(g)
     dots = g @ med
     med2 = (med * med).sum()

@@ -65,10 +65,27 @@ class DataParallelStrategy:
         use_fused = c.engine == "fused" or (c.engine == "auto" and self.device.type == "cuda"
                                             and c.model_name.startswith("gpt2") and c.dtype == "bf16")
         if use_fused:
+            # the fused engine runs AdamW at a constant learning rate over full, 128-aligned batches; anything else
+            # goes through the eager path (with a log line) instead of being silently ignored
+            T = c.seq_len or model.config.n_positions
+            why = [m for ok, m in [(T % 128 == 0, f"seq_len {T} is not a multiple of 128"),
+                                   (str(c.optimizer).lower() == "adamw", f"optimizer {c.optimizer!r} (engine: adamw)"),
+                                   (str(c.lr_schedule).lower() in ("constant", "none", ""), f"lr_schedule {c.lr_schedule!r}"),
+                                   (not c.clip_norm, "clip_norm > 0 (the engine clips per rank inside the aggregation)"),
+                                   (c.batch_size % self.world == 0, "batch_size not divisible by the world size"),
+                                   (model.config.n_embd // model.config.n_head == 64, "head_dim != 64")] if not ok]
+            if why:
+                if c.engine == "fused":
+                    raise ValueError("engine: fused cannot honour this configuration: " + "; ".join(why))
+                logger.info("engine: auto -> eager path (%s)", "; ".join(why))
+                use_fused = False
+        if use_fused:
             from ..engine.gpt2_engine import GPT2Engine
             self.engine = GPT2Engine.from_module(model, batch_size=max(1, c.batch_size // self.world),
                                                  seq_len=c.seq_len or model.config.n_positions,
                                                  lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
+                                                 security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
+                                                 zero=int(getattr(c, "zero", 0) or 0),
                                                  trust_threshold=c.trust_threshold)
             self.reducer = self.engine.reducer
             t.model_partitions[0] = model
@@ -208,7 +225,7 @@ class DataParallelStrategy:
         self._step_s += time.perf_counter() - t0
         t.metrics_collector.collect_batch_metrics({
             "loss": loss, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
-            "step_time": time.perf_counter() - t0, "samples": batch["input"].numel()})
+            "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
         return loss
 
     def _deviation(self, node: int, st) -> float:
@@ -237,6 +254,8 @@ class DataParallelStrategy:
     @torch.no_grad()
     def validate(self, loader) -> float:
         model = self.t.model_partitions[0]
+        if self.engine is not None:
+            self.engine.export_to_module(model)       # the engine trains its own flat buffers: evaluate THOSE weights
         model.eval()
         total, n = 0.0, 0
         for batch in loader:

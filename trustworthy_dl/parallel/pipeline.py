@@ -306,7 +306,10 @@ class PipelineStrategy:
             if self._owner(sid) != self.rank:
                 continue
             opt = t.optimizers[sid]
-            if self.rank in t._last_step_info["invalid_nodes"]:
+            # a rank that failed verification drops its own step ONLY when it is the sole holder of the stage: with
+            # dp > 1 every replica already holds the same trust-weighted aggregate (the coefficients excluded the bad
+            # rank), and skipping the step on one replica would make the stage's copies diverge for good
+            if self.dp == 1 and self.rank in t._last_step_info["invalid_nodes"]:
                 opt.zero_grad(set_to_none=True)
                 continue
             if c.clip_norm > 0:
