@@ -26,7 +26,11 @@ def parse():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=10)
     p.add_argument("--warmup", type=int, default=3)
-    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--impl", default="ours", choices=["ours", "reference", "stock"])
+    p.add_argument("--stock", default="auto", choices=["auto", "skip", "compile"],
+                   help="after our arm, time the stock-library arm (torch eager + SDPA + fused AdamW, DDP for N>1, security "
+                        "off) on the same box and report vs_baseline against it; 'compile' wraps the stock model in torch.compile")
+    p.add_argument("--zero", type=int, default=0, help="1 = ZeRO-1 optimizer sharding + integrity-checked parameter all-gather")
     p.add_argument("--model", default="gpt2-medium")
     p.add_argument("--batch", type=int, default=32, help="sequences per GPU (reference batch_size=32)")
     p.add_argument("--seq-len", type=int, default=1024)
@@ -41,6 +45,60 @@ def reference_unavailable():
            "(node_monitor, gradient_verification, attack_detection, metrics, model_factory)")
     print(json.dumps({"impl": "reference", "unavailable": why}))
     return 0
+
+
+def stock_arm(args, world, rank, local, steps, warmup, compile_model=False):
+    """Reference semantics on stock libraries (baseline A): the repo's plain nn.Module GPT-2 under
+    torch eager + cuBLAS + SDPA + fused torch AdamW (+ NCCL DDP), bf16 autocast, security off.  Same box, same batch."""
+    import torch
+    import torch.distributed as dist
+    from trustworthy_dl.models.gpt2 import GPT2Config, GPT2LMHeadModel, GPT2_PRESETS
+    dev = torch.device("cuda", local)
+    torch.manual_seed(0)
+    cfg = GPT2Config(**GPT2_PRESETS[args.model])
+    model = GPT2LMHeadModel(cfg).to(dev)
+    if compile_model:
+        model = torch.compile(model)
+    if world > 1:
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    opt = torch.optim.AdamW(model.parameters(), lr=5e-5, weight_decay=0.01, fused=True)
+    B, T = args.batch, args.seq_len
+    g = torch.Generator().manual_seed(1234 + rank)
+    data = [(torch.randint(0, cfg.vocab_size, (B, T), generator=g).to(dev), torch.randint(0, cfg.vocab_size, (B, T), generator=g).to(dev))
+            for _ in range(4)]
+
+    def step(i):
+        idx, tgt = data[i % 4]
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            logits = model(idx)
+            loss = torch.nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]), tgt.reshape(-1))
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = step(i)
+    e1.record(); e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    out = {"what": "torch eager + cuBLAS + SDPA + fused torch AdamW" + (" + torch.compile" if compile_model else "") +
+                   (" + NCCL DDP" if world > 1 else "") + ", bf16 autocast, security off, same box, same batch",
+           "value": B * T * world / (ms / steps / 1e3), "unit": "tokens/s", "ms_per_step": ms / steps, "steps": steps,
+           "final_loss": float(loss.item())}
+    del model, opt, data
+    torch.cuda.empty_cache()
+    return out
 
 
 def main() -> int:
@@ -69,9 +127,18 @@ def main() -> int:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
+    if args.impl == "stock":
+        out = stock_arm(args, world, rank, local, args.steps, max(3, args.warmup), compile_model=args.stock == "compile")
+        if rank == 0:
+            print(json.dumps({"impl": "stock", "metric": "gpt2_medium_train_tokens_per_s", "n_gpus": world, **out}))
+        if world > 1:
+            dist.barrier(); dist.destroy_process_group()
+        return 0
+
     cfg = GPT2Config(**GPT2_PRESETS[args.model])
     B, T = args.batch, args.seq_len
-    eng = GPT2Engine(cfg, batch_size=B, seq_len=T, lr=5e-5, device=dev, security=True, use_graph=not args.no_graph)
+    eng = GPT2Engine(cfg, batch_size=B, seq_len=T, lr=5e-5, device=dev, security=True, use_graph=not args.no_graph,
+                     zero=args.zero)
     tokens_per_step = B * T * world
 
     g = torch.Generator().manual_seed(1234 + rank)
@@ -87,8 +154,8 @@ def main() -> int:
             dist.barrier()
 
     def device_step(i):
-        eng.idx.copy_(dev_idx[i % n_batches])
-        eng.tgt.copy_(dev_tgt[i % n_batches])
+        eng.idx[0].copy_(dev_idx[i % n_batches])
+        eng.tgt[0].copy_(dev_tgt[i % n_batches])
         eng.run_step_device()
 
     def timed(step_fn, steps, warmup):
@@ -118,8 +185,8 @@ def main() -> int:
     sampler = ClockSampler(gpu_index=local).start() if rank == 0 else None
     total_ms = timed(device_step, args.steps, warm)
     clocks = sampler.stop() if sampler is not None else {}
-    calls_per_step = getattr(eng, "_calls_per_step", None)
     ms_per_step = total_ms / args.steps
+    kernels_per_step = eng.kernels_per_step()          # counted while this (security-on) step was captured
     value = tokens_per_step / (ms_per_step / 1e3)
 
     # ---- end to end through the public API (H2D of the batch + D2H of the loss every step) --------
@@ -144,14 +211,31 @@ def main() -> int:
         eng.set_security(True)
 
     snap = eng.security_snapshot()
+    n_segments = len(eng.segments)
+    overlap = bool(eng.overlap and n_segments > 1)
+    multimem = bool(eng.reducer.use_multimem)
+    # ---- same-box stock-library arm (the bar BASELINE.md names): run after ours, our buffers released first ----
+    stock = None
+    if args.stock != "skip":
+        del eng, dev_idx, dev_tgt
+        torch.cuda.empty_cache()
+        try:
+            stock = stock_arm(args, world, rank, local, min(args.steps, 10), 3, compile_model=args.stock == "compile")
+        except Exception as e:          # the headline must not die with the comparison arm
+            stock = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0:
-        kernels_per_step = eng.kernels_per_step()
         out = {
             "metric": "gpt2_medium_train_tokens_per_s_trust_detection_on", "value": value, "unit": "tokens/s",
             "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (value / stock["value"]) if stock and "value" in stock else None,
+            "baseline": stock, "dtype": "bf16", "data": "synthetic",
             "config": {"model": args.model, "global_batch": B * world, "seq_len": T, "parallelism": f"dp{world}",
-                       "per_gpu_batch": B, "security": "activation stats + bucket norm/median-cosine + trust update, in-step on device",
+                       "per_gpu_batch": B, "security": "activation stats + per-bucket norm/median-cosine/clip inside the trust-weighted "
+                       "all-reduce + trust update, in-step on device",
+                       "aggregation": f"{n_segments} gradient segments" + (", reduced + AdamW on a side stream under backward" if overlap else ", serial")
+                                      + (", NVLS multimem.st write-back" if multimem else "") + (", ZeRO-1 + checked param all-gather" if args.zero else ""),
+                       "optimizer_input": "fp32 main grads" if world == 1 else "bf16 bucket (aggregated over NVLink), fp32 master weights + moments",
                        "l2_policy": "per-step working set (~30 GB activations+params) far exceeds the 126 MB L2; no explicit flush",
                        "cuda_graph": not args.no_graph},
             "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
@@ -161,6 +245,9 @@ def main() -> int:
             "gpu_launches": kernels_per_step * args.steps,
             "kernels_per_step": kernels_per_step,
             "detection_overhead_pct": overhead,
+            "detection_overhead_vs": ("same engine, security kernels off" if world == 1 else
+                                      "same engine with K4 (plain mean all-reduce over the same symmetric bucket: multimem.ld_reduce/"
+                                      "multimem.st, or P2P when no multicast object) instead of K2, activation statistics and trust update off"),
             "final_loss": losses[-1] if losses else None,
             "trust": [float(x) for x in snap["trust"]],
             "impl": "ours",

@@ -1,11 +1,16 @@
 #!/usr/bin/env python
-"""Where a data-parallel step spends its time: forward / backward / (security + all-reduce + AdamW), device-timed with CUDA
-events around the three engine phases of a non-graph step, max over ranks, plus the individual calls of the last phase.
+"""Where a data-parallel step spends its time, device-timed with CUDA events, max over ranks:
 
-  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/phase_times.py
+* serial schedule (TDL_OVERLAP=0 semantics): forward / backward / per-segment pack+reduce+AdamW, each reduction with
+  its NVLink bytes per direction and the achieved fraction of the 0.9 TB/s link rate;
+* overlapped schedule (the default): whole step, and the exposed tail after the last backward kernel.
+
+  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/phase_times.py [--batch 32]
 """
 from __future__ import annotations
 
+import argparse
+import json
 import os
 import sys
 
@@ -17,20 +22,27 @@ import torch.distributed as dist
 from trustworthy_dl.engine.gpt2_engine import GPT2Engine
 from trustworthy_dl.models.gpt2 import GPT2_PRESETS, GPT2Config
 from trustworthy_dl.ops import nn as K
-from trustworthy_dl.ops.stats import tensor_statistics_device
+
+LINK_BYTES_PER_S = 0.9e12
 
 
 def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--model", default="gpt2-medium")
+    ap.add_argument("--reps", type=int, default=5)
+    args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    cfg = GPT2Config(**GPT2_PRESETS["gpt2-medium"])
-    eng = GPT2Engine(cfg, batch_size=32, seq_len=1024, lr=5e-5, device=dev, security=True, use_graph=False)
+    cfg = GPT2Config(**GPT2_PRESETS[args.model])
+    T = min(1024, cfg.n_positions)
+    eng = GPT2Engine(cfg, batch_size=args.batch, seq_len=T, lr=5e-5, device=dev, security=True, use_graph=False)
     g = torch.Generator().manual_seed(rank)
-    idx = torch.randint(0, cfg.vocab_size, (32, 1024), generator=g).to(dev)
-    eng.idx.copy_(idx); eng.tgt.copy_(idx)
+    idx = torch.randint(0, cfg.vocab_size, (args.batch, T), generator=g).to(dev)
+    eng.idx[0].copy_(idx); eng.tgt[0].copy_(idx)
     for _ in range(3):
         eng._step_body()
     torch.cuda.synchronize()
@@ -39,37 +51,71 @@ def main() -> int:
     def mark(name):
         e = torch.cuda.Event(enable_timing=True); e.record(); names.append(name); evs.append(e)
 
-    acc = {}
-    reps = 5
-    for _ in range(reps):
+    def sync():
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+
+    acc = {}
+    for _ in range(args.reps):
+        sync()
         names.clear(); evs.clear()
         mark("start")
-        eng.loss_sum.zero_(); eng.g32.zero_(); mark("zero")
-        eng._forward(); mark("forward")
-        eng._backward(); mark("backward")
-        r = eng.reducer
-        tensor_statistics_device(eng.res[eng.L].view(-1), out=eng.act_stats); mark("act_stats")
-        K.pack_norm(eng.g32, eng.bucket, r.sumsq, eng.attack_scale); mark("pack_norm")
-        r.enqueue_reduce(update_trust=True); mark("trust_allreduce")
-        K.adam_tick(eng.hyper, eng.lr, eng.betas[0], eng.betas[1])
-        K.adamw(eng.p32, eng.p16, eng.bucket, eng.m, eng.v, eng.n_decay, eng.lr, eng.betas[0], eng.betas[1], eng.eps, eng.wd, 1,
-                hyper=eng.hyper); mark("adamw")
+        eng.begin_step(); mark("zero+tick")
+        eng._forward(0); mark("forward")
+        eng._backward(0, 0); mark("backward")
+        for i, seg in enumerate(eng.segments):
+            eng._reduce_segment(i, overlapped=False); mark(f"seg{i} pack+reduce+adamw [{seg.name}, {seg.n * 2 / 1e6:.0f} MB bf16]")
+        eng.reduce_and_update(overlapped_already=True); mark("finalize")
         torch.cuda.synchronize()
         for i in range(1, len(evs)):
             acc.setdefault(names[i], []).append(evs[i - 1].elapsed_time(evs[i]))
-    out = torch.tensor([sum(v) / len(v) for v in acc.values()], dtype=torch.float64, device=dev)
-    lo = out.clone()
+    # reduction alone (K2 only) per segment
+    red = {}
+    if world > 1:
+        r = eng.reducer
+        for i, seg in enumerate(eng.segments):
+            ts = []
+            for _ in range(args.reps):
+                K.pack_norm(eng.g32[seg.off:seg.off + seg.n], eng.bucket[seg.off:seg.off + seg.n], r.sumsq, eng.attack_scale)
+                sync()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); r.enqueue_bucket(seg.off, seg.n); e1.record(); torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            red[i] = min(ts)
+        r.enqueue_finalize(update_trust=False)
+    # overlapped schedule: whole step
+    whole = []
+    for _ in range(args.reps):
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); eng._step_body(); e1.record(); torch.cuda.synchronize()
+        whole.append(e0.elapsed_time(e1))
+    keys = list(acc.keys())
+    vals = [sum(v) / len(v) for v in acc.values()] + [red.get(i, 0.0) for i in range(len(eng.segments))] + [sum(whole) / len(whole)]
+    out = torch.tensor(vals, dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(out, op=dist.ReduceOp.MAX)
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    out = out.tolist()
     if rank == 0:
-        print(f"world {world}: phase = max over ranks (min over ranks) in ms, eager launches")
-        for n, hi, l in zip(acc.keys(), out.tolist(), lo.tolist()):
-            print(f"  {n:16s} {hi:8.3f} ({l:8.3f})")
-        print(f"  {'total':16s} {sum(out.tolist()):8.3f}")
+        nk = len(keys)
+        serial = sum(out[:nk])
+        print(f"world {world}, {args.model}, batch {args.batch} x {T}: ms, max over ranks, eager launches")
+        for n, v in zip(keys, out[:nk]):
+            print(f"  {n:64s} {v:8.3f}")
+        print(f"  {'serial total':64s} {serial:8.3f}")
+        print(f"  {'overlapped schedule, whole step':64s} {out[-1]:8.3f}   (hidden: {serial - out[-1]:.3f} ms)")
+        if world > 1:
+            print("  trust-weighted reduction alone (exchange + coefficients + K2 + barrier), NVLink bytes per direction:")
+            tot_b, tot_t = 0.0, 0.0
+            for i, seg in enumerate(eng.segments):
+                b = seg.n * 2 * (world - 1) / world
+                t = out[nk + i] / 1e3
+                tot_b += b; tot_t += t
+                print(f"    seg{i}: {b / 1e6:8.1f} MB in {t * 1e3:7.3f} ms = {b / t / 1e9:6.1f} GB/s = {b / t / LINK_BYTES_PER_S:.2f} of link rate")
+            print(f"    all : {tot_b / 1e6:8.1f} MB in {tot_t * 1e3:7.3f} ms = {tot_b / tot_t / 1e9:6.1f} GB/s = {tot_b / tot_t / LINK_BYTES_PER_S:.2f} of link rate")
+        print(json.dumps({"world": world, "serial_ms": serial, "overlapped_ms": out[-1],
+                          "phases": dict(zip(keys, out[:nk])), "reduce_ms": out[nk:nk + len(eng.segments)]}))
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
     return 0

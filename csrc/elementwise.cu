@@ -760,6 +760,31 @@ __global__ void __launch_bounds__(256) reduce_slots_kernel(const __nv_bfloat16* 
     }
 }
 
+// reduce-scatter epilogue of a row-parallel linear: out[r, c] = sum_slots staging[s][r][c] + bias[c] + residual[r, c]
+__global__ void __launch_bounds__(256) reduce_slots_bias_kernel(const __nv_bfloat16* __restrict__ staging, int W, long long slot_elems,
+        int cols, const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ out) {
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < slot_elems; i += (long long)gridDim.x * blockDim.x * 8) {
+        float acc[8];
+        if (residual != nullptr) bf16x8_to_f32(*reinterpret_cast<const uint4*>(residual + i), acc);
+        else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        }
+        if (bias != nullptr) {
+            const int c = (int)(i % cols);
+            const float4 b0 = *reinterpret_cast<const float4*>(bias + c), b1 = *reinterpret_cast<const float4*>(bias + c + 4);
+            acc[0] += b0.x; acc[1] += b0.y; acc[2] += b0.z; acc[3] += b0.w; acc[4] += b1.x; acc[5] += b1.y; acc[6] += b1.z; acc[7] += b1.w;
+        }
+        for (int s2 = 0; s2 < W; ++s2) {
+            float f[8];
+            bf16x8_to_f32(ld_nc_v4(staging + s2 * slot_elems + i), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+        *reinterpret_cast<uint4*>(out + i) = f32_to_bf16x8(acc);
+    }
+}
+
 inline int grid_for(long long n, int per_block) {
     long long b = (n + per_block - 1) / per_block;
     const long long cap = (long long)tdl_num_sms() * 8;
@@ -980,6 +1005,17 @@ extern "C" int tdl_reduce_slots(const void* staging, int W, int64_t slot_elems, 
     TDL_REQUIRE(slot_elems % 8 == 0, "slot size must be a multiple of 8 elements");
     reduce_slots_kernel<<<grid_for(slot_elems, 256 * 8 * 2), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)staging, W, slot_elems,
                                                                                     (const __nv_bfloat16*)residual, (__nv_bfloat16*)out);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+// as tdl_reduce_slots for a [rows, cols] slot, plus the (replicated, fp32) bias of the row-parallel layer
+extern "C" int tdl_reduce_slots_bias(const void* staging, int W, int64_t rows, int64_t cols, const float* bias, const void* residual,
+                                     void* out, void* stream) {
+    TDL_REQUIRE(cols % 8 == 0, "columns must be a multiple of 8");
+    const long long n = rows * cols;
+    reduce_slots_bias_kernel<<<grid_for(n, 256 * 8 * 2), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)staging, W, n, (int)cols, bias,
+                                                                                (const __nv_bfloat16*)residual, (__nv_bfloat16*)out);
     TDL_LAUNCH_CHECK();
     return 0;
 }

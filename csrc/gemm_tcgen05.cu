@@ -424,7 +424,8 @@ __device__ __forceinline__ void tile_mn(int t, int n_blocks, int m_blocks, int g
 template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid_constant__ CUtensorMap tmap_b,
-                              const __grid_constant__ EpiMaps emaps, const __grid_constant__ GemmParams p) {
+                              const __grid_constant__ EpiMaps emaps, const __grid_constant__ TmapArray cmaps,
+                              const __grid_constant__ GemmParams p) {
     using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     const CUtensorMap& tmap_a = tmaps_a.m[0];
     extern __shared__ uint8_t smem_raw[];
@@ -567,7 +568,9 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
         const int quarter = warp & 3;
         const int half = e >> 2;
         constexpr int NC = BLOCK_N / 64;
-        const bool staged = !p.out_f32_atomic && !p.c_scatter;          // coalesced path: smem panels + TMA
+        // coalesced path: smem panels + TMA stores.  c_scatter == 2 (K7): the finished panel of a 128-row tile is stored by
+        // TMA straight into the OWNER rank's staging slot over NVLink (one tensor map per owner in `cmaps`)
+        const bool staged = !p.out_f32_atomic && p.c_scatter != 1;
         const bool aux_in = AUX && (p.epilogue == EPI_RESIDUAL || p.epilogue == EPI_DGELU || p.epilogue == EPI_MUL);
         const bool aux_out = AUX && (p.epilogue == EPI_GELU || p.epilogue == EPI_GELU_DG);
         uint8_t* out_panel = staging + half * (AUX ? 2 : 1) * PANEL_BYTES;
@@ -730,7 +733,12 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                         if (group_leader) {
                             const int pc = n_idx + pi * 64;
                             if (pc < p.N) {
-                                tma_store_2d(&emaps.c, out_panel, pc, m_idx);
+                                if (p.c_scatter) {
+                                    const int owner = m_idx / p.c_shard_rows;
+                                    tma_store_2d(&cmaps.m[owner], out_panel, pc, p.c_src_slot * p.c_shard_rows + (m_idx - owner * p.c_shard_rows));
+                                } else {
+                                    tma_store_2d(&emaps.c, out_panel, pc, m_idx);
+                                }
                                 if (aux_out) tma_store_2d(&emaps.aux, aux_panel, pc, m_idx);
                             }
                             tma_store_commit();
@@ -854,7 +862,8 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
 }
 
 template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
-static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const EpiMaps& em, GemmParams& p, cudaStream_t stream) {
+static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const EpiMaps& em, const TmapArray& cm, GemmParams& p,
+                            cudaStream_t stream) {
     using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     static bool configured = false;
     if (!configured) {
@@ -867,7 +876,7 @@ static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const Ep
     const int max_clusters = tdl_num_sms() / 2;
     const int clusters = work < max_clusters ? work : max_clusters;
     TDL_CHECK(tdl_launch_pdl(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM>, dim3(2 * clusters), dim3(NUM_THREADS),
-                             C::SMEM_BYTES, stream, ta, tb, em, p));
+                             C::SMEM_BYTES, stream, ta, tb, em, cm, p));
     TDL_LAUNCH_CHECK();
     return 0;
 }
@@ -951,9 +960,22 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         if (raster < 0) { const char* e = getenv("TDL_GEMM_RASTER"); raster = e ? atoi(e) : 16; }
         if (p.n_blocks >= 32 && p.split_k == 1 && p.m_block_offset == 0) p.raster_group = raster;
         EpiMaps em;
-        const bool staged = !out_f32_atomic && !c_scatter;
+        TmapArray cm = ta;                               // only read when c_scatter == 2
+        // K7 through TMA stores needs every 128-row tile to belong to one owner; otherwise per-thread peer stores
+        static int scatter_tma = -1;
+        if (scatter_tma < 0) { const char* e = getenv("TDL_SCATTER_TMA"); scatter_tma = e ? atoi(e) : 1; }
+        if (c_scatter && scatter_tma && c_shard_rows % BLOCK_M == 0 && M % BLOCK_M == 0) {
+            p.c_scatter = 2;
+            const int owners = (int)(M / c_shard_rows);
+            for (int i = 0; i < owners && !rc; ++i)
+                rc = tdl_make_tmap_2d_bf16(&cm.m[i], c_ptrs[i], (uint64_t)N, (uint64_t)(owners * c_shard_rows), (uint64_t)ldc, 64, 128);
+            if (rc) return rc;
+        }
+        const bool staged = !out_f32_atomic && p.c_scatter != 1;
         const bool needs_aux = epilogue != EPI_NONE;
-        if (staged) {
+        if (staged && p.c_scatter == 2) {
+            em.c = tb; em.aux = tb;
+        } else if (staged) {
             rc = tdl_make_tmap_2d_bf16(&em.c, Cout, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 128);
             if (rc) return rc;
             const void* auxp = (epilogue == EPI_GELU || epilogue == EPI_GELU_DG) ? aux_out : aux_in;
@@ -965,11 +987,11 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         const bool fuse_colsum = colsum != nullptr && staged && (reinterpret_cast<uintptr_t>(colsum) & 15) == 0;
         if (fuse_colsum) p.colsum = colsum;             // column sums leave from the staged epilogue panels
         if (fuse_colsum)
-            rc = needs_aux ? launch_gemm_2cta<256, 5, true, true>(ta, tb, em, p, s)
-                           : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, p, s);
+            rc = needs_aux ? launch_gemm_2cta<256, 5, true, true>(ta, tb, em, cm, p, s)
+                           : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, cm, p, s);
         else
-            rc = (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, p, s)
-                                       : launch_gemm_2cta<256, 6, false>(ta, tb, em, p, s);
+            rc = (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, cm, p, s)
+                                       : launch_gemm_2cta<256, 6, false>(ta, tb, em, cm, p, s);
         if (!rc && colsum != nullptr && !fuse_colsum) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
         return rc;
     }
@@ -1013,6 +1035,18 @@ extern "C" int tdl_allgather_gemm_bf16(const void* const* a_shard_ptrs, int W, i
     const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
     return gemm_common(a_shard_ptrs, W, shard_rows, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, 0, bias,
                        bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, nullptr, stream);
+}
+
+// K8 with the operand layouts of the backward pass: B may be stored [K, N] (dgrad of a row-parallel layer reads the
+// weight MN-major) and the column sums of the bf16 output (a bias gradient) can leave from the epilogue panels.
+extern "C" int tdl_allgather_gemm_bf16_ex(const void* const* a_shard_ptrs, int W, int my_rank, int64_t shard_rows, const void* B,
+                                          void* Cout, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major,
+                                          const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
+                                          int64_t ld_aux, int block_n, float* colsum, void* stream) {
+    const int64_t M = shard_rows * W;
+    const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
+    return gemm_common(a_shard_ptrs, W, shard_rows, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, b_mn_major, bias,
+                       bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, colsum, stream);
 }
 
 // K7: GEMM -> reduce-scatter (first half).  The partial product tile for rows owned by rank o is stored from

@@ -60,6 +60,14 @@ int tdl_gemm_scatter_bf16(const void* A, const void* B, void* const* c_ptrs, int
                           int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major, int block_n,
                           void* stream);
 int tdl_reduce_slots(const void* staging, int W, int64_t slot_elems, const void* residual, void* out, void* stream);
+/* as above for a [rows, cols] slot, adding the row-parallel layer's replicated fp32 bias[cols] */
+int tdl_reduce_slots_bias(const void* staging, int W, int64_t rows, int64_t cols, const float* bias, const void* residual,
+                          void* out, void* stream);
+/* K8 with backward-pass layouts: B may be MN-major ([K, N]); colsum (fp32 [N], may be NULL) += column sums of the output */
+int tdl_allgather_gemm_bf16_ex(const void* const* a_shard_ptrs, int W, int my_rank, int64_t shard_rows, const void* B, void* C,
+                               int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major, const void* bias,
+                               int bias_f32, int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux, int block_n,
+                               float* colsum, void* stream);
 
 /* ---- K12: causal attention, head_dim 64 (ATen/HF attention under :160-161) -------------------- */
 int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t B, int64_t T, int64_t H, int64_t Dh, void* stream);

@@ -494,10 +494,10 @@ class GPT2Engine:
         _lib.call("tdl_exchange", r._pad_ptrs, i32(r.rank), i32(W), i32(1), ptr(self.pg_own), i32(2), ptr(r.epochs), i32(0),
                   stream_ptr())
         _lib.call("tdl_exchange_read", r._my_pad, i32(W), i32(1), i32(2), ptr(self.pg_pub[i]), stream_ptr())
-        shard_ptrs = self.p16_sym.ptr_array(r.ranks if self.p16_sym.world > 1 else [0], seg.off)
-        # peer k's slice sits at offset k*per of the segment on peer k: advance each pointer by its own slice offset
+        # peer k's freshly updated slice sits at offset k*per of the segment in peer k's copy of the bf16 parameters
         import ctypes
-        arr = (ctypes.c_void_p * W)(*[int(shard_ptrs[k]) + k * per * 2 for k in range(W)])
+        peers = r.ranks if self.p16_sym.world > 1 else [0] * W
+        arr = (ctypes.c_void_p * W)(*[self.p16_sym.peer_ptrs[peers[k]] + (seg.off + k * per) * 2 for k in range(W)])
         _lib.call("tdl_param_gather", arr, i32(W), i32(1), ptr(self.p16[seg.off:seg.off + seg.n]),
                   ptr(self.p16_prev[seg.off:seg.off + seg.n]), i64(per), ptr(self.pg_sums[i]), ptr(self.pg_drift[i]),
                   stream_ptr())

@@ -25,13 +25,19 @@ def _arr(ptrs: List[int]):
 
 
 def allgather_gemm(a_shard_ptrs: List[int], rank: int, shard_rows: int, w: torch.Tensor, out: torch.Tensor, *,
-                   bias: Optional[torch.Tensor] = None, epilogue: int = 0, aux_in=None, aux_out=None, block_n: int = 0):
+                   bias: Optional[torch.Tensor] = None, epilogue: int = 0, aux_in=None, aux_out=None, block_n: int = 0,
+                   b_mn: bool = False, colsum: Optional[torch.Tensor] = None):
+    """out [W*shard_rows, N] = AG(a shards) @ w^T (``w`` [N, K]) or @ w (``b_mn``: ``w`` [K, N], the dgrad of a row-parallel
+    layer); ``colsum`` (fp32 [N]) += column sums of the bf16 output."""
     W = len(a_shard_ptrs)
-    N, K = w.shape
+    if b_mn:
+        K, N = w.shape
+    else:
+        N, K = w.shape
     bias_f32 = 1 if (bias is not None and bias.dtype == torch.float32) else 0
-    _lib.call("tdl_allgather_gemm_bf16", _arr(a_shard_ptrs), i32(W), i32(rank), i64(shard_rows), ptr(w), ptr(out), i64(N), i64(K),
-              i64(K), i64(K), i64(N), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in), ptr(aux_out), i64(N), i32(block_n),
-              stream_ptr())
+    _lib.call("tdl_allgather_gemm_bf16_ex", _arr(a_shard_ptrs), i32(W), i32(rank), i64(shard_rows), ptr(w), ptr(out), i64(N), i64(K),
+              i64(K), i64(w.shape[1]), i64(N), i32(b_mn), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in), ptr(aux_out), i64(N),
+              i32(block_n), ptr(colsum), stream_ptr())
 
 
 def gemm_scatter(a: torch.Tensor, w: torch.Tensor, staging_ptrs: List[int], rank: int, shard_rows: int, *,
@@ -45,5 +51,26 @@ def gemm_scatter(a: torch.Tensor, w: torch.Tensor, staging_ptrs: List[int], rank
               i64(K), i64(w.shape[1]), i64(N), i32(b_mn), i32(block_n), stream_ptr())
 
 
-def reduce_slots(staging: torch.Tensor, W: int, out: torch.Tensor, residual: Optional[torch.Tensor] = None):
-    _lib.call("tdl_reduce_slots", ptr(staging), i32(W), i64(out.numel()), ptr(residual), ptr(out), stream_ptr())
+def reduce_slots(staging: torch.Tensor, W: int, out: torch.Tensor, residual: Optional[torch.Tensor] = None,
+                 bias: Optional[torch.Tensor] = None):
+    """out [rows, cols] = sum of the W staged partial slots (+ fp32 bias[cols]) (+ residual)."""
+    if bias is None:
+        _lib.call("tdl_reduce_slots", ptr(staging), i32(W), i64(out.numel()), ptr(residual), ptr(out), stream_ptr())
+    else:
+        rows, cols = out.shape
+        _lib.call("tdl_reduce_slots_bias", ptr(staging), i32(W), i64(rows), i64(cols), ptr(bias), ptr(residual), ptr(out),
+                  stream_ptr())
+
+
+_gather_dummy = {}
+
+
+def gather_rows(shard_ptrs: List[int], shard_elems: int, dst: torch.Tensor):
+    """dst [W * shard_elems] <- the W peer shards (plain P2P pull with the K9 kernel, integrity outputs discarded)."""
+    W = len(shard_ptrs)
+    key = dst.device.index
+    if key not in _gather_dummy:
+        _gather_dummy[key] = (torch.zeros(16, dtype=torch.int64, device=dst.device), torch.zeros(8, dtype=torch.float64, device=dst.device))
+    sums, drift = _gather_dummy[key]
+    _lib.call("tdl_param_gather", _arr(shard_ptrs), i32(W), i32(_lib.DTYPE_CODES[dst.dtype]), ptr(dst), None, i64(shard_elems),
+              ptr(sums), ptr(drift), stream_ptr())
