@@ -260,3 +260,33 @@ def test_conv_epilogue(dev, channels_last):
     xb = torch.randn(2, 8, 4, 4, device=dev).bfloat16()
     b = torch.randn(8, device=dev)
     assert torch.allclose(fused_bias_relu(xb, b).float(), torch.relu(xb.float() + b.view(1, -1, 1, 1)), atol=2e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_resnet_bnact_matches_batchnorm_add_relu(dev, dtype):
+    """Training-mode BatchNorm + residual + ReLU through the K13 epilogue (models/resnet.py:BNAct) against the stock
+    three-op sequence: outputs, input / residual / affine gradients and running statistics."""
+    from trustworthy_dl.models.resnet import BNAct
+    torch.manual_seed(0)
+    ours, ref = BNAct(32).to(dev), torch.nn.BatchNorm2d(32).to(dev)
+    with torch.no_grad():
+        ours.weight.uniform_(0.5, 1.5); ours.bias.normal_()
+    ref.load_state_dict(ours.state_dict())
+    x = (torch.randn(8, 32, 14, 14, device=dev) * 2 + 0.5).to(dtype)
+    r = torch.randn(8, 32, 14, 14, device=dev).to(dtype)
+    x1, r1 = x.clone().requires_grad_(True), r.clone().requires_grad_(True)
+    x2, r2 = x.float().clone().requires_grad_(True), r.float().clone().requires_grad_(True)
+    y = ours(x1, residual=r1, relu=True)
+    y_ref = torch.relu(ref(x2) + r2)
+    tol = 1e-4 if dtype == torch.float32 else 3e-2
+    assert torch.allclose(y.float(), y_ref, atol=tol, rtol=tol)
+    g = torch.randn_like(y_ref)
+    y.backward(g.to(dtype)); y_ref.backward(g)
+    gt = 2e-3 if dtype == torch.float32 else 6e-2
+    assert torch.allclose(x1.grad.float(), x2.grad, atol=gt, rtol=gt), (x1.grad.float() - x2.grad).abs().max().item()
+    assert torch.allclose(r1.grad.float(), r2.grad, atol=gt, rtol=gt)
+    assert torch.allclose(ours.weight.grad, ref.weight.grad, atol=gt * 30, rtol=gt)
+    assert torch.allclose(ours.bias.grad, ref.bias.grad, atol=gt * 30, rtol=gt)
+    assert torch.allclose(ours.running_mean, ref.running_mean, atol=1e-2) and torch.allclose(ours.running_var, ref.running_var, rtol=2e-2)
+    ours.eval(); ref.eval()
+    assert torch.allclose(ours(x, relu=False).float(), ref(x.float()), atol=tol * 2, rtol=tol * 2)

@@ -204,3 +204,209 @@ def test_pipeline_over_nccl_with_reassignment():
     assert all(r["losses"] == pytest.approx(res[0]["losses"], rel=1e-4) for r in res)
     assert res[0]["attacks"] == [(1, 10)] and res[0]["reassign"][0][0] == 1 and res[0]["reassign"][0][2] == 10
     assert 1 not in res[0]["owner"] and len(res[0]["losses"]) == 14
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# round 2: K4, non-finite ranks, bucketed / ZeRO-1 engine, tensor-parallel engine, fused pipeline stages
+# ------------------------------------------------------------------------------------------------------------------
+def _k4_worker(rank, world):
+    """Plain mean all-reduce (K4) through the switch (multimem) and over P2P, and K2's multimem write-back."""
+    from trustworthy_dl.parallel.symm import SymmetricTrustReducer
+    dev = torch.device("cuda", rank)
+    N = 8 * world * 4096
+    out = {}
+    for mode in ("multimem", "p2p"):
+        os.environ["TDL_TR_MULTIMEM"] = "1" if mode == "multimem" else "0"
+        red = SymmetricTrustReducer(N, torch.bfloat16, dev)
+        out[mode + "_used"] = bool(red.use_multimem)
+        g = torch.Generator().manual_seed(7)
+        alls = [torch.randn(N, generator=g).bfloat16() for _ in range(world)]
+        red.buffer.copy_(alls[rank].to(dev))
+        red.enqueue_sum_allreduce()
+        torch.cuda.synchronize()
+        ref = torch.stack([a.float() for a in alls]).mean(0)
+        out[mode + "_err"] = (red.buffer.float().cpu() - ref).abs().max().item()
+        # K2 with the same write-back mode
+        red.buffer.copy_(alls[rank].to(dev))
+        red.enqueue_local_norm()
+        red.enqueue_reduce(update_trust=False)
+        torch.cuda.synchronize()
+        out[mode + "_k2_err"] = (red.buffer.float().cpu() - ref).abs().max().item()
+    return out
+
+
+def test_k4_sum_allreduce_and_multimem_writeback():
+    world = torch.cuda.device_count()
+    res = _run(_k4_worker, world)
+    for r in res:
+        assert r["p2p_used"] is False
+        for k in ("multimem_err", "p2p_err", "multimem_k2_err", "p2p_k2_err"):
+            assert r[k] < 0.05, (k, r)
+
+
+def _nan_worker(rank, world):
+    """One rank ships NaN / Inf gradients: the aggregate stays finite, that rank gets coefficient 0 and is flagged."""
+    from trustworthy_dl.ops import reference_impl as R
+    from trustworthy_dl.parallel.symm import SymmetricTrustReducer
+    dev = torch.device("cuda", rank)
+    N = 8 * world * 2048
+    red = SymmetricTrustReducer(N, torch.bfloat16, dev)
+    g = torch.Generator().manual_seed(11)
+    base = torch.randn(N, generator=g)
+    alls = [(base + 0.3 * torch.randn(N, generator=g)).bfloat16() for _ in range(world)]
+    bad = world - 1
+    alls[bad][::7] = float("nan")
+    alls[bad][3::11] = float("inf")
+    red.buffer.copy_(alls[rank].to(dev))
+    red.enqueue_local_norm()
+    red.enqueue_reduce(update_trust=True)
+    torch.cuda.synchronize()
+    norms = torch.stack([a.float().norm() for a in alls])
+    coeff = R.robust_coefficients(norms, torch.full((world,), 1.0 / world))
+    ref, _ = R.trust_weighted_reduce([a.float() for a in alls], coeff, 0.0, norms)
+    got = red.buffer.float().cpu()
+    return {"finite": bool(torch.isfinite(got).all()), "err": (got - ref).abs().max().item(), "coeff": red.coeff.cpu().tolist(),
+            "flags": red.flags.cpu().tolist(), "ref_finite": bool(torch.isfinite(ref).all())}
+
+
+def test_non_finite_rank_cannot_poison_the_aggregate():
+    world = torch.cuda.device_count()
+    for r in _run(_nan_worker, world):
+        assert r["finite"] and r["ref_finite"] and r["err"] < 0.13, r
+        assert r["coeff"][-1] == 0.0 and r["flags"][-1] != 0 and all(f == 0 for f in r["flags"][:-1])
+
+
+def _zero_worker(rank, world):
+    """ZeRO-1 (sharded optimizer step + integrity-checked parameter all-gather) against the replicated step, then one
+    rank corrupts the shard it publishes."""
+    from trustworthy_dl.engine.gpt2_engine import GPT2Engine
+    from trustworthy_dl.models.gpt2 import GPT2Config
+    dev = torch.device("cuda", rank)
+    cfg = GPT2Config(vocab_size=1000, padded_vocab_size=1024, n_positions=128, n_embd=128, n_layer=2, n_head=2)
+    g = torch.Generator().manual_seed(rank)
+    idx = torch.randint(0, 1000, (2, 128), generator=g)
+    out = {}
+    for zero in (0, 1):
+        eng = GPT2Engine(cfg, batch_size=2, seq_len=128, lr=1e-3, device=dev, use_graph=True, security=True, zero=zero, n_buckets=2)
+        losses = [eng.train_step(idx, idx.roll(-1, 1)) for _ in range(6)]
+        torch.cuda.synchronize()
+        out[f"loss{zero}"] = losses
+        out[f"p16sum{zero}"] = float(eng.p16.double().sum().item())
+        if zero:
+            snap = eng.security_snapshot()
+            out["clean_flags"] = snap["param_flags"].tolist()
+            out["clean_drift"] = snap["param_drift"].tolist()
+            if rank == 1:
+                eng.param_attack.fill_(0.05)                        # rank 1 publishes a corrupted shard from now on
+            eng.train_step(idx, idx.roll(-1, 1))
+            torch.cuda.synchronize()
+            out["attack_flags"] = eng.security_snapshot()["param_flags"].tolist()
+    return out
+
+
+def test_zero1_matches_replicated_step_and_flags_poisoned_shard():
+    world = torch.cuda.device_count()
+    if world & (world - 1):
+        pytest.skip("ZeRO-1 slices need a power-of-two world")
+    res = _run(_zero_worker, world)
+    for r in res:
+        assert r["loss1"] == pytest.approx(r["loss0"], rel=2e-3)
+        assert r["p16sum1"] == pytest.approx(r["p16sum0"], rel=1e-4, abs=0.5)
+        assert r["clean_flags"] == [0] * world and all(d > 0 for d in r["clean_drift"])
+    assert len({round(r["p16sum1"], 3) for r in res}) == 1                  # every rank holds the same gathered parameters
+    for rank, r in enumerate(res):
+        want = [0] * world
+        if rank != 1:
+            want[1] = 1                                                     # everyone but the culprit sees its shard mismatch
+        assert r["attack_flags"] == want, (rank, r["attack_flags"])
+
+
+def _tp_engine_worker(rank, world):
+    from trustworthy_dl.engine.gpt2_engine import GPT2Engine
+    from trustworthy_dl.engine.gpt2_tp_engine import GPT2TPEngine
+    from trustworthy_dl.models.gpt2 import GPT2Config
+    dev = torch.device("cuda", rank)
+    heads = max(4, world)
+    cfg = GPT2Config(vocab_size=1000, padded_vocab_size=1024, n_positions=256, n_embd=64 * heads, n_layer=2, n_head=heads)
+    B, T = 2 * world, 256
+    g = torch.Generator().manual_seed(3)
+    idx = torch.randint(0, 1000, (B, T), generator=g)
+    tgt = torch.randint(0, 1000, (B, T), generator=g)
+    tp = GPT2TPEngine(cfg, batch_size=B, seq_len=T, lr=1e-3, device=dev, use_graph=True, security=True, seed=5)
+    parts = [tp.train_step(idx, tgt) for _ in range(6)]
+    lt = torch.tensor(parts, dtype=torch.float64, device=dev)
+    import torch.distributed as dist
+    dist.all_reduce(lt)
+    out = {"tp": lt.cpu().tolist(), "coeff": tp.security_snapshot()["coeff"].tolist(), "calls": tp.kernels_per_step()}
+    # poisoned replicated gradients on the last rank
+    tp.train_step(idx, tgt, attack_scale=25.0 if rank == world - 1 else 1.0)
+    snap = tp.security_snapshot()
+    out["flags"], out["trust"] = snap["flags"].tolist(), snap["trust"].tolist()
+    if rank == 0:
+        # the unsharded model on one GPU, same seed, same data (its aggregation group is this rank alone)
+        ref = GPT2Engine(cfg, batch_size=B, seq_len=T, lr=1e-3, device=dev, use_graph=False, security=False, seed=5,
+                         dp_ranks=[0], overlap=False)
+        out["ref"] = [ref.train_step(idx, tgt) for _ in range(6)]
+    dist.barrier()
+    return out
+
+
+def test_tensor_parallel_engine_matches_unsharded_engine():
+    """Runs at 2, 4 and 8 ranks (K7 / K8 / local-head attention / sequence-parallel LayerNorm on our kernels)."""
+    world = torch.cuda.device_count()
+    res = _run(_tp_engine_worker, world)
+    assert res[0]["tp"] == pytest.approx(res[0]["ref"], rel=2e-2), (res[0]["tp"], res[0]["ref"])
+    assert res[0]["tp"][-1] < res[0]["tp"][0]
+    assert res[0]["coeff"] == pytest.approx([1.0 / world] * world, abs=0.05)
+    for r in res:
+        assert r["flags"][-1] != 0 and all(f == 0 for f in r["flags"][:-1]) and r["trust"][-1] < 0.2 < r["trust"][0]
+
+
+def _pp_fused_worker(rank, world):
+    """GPT-2 stages on the stage engine: PP x DP over NCCL p2p + K2, a rank compromised mid-run, its stage (parameters AND
+    Adam state) migrated to a peer of the same replica, training continues."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    dp = 2 if world >= 4 else 1
+    att = None
+    target = world - 1 if dp == 1 else 1
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[target], intensity=0.5, start_step=12,
+                                           end_step=13))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=8 * dp, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, parallelism="pipeline", pp_size=world // dp, dp_size=dp, micro_batches=4,
+                         dtype="bf16", seq_len=128, optimizer="adamw", migration_model="nvlink",
+                         model_kwargs={"n_positions": 128, "n_embd": 128, "n_head": 2, "n_layer": 4, "vocab_size": 512,
+                                       "padded_vocab_size": 512})
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 8 * dp, num_batches=20, seq_len=128)]
+    impl = t._backend_impl
+    val = impl.validate(get_dataloader("tiny-tokens", "validation", 8 * dp, num_batches=2, seq_len=128))
+    return {"losses": losses, "fused": type(impl).__name__, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history],
+            "reassign": [(r["from_node"], r["to_node"], r["step"]) for r in t.reassignment_history],
+            "owner": list(t.stage_map.owner), "stages": sorted(impl.engines), "val": val,
+            "psum": {sid: float(e.p32.double().sum().item()) for sid, e in impl.engines.items()},
+            "msum": {sid: float(e.m.double().abs().sum().item()) for sid, e in impl.engines.items()}}
+
+
+def test_fused_pipeline_stages_with_reassignment():
+    world = torch.cuda.device_count()
+    res = _run(_pp_fused_worker, world)
+    assert all(r["fused"] == "FusedPipelineStrategy" for r in res)
+    assert all(r["losses"] == pytest.approx(res[0]["losses"], rel=1e-6) for r in res)        # replicated decisions / loss
+    L = res[0]["losses"]
+    assert L[11] < L[0] - 0.3, L                                                              # it learns
+    dp = 2 if world >= 4 else 1
+    target = world - 1 if dp == 1 else 1
+    assert res[0]["attacks"] and res[0]["attacks"][0] == (target, 12), res[0]["attacks"]
+    assert res[0]["reassign"] and res[0]["reassign"][0][0] == target and target not in res[0]["owner"]
+    assert max(L[13:]) < L[11] + 0.35, L                                                      # no bump beyond the poisoned step
+    assert all(v > 0 for r in res for v in r["msum"].values())                               # Adam moments travelled with the stage
+    if dp > 1:                                                                                # replicas of a stage hold the same weights
+        S = world // dp
+        owner = res[0]["owner"]
+        for s in range(S):
+            a, b = owner[s], owner[S + s]
+            assert res[a]["psum"][s] == pytest.approx(res[b]["psum"][s], rel=1e-6)
+    assert res[0]["val"] == pytest.approx(res[-1]["val"], rel=1e-6) and res[0]["val"] < L[0]

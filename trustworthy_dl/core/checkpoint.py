@@ -26,6 +26,9 @@ def save_checkpoint(trainer, directory: Optional[str] = None, rank: Optional[int
     engine = getattr(getattr(trainer, "_backend_impl", None), "engine", None)
     if engine is not None:                       # fused path: weights live in the engine's flat buffers
         engine.export_to_module(trainer.model_partitions[0])
+    impl = getattr(trainer, "_backend_impl", None)
+    if hasattr(impl, "export_to_model"):         # fused pipeline stages: same, one engine per hosted stage
+        impl.export_to_model()
     ckpt: Dict[str, Any] = {
         # ---- reference schema ----
         "epoch": trainer.current_epoch,
@@ -50,6 +53,8 @@ def save_checkpoint(trainer, directory: Optional[str] = None, rank: Optional[int
     }
     if engine is not None:
         ckpt["engine"] = {k: v.cpu() for k, v in engine.state_dict().items()}
+    if hasattr(impl, "checkpoint_state"):
+        ckpt["strategy"] = impl.checkpoint_state()
     path = _path(directory, trainer.global_step, rank)
     tmp = path + ".tmp"
     torch.save(ckpt, tmp)
@@ -90,6 +95,9 @@ def load_checkpoint(trainer, path: str, strict: bool = True, restore_rng: bool =
     engine = getattr(getattr(trainer, "_backend_impl", None), "engine", None)
     if engine is not None and ckpt.get("engine"):
         engine.load_state_dict({k: v.to(engine.device) if v.dim() else v for k, v in ckpt["engine"].items()})
+    impl = getattr(trainer, "_backend_impl", None)
+    if hasattr(impl, "load_checkpoint_state") and ckpt.get("strategy"):
+        impl.load_checkpoint_state(ckpt["strategy"])
     if restore_rng and ckpt.get("rng"):
         torch.set_rng_state(ckpt["rng"]["torch"])
         if ckpt["rng"].get("cuda") is not None and torch.cuda.is_available():

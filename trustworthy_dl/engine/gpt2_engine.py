@@ -73,7 +73,8 @@ class GPT2Engine:
                  has_head: bool = True, tied_head: Optional[bool] = None, micro_slots: int = 1, micro_batches: int = 1,
                  n_buckets: Optional[int] = None, overlap: Optional[bool] = None, zero: int = 0,
                  dp_ranks: Optional[Sequence[int]] = None, arena: Optional[SymmetricBuffer] = None, arena_offset: int = 0,
-                 pad: Optional[SymmetricBuffer] = None, pad_index: int = 0):
+                 pad: Optional[SymmetricBuffer] = None, pad_index: int = 0, init: bool = True,
+                 device_trust_update: bool = True):
         assert cfg.n_embd % cfg.n_head == 0 and cfg.n_embd // cfg.n_head == 64, "engine is specialised for head_dim 64"
         assert seq_len % 128 == 0 and seq_len <= cfg.n_positions
         self.cfg = cfg
@@ -93,6 +94,8 @@ class GPT2Engine:
         self.security = security
         self.use_graph = use_graph and self.slots == 1 and self.micro_batches == 1
         self.zero = int(zero)
+        self.device_trust_update = bool(device_trust_update)   # False: the host trust manager owns the trust vector (pipeline stages)
+        self._init_params = bool(init)
         self.step_count = 0
         self._graph = None
         self._calls_per_step: Optional[int] = None
@@ -185,10 +188,11 @@ class GPT2Engine:
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         self.attack_scale = torch.ones(1, dtype=torch.float32, device=dev)      # fault-injection hook (1 = honest)
         self._attack_scale_host = 1.0
+        self.grad_sumsq = torch.zeros(1, dtype=torch.float64, device=dev)       # this rank's squared gradient norm of the step
         # GPT-2 initialisation (same on every rank: replicas start identical); drawn per tensor in canonical model
         # order so a stage engine holds exactly the values the full-model engine would
         g = torch.Generator(device="cpu").manual_seed(seed)
-        for name, shape in self._canonical_order():
+        for name, shape in (self._canonical_order() if self._init_params else []):
             n = math.prod(shape)
             vals = None
             if len(shape) > 1:
@@ -458,6 +462,7 @@ class GPT2Engine:
             # the norm still feeds the verifier / trust update, the median of one rank is the rank itself
             if self.security:
                 _lib.call("tdl_sumsq", ptr(self.g32[sl]), i32(0), i64(seg.n), ptr(r.sumsq), stream_ptr())
+                self.grad_sumsq.add_(r.sumsq)
                 r.partials.add_(r.sumsq)                     # dot(g, median) = |median|^2 = |g|^2
                 r.acc_sq.add_(r.sumsq)
                 r.sumsq.zero_()
@@ -465,6 +470,7 @@ class GPT2Engine:
                     self.wd, 1, grad_scale=self.attack_scale, hyper=self.hyper)
             return
         K.pack_norm(self.g32[sl], self.bucket[sl], r.sumsq, self.attack_scale)           # K1 (+ fault-injection scale)
+        self.grad_sumsq.add_(r.sumsq)
         if self.security:
             r.enqueue_bucket(seg.off, seg.n, overlapped=overlapped, owner_only=bool(self.zero))      # K2
         else:
@@ -508,6 +514,7 @@ class GPT2Engine:
     def begin_step(self) -> None:
         self.loss_sum.zero_()
         self.g32.zero_()
+        self.grad_sumsq.zero_()
         K.adam_tick(self.hyper, self.lr, self.betas[0], self.betas[1])
         if self.zero:
             self.pg_sums.zero_(); self.pg_drift.zero_(); self.pg_flags.zero_()
@@ -520,7 +527,7 @@ class GPT2Engine:
             for i in range(len(self.segments)):
                 self._reduce_segment(i, overlapped=False)
         if self.security:
-            r.enqueue_finalize(update_trust=True)
+            r.enqueue_finalize(update_trust=self.device_trust_update)
         elif self.world > 1:
             r.partials.zero_(); r.acc_sq.zero_(); r.acc_bad.zero_()
 

@@ -36,9 +36,11 @@ TRUST_PARAM_DEFAULTS = [0.1, 0.7, 0.3, 0.8, 0.9, 0.1, 2.0, 2.5, 0.0, 0.3, 0.3, 0
 class SymmetricBuffer:
     """A tensor every rank allocates identically plus the peer pointers to all copies."""
 
-    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, zero: bool = True):
-        self.world = dist.get_world_size() if dist.is_initialized() else 1
-        self.rank = dist.get_rank() if dist.is_initialized() else 0
+    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, zero: bool = True, local: bool = False):
+        """``local``: plain device memory even inside a multi-rank job (a group of one has no peers to map; the
+        symmetric rendezvous is a world collective and must not be entered by one rank alone)."""
+        self.world = dist.get_world_size() if dist.is_initialized() and not local else 1
+        self.rank = dist.get_rank() if dist.is_initialized() and not local else 0
         self.handle = None
         self.itemsize = torch.empty(0, dtype=dtype).element_size()
         if self.world == 1:
@@ -97,7 +99,7 @@ class SymmetricTrustReducer:
         self.dtype = dtype
         self.device = device
         if arena is None:
-            self.bucket = SymmetricBuffer(padded, dtype, device)
+            self.bucket = SymmetricBuffer(padded, dtype, device, local=W == 1)
             self.arena_offset = 0
         else:
             assert arena_offset % vec == 0 and arena_offset + padded <= arena.tensor.numel()
@@ -108,7 +110,7 @@ class SymmetricTrustReducer:
         self.pad_bytes = int(_lib.lib().tdl_exchange_pad_bytes())
         self.pad_words = (self.pad_bytes + 7) // 8
         if pad is None:
-            self.pad = SymmetricBuffer(self.pad_words, torch.int64, device)
+            self.pad = SymmetricBuffer(self.pad_words, torch.int64, device, local=W == 1)
             self.pad_index = 0
         else:
             self.pad, self.pad_index = pad, int(pad_index)

@@ -268,6 +268,24 @@ class TensorParallelStrategy:
             t.trust_manager.resize(self.world)
         base = t._build_model()
         assert hasattr(base, "transformer"), "tensor parallelism is implemented for the GPT-2 family"
+        self.engine = None
+        why = self._fused_blockers(base)
+        if not why:
+            # the whole tensor-parallel step on the repo's kernels (engine/gpt2_tp_engine.py): K7 / K8 for every fused
+            # collective, tcgen05 wgrads, local-head attention, LayerNorm on the token shard, one CUDA graph
+            from ..engine.gpt2_tp_engine import GPT2TPEngine
+            self.engine = GPT2TPEngine.from_module(base, batch_size=c.batch_size, seq_len=c.seq_len or base.config.n_positions,
+                                                   lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
+                                                   security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
+                                                   trust_threshold=c.trust_threshold)
+            self.model = base
+            t.model_partitions[0] = base
+            t.stage_map = StageMap(self.world, self.world)
+            t.stage_costs = [1.0] * self.world
+            return
+        if c.engine == "fused":
+            raise ValueError("engine: fused is not available for this tensor-parallel configuration: " + "; ".join(why))
+        logger.info("tensor parallel: eager modules between the fused collectives (%s)", "; ".join(why))
         dtype = torch.bfloat16 if (c.dtype == "bf16" and self.device.type == "cuda") else torch.float32
         self.model = TPGPT2(base, self.rank, self.world).to(self.device, dtype)
         t.model_partitions[0] = self.model
@@ -284,10 +302,73 @@ class TensorParallelStrategy:
         t.stage_map = StageMap(self.world, self.world)
         t.stage_costs = [1.0] * self.world
 
+    def _fused_blockers(self, base) -> List[str]:
+        c, cfg = self.t.config, base.config
+        T = c.seq_len or cfg.n_positions
+        checks = [(self.device.type == "cuda" and dist.is_initialized() and dist.get_backend() == "nccl", "needs CUDA + NCCL"),
+                  (c.dtype == "bf16", "dtype is not bf16"), (c.engine != "eager", "engine: eager"),
+                  (str(c.optimizer).lower() == "adamw", f"optimizer {c.optimizer!r} (engine: adamw)"),
+                  (str(c.lr_schedule).lower() in ("constant", "none", ""), f"lr_schedule {c.lr_schedule!r}"),
+                  (not c.clip_norm, "clip_norm > 0"), (cfg.n_embd // cfg.n_head == 64, "head_dim != 64"),
+                  (cfg.n_head % self.world == 0, "heads not divisible by the TP degree"),
+                  (c.batch_size % self.world == 0, "batch not divisible by the TP degree"),
+                  ((c.batch_size * T) % (128 * self.world) == 0 and T % 128 == 0, "token shard not a multiple of 128 rows")]
+        return [m for ok, m in checks if not ok]
+
+    def _engine_step(self, batch, t0) -> float:
+        """Fused path: one graph replay per step; afterwards the host trust manager / histories are refreshed from the
+        device-resident security state (a few hundred bytes)."""
+        from ..core.trust_manager import NodeStatus
+        t, c, eng = self.t, self.t.config, self.engine
+        step = t.global_step
+        scale = 1.0
+        if t.attacker is not None and t.attacker._armed("gradient_poisoning", step, self.rank):
+            i = t.attacker.config.intensity
+            scale = -(1.0 + 4.0 * i) if t.attacker.config.gradient_mode == "sign_flip" else 1.0 + 20.0 * i
+            t.attacker._record("gradient_poisoning", step, self.rank, mode=t.attacker.config.gradient_mode)
+        eng.train_step(batch["input"], batch["target"], attack_scale=scale)
+        lt = eng.loss_sum.double() / eng.M
+        if self.world > 1:
+            dist.all_reduce(lt)
+        ts = time.perf_counter()
+        snap = eng.security_snapshot()
+        loss_val = float(lt.item())
+        trust, status, flags = snap["trust"].tolist(), snap["status"].tolist(), snap["flags"].tolist()
+        tm = t.trust_manager
+        t._last_step_info = {"out_stats": {}, "invalid_nodes": set(), "grad_norms": {}}
+        for node in range(self.world):
+            if flags[node] & 1 and tm.get_node_status(node) is not NodeStatus.COMPROMISED:
+                t._last_step_info["invalid_nodes"].add(node)
+                t.attack_history.append({"node_id": node, "timestamp": time.time(), "step": step,
+                                         "attack_type": "gradient_poisoning",
+                                         "gradient_stats": {"total_norm": float(snap["stats"][node, 0]),
+                                                            "cosine_to_median": float(snap["stats"][node, 3])}})
+                tm.attack_history[node].append({"timestamp": tm.clock(), "attack_type": "gradient_poisoning",
+                                                "previous_trust": tm.get_trust_score(node)})
+                t.metrics_collector.record_event("attack", node_id=node, type="gradient_poisoning", step=step)
+                self.reassign(node)
+                from ..core.distributed_trainer import TrainingState
+                t.training_state = TrainingState.UNDER_ATTACK
+            tm._value[node] = trust[node]                   # device state is authoritative on this path
+            tm._status[node] = status[node]
+            tm._count[node] += 1
+        if c.attack_detection_enabled:
+            res = t.attack_detector.observe_stats(snap["act_stats"].numpy(), self.rank, step)
+            if res.is_attack:
+                t.metrics_collector.record_event("output_anomaly", node_id=self.rank, step=step)
+        self._sec_s += time.perf_counter() - ts
+        self._step_s += time.perf_counter() - t0
+        t.metrics_collector.collect_batch_metrics({
+            "loss": loss_val, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
+            "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        return loss_val
+
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
         t, c = self.t, self.t.config
         t0 = time.perf_counter()
         step = t.global_step
+        if self.engine is not None:
+            return self._engine_step(batch, t0)
         idx, tgt = batch["input"].to(self.device), batch["target"].to(self.device)
         logits, loss = self.model(idx, tgt)
         loss.backward()
@@ -338,8 +419,10 @@ class TensorParallelStrategy:
         return loss_val
 
     def reassign(self, src: int) -> Optional[int]:
-        """A TP rank cannot be dropped without re-sharding every layer; the compromised rank keeps computing
-        but its replicated-parameter gradients get coefficient 0 (recorded as a reassignment of its share)."""
+        """A tensor-parallel rank holds 1/W of every layer, so it cannot be dropped without re-sharding the whole model
+        onto W - 1 ranks (head counts and hidden widths do not divide).  What the framework does instead -- and what the
+        history entry says (``kind: tp_zero_weighted``) -- is zero-weight the rank: it keeps computing its slice, but its
+        replicated-parameter gradients enter the aggregation with coefficient 0 from the same step on."""
         t = self.t
         if not t.planner.allowed(src):
             return None
@@ -348,17 +431,33 @@ class TensorParallelStrategy:
             return None
         t.planner.note_attempt(src)
         t.reassignment_history.append({"from_node": src, "to_node": dst, "timestamp": time.time(), "step": t.global_step,
-                                       "stages": [], "migration_time": 0.0, "kind": "tp_gradient_share"})
+                                       "stages": [], "migration_time": 0.0, "kind": "tp_zero_weighted"})
         return dst
 
     @torch.no_grad()
     def validate(self, loader) -> float:
+        if self.engine is not None:
+            return self._validate_engine(loader)
         total, n = 0.0, 0
         for batch in loader:
             _, loss = self.model(batch["input"].to(self.device), batch["target"].to(self.device))
             lt = loss.detach().float().reshape(1)
             if self.world > 1:
                 lt = lt.cpu() if comm.is_gloo() else lt
+                dist.all_reduce(lt)
+            total += float(lt.item())
+            n += 1
+        return total / max(1, n)
+
+    def _validate_engine(self, loader) -> float:
+        """Forward-only through the engine (same kernels, same collectives), mean loss over the loader."""
+        eng, total, n = self.engine, 0.0, 0
+        for batch in loader:
+            eng.idx.copy_(batch["input"].view(eng.B, eng.T)); eng.tgt.copy_(batch["target"].view(eng.B, eng.T))
+            eng.loss_sum.zero_()
+            eng._forward()
+            lt = eng.loss_sum.double() / eng.M
+            if self.world > 1:
                 dist.all_reduce(lt)
             total += float(lt.item())
             n += 1
