@@ -214,6 +214,7 @@ def main() -> int:
     n_segments = len(eng.segments)
     overlap = bool(eng.overlap and n_segments > 1)
     multimem = bool(eng.reducer.use_multimem)
+    k4_multimem = bool(eng.reducer.k4_multimem)
     # ---- same-box stock-library arm (the bar BASELINE.md names): run after ours, our buffers released first ----
     stock = None
     if args.stock != "skip":
@@ -246,8 +247,9 @@ def main() -> int:
             "kernels_per_step": kernels_per_step,
             "detection_overhead_pct": overhead,
             "detection_overhead_vs": ("same engine, security kernels off" if world == 1 else
-                                      "same engine with K4 (plain mean all-reduce over the same symmetric bucket: multimem.ld_reduce/"
-                                      "multimem.st, or P2P when no multicast object) instead of K2, activation statistics and trust update off"),
+                                      ("same engine with K4 instead of K2 (plain mean all-reduce of the same symmetric bucket, " +
+                                       ("multimem.ld_reduce + multimem.st through the switch" if k4_multimem else "P2P loads/stores") +
+                                       "), activation statistics and trust update off")),
             "final_loss": losses[-1] if losses else None,
             "trust": [float(x) for x in snap["trust"]],
             "impl": "ours",

@@ -29,40 +29,95 @@ from trustworthy_dl.utils.data_loader import get_dataloader
 
 def build(name: str, world: int, args):
     att = None
+    base = args.impl == "baseline"
+    sec = dict(attack_detection_enabled=not base, gradient_verification_enabled=not base)
+    eng = "eager" if base else "auto"
     if name == "vgg16_mp8":
         cfg = TrainingConfig(model_name="vgg16", dataset_name="imagenet", batch_size=args.batch or 64, num_nodes=world,
                              learning_rate=1e-3, checkpoint_interval=0, parallelism="pipeline", micro_batches=8, dtype="bf16",
-                             optimizer="sgd")
+                             optimizer="sgd", **sec)
         data = ("imagenet", {})
         unit = "images/s"
     elif name == "resnet50_dp":
         cfg = TrainingConfig(model_name="resnet50", dataset_name="imagenet", batch_size=(args.batch or 32) * world, num_nodes=world,
                              learning_rate=1e-3, checkpoint_interval=0, parallelism="data", dtype="bf16", optimizer="sgd",
-                             engine="eager")
+                             engine="eager", **sec)
         data = ("imagenet", {})
         unit = "images/s"
     elif name == "gpt2_tp8":
-        cfg = TrainingConfig(model_name="gpt2", model_size="medium", dataset_name="openwebtext", batch_size=args.batch or 8,
+        cfg = TrainingConfig(model_name="gpt2", model_size="medium", dataset_name="openwebtext", batch_size=args.batch or 32,
                              num_nodes=world, learning_rate=5e-5, checkpoint_interval=0, parallelism="tensor", tp_size=world,
-                             dtype="bf16", seq_len=1024, optimizer="sgd")
+                             dtype="bf16", seq_len=1024, optimizer="adamw", engine=eng, **sec)
+        if base:
+            os.environ["TDL_TP_FUSED"] = "0"          # Megatron-style arm: torch matmul + NCCL all-gather / reduce-scatter
         att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[min(3, world - 1)], intensity=0.5,
                                                start_step=args.attack_step))
         data = ("openwebtext", {"seq_len": 1024})
         unit = "tokens/s"
     elif name == "gpt2_pp4dp2":
         dp = 2 if world % 2 == 0 and world >= 4 else 1
-        cfg = TrainingConfig(model_name="gpt2", model_size="medium", dataset_name="openwebtext", batch_size=args.batch or 32,
+        cfg = TrainingConfig(model_name="gpt2", model_size="medium", dataset_name="openwebtext", batch_size=args.batch or 128 * dp,
                              num_nodes=world, learning_rate=5e-5, checkpoint_interval=0, parallelism="pipeline", pp_size=world // dp,
-                             dp_size=dp, micro_batches=8, dtype="bf16", seq_len=1024, optimizer="sgd", migration_model="nvlink")
+                             dp_size=dp, micro_batches=args.micro, dtype="bf16", seq_len=1024, optimizer="adamw", migration_model="nvlink",
+                             engine=eng, **sec)
         att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[min(2, world - 1)], intensity=0.5,
                                                start_step=args.attack_step))
         data = ("openwebtext", {"seq_len": 1024})
         unit = "tokens/s"
     else:
         raise SystemExit(f"unknown config {name}")
+    if base or args.no_attack:
+        att = None
     if att is not None:
         att.activate_attacks()
     return cfg, att, data, unit
+
+
+def ddp_baseline(cfg, dname, dkw, unit, args, world, rank, local, dev) -> int:
+    """Baseline A of the data-parallel configuration: the same nn.Module under torch DDP (NCCL all-reduce), stock optimizer,
+    bf16 autocast, no security."""
+    from trustworthy_dl.models.model_factory import ModelFactory
+    torch.manual_seed(0)
+    model = ModelFactory().create_model(cfg.model_name, cfg.model_size).to(dev)
+    if world > 1:
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    opt = torch.optim.SGD(model.parameters(), lr=cfg.learning_rate, momentum=0.9, weight_decay=cfg.weight_decay)
+    loader = list(get_dataloader(dname, "train", cfg.batch_size, num_batches=4, **dkw))
+    core = model.module if world > 1 else model
+
+    def step(i):
+        b = loader[i % len(loader)]
+        x = b["input"].chunk(world)[rank].to(dev, non_blocking=True)
+        y = b["target"].chunk(world)[rank].to(dev, non_blocking=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = model(x)
+        loss = core.loss(out, y)
+        loss.backward()
+        opt.step(); opt.zero_grad(set_to_none=True)
+        return loss
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = step(i)
+    e1.record(); e1.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        total = float(ms.item())
+        print(json.dumps({"config": args.config, "impl": "baseline", "strategy": "torch DDP + NCCL all-reduce", "n_gpus": world,
+                          "steps": args.steps, "warmup": args.warmup, "value": cfg.batch_size * args.steps / (total / 1e3), "unit": unit,
+                          "ms_per_step": total / args.steps, "dtype": cfg.dtype, "data": "synthetic", "global_batch": cfg.batch_size,
+                          "final_loss": float(loss.item())}))
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+    return 0
 
 
 def main() -> int:
@@ -72,6 +127,11 @@ def main() -> int:
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--batch", type=int, default=0)
     p.add_argument("--attack-step", type=int, default=8)
+    p.add_argument("--micro", type=int, default=8, help="micro-batches per step of the pipeline configurations")
+    p.add_argument("--no-attack", action="store_true")
+    p.add_argument("--impl", default="ours", choices=["ours", "baseline"],
+                   help="baseline = BASELINE.md baseline A: stock kernels (torch eager, cuBLAS/cuDNN/SDPA) + NCCL collectives, "
+                        "security off, same box, same model/config")
     args = p.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -79,6 +139,8 @@ def main() -> int:
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     cfg, att, (dname, dkw), unit = build(args.config, world, args)
+    if args.impl == "baseline" and args.config == "resnet50_dp":
+        return ddp_baseline(cfg, dname, dkw, unit, args, world, rank, local, dev)
     t = DistributedTrainer(cfg, attacker=att)
     t._rank, t._world = rank, world
     t.device = dev
@@ -112,7 +174,9 @@ def main() -> int:
         attack_at = None
         if t.attack_history:
             attack_at = t.attack_history[0]["step"] - args.warmup - 1       # index into the timed steps
-        out = {"config": args.config, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        out = {"config": args.config, "impl": args.impl, "strategy": type(t._backend_impl).__name__,
+               "fused_engine": bool(getattr(t._backend_impl, "engine", None) is not None or getattr(t._backend_impl, "engines", None)),
+               "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "value": per_step * args.steps / (total / 1e3), "unit": unit, "ms_per_step": total / args.steps,
                "ms_per_step_median": sorted(ms)[len(ms) // 2], "step_ms": [round(x, 2) for x in ms], "dtype": cfg.dtype,
                "data": "synthetic", "global_batch": cfg.batch_size, "parallelism": cfg.parallelism,

@@ -601,7 +601,7 @@ __global__ void __launch_bounds__(256) pack_norm_kernel(const float* __restrict_
     __syncthreads();
     if (threadIdx.x == 0) {
         double t = 0;
-        for (int w = 0; w < 8; ++w) t += sh[w];
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sh[w];
         atomicAdd(sumsq, t);
     }
 }
@@ -624,7 +624,7 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const T* __restrict__ x, lon
     __syncthreads();
     if (threadIdx.x == 0) {
         double t = 0;
-        for (int w = 0; w < 8; ++w) t += sh[w];
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sh[w];
         atomicAdd(sumsq, t);
     }
 }
@@ -729,6 +729,11 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
     }
 }
 
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dst[i] = __bfloat162float(src[i]);
+}
+
 // advances the optimizer step on the device and refreshes (lr, 1-b1^t, 1-b2^t): graph-replay safe
 __global__ void adam_tick_kernel(float* hyper, float lr, float b1, float b2) {
     if (threadIdx.x == 0) {
@@ -783,6 +788,16 @@ __global__ void __launch_bounds__(256) reduce_slots_bias_kernel(const __nv_bfloa
         }
         *reinterpret_cast<uint4*>(out + i) = f32_to_bf16x8(acc);
     }
+}
+
+// block size / grid of a memory-bound helper kernel: 256 threads x up to 8 blocks per SM, or (small-footprint mode) 128
+// threads x 2 blocks per SM so the blocks fit beside a resident tensor-core CTA
+inline int helper_threads() { return tdl_small_footprint() ? 128 : 256; }
+inline int helper_grid(long long n, int per_thread) {
+    const int th = helper_threads();
+    long long b = (n + (long long)th * per_thread - 1) / ((long long)th * per_thread);
+    const long long cap = (long long)tdl_num_sms() * (tdl_small_footprint() ? 2 : 8);
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
 inline int grid_for(long long n, int per_block) {
@@ -884,12 +899,12 @@ extern "C" int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype
                          const float* grad_scale, const float* hyper_dev, void* stream) {
     TDL_REQUIRE(n % 4 == 0, "AdamW length must be a multiple of 4 (pad the flat buffer)");
     const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
-    const int grid = grid_for(n, 256 * 4 * 4);
+    const int grid = helper_grid(n, 4 * 4), th = helper_threads();
     if (grad_dtype == TDL_F32)
-        adamw_kernel<float><<<grid, 256, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const float*)grad, m, v, n, n_decay,
+        adamw_kernel<float><<<grid, th, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const float*)grad, m, v, n, n_decay,
                                                               lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, hyper_dev);
     else if (grad_dtype == TDL_BF16)
-        adamw_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const __nv_bfloat16*)grad, m, v, n,
+        adamw_kernel<__nv_bfloat16><<<grid, th, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const __nv_bfloat16*)grad, m, v, n,
                                                                       n_decay, lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, hyper_dev);
     else return tdl_set_error("AdamW grads must be fp32 or bf16");
     TDL_LAUNCH_CHECK();
@@ -928,17 +943,17 @@ extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row
 
 extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, const float* scale_dev, void* stream) {
     TDL_REQUIRE(n % 8 == 0, "bucket length must be a multiple of 8");
-    pack_norm_kernel<<<grid_for(n, 256 * 8 * 4), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq, scale_dev);
+    pack_norm_kernel<<<helper_grid(n, 8 * 4), helper_threads(), 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq, scale_dev);
     TDL_LAUNCH_CHECK();
     return 0;
 }
 
 // sumsq (device double) += sum x^2 ; the cross-rank exchange re-zeroes the accumulator after publishing it
 extern "C" int tdl_sumsq(const void* x, int dtype, int64_t n, double* sumsq, void* stream) {
-    const int grid = grid_for(n, 256 * 16);
-    if (dtype == TDL_F32) sumsq_kernel<float><<<grid, 256, 0, STREAM(stream)>>>((const float*)x, n, sumsq);
-    else if (dtype == TDL_BF16) sumsq_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)x, n, sumsq);
-    else if (dtype == TDL_F16) sumsq_kernel<__half><<<grid, 256, 0, STREAM(stream)>>>((const __half*)x, n, sumsq);
+    const int grid = helper_grid(n, 16), th = helper_threads();
+    if (dtype == TDL_F32) sumsq_kernel<float><<<grid, th, 0, STREAM(stream)>>>((const float*)x, n, sumsq);
+    else if (dtype == TDL_BF16) sumsq_kernel<__nv_bfloat16><<<grid, th, 0, STREAM(stream)>>>((const __nv_bfloat16*)x, n, sumsq);
+    else if (dtype == TDL_F16) sumsq_kernel<__half><<<grid, th, 0, STREAM(stream)>>>((const __half*)x, n, sumsq);
     else return tdl_set_error("unsupported dtype %d", dtype);
     TDL_LAUNCH_CHECK();
     return 0;
@@ -1016,6 +1031,13 @@ extern "C" int tdl_reduce_slots_bias(const void* staging, int W, int64_t rows, i
     const long long n = rows * cols;
     reduce_slots_bias_kernel<<<grid_for(n, 256 * 8 * 2), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)staging, W, n, (int)cols, bias,
                                                                                 (const __nv_bfloat16*)residual, (__nv_bfloat16*)out);
+    TDL_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int tdl_cast_bf16_f32(const void* src, float* dst, int64_t n, void* stream) {
+    if (n <= 0) return 0;
+    cast_bf16_f32_kernel<<<grid_for(n, 256 * 4), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)src, dst, n);
     TDL_LAUNCH_CHECK();
     return 0;
 }

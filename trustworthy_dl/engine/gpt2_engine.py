@@ -59,10 +59,11 @@ def _round_up(x: int, m: int) -> int:
 
 class _Segment:
     """A contiguous slice of the flat parameter buffer whose gradients complete together."""
-    __slots__ = ("name", "off", "n", "n_decay", "tensors")
+    __slots__ = ("name", "off", "n", "n_decay", "tensors", "nd_off", "nd_n")
 
     def __init__(self, name: str):
         self.name, self.off, self.n, self.n_decay, self.tensors = name, 0, 0, 0, []
+        self.nd_off = self.nd_n = 0            # this segment's 1-D tensors inside the fp32 view used by ZeRO-1
 
 
 class GPT2Engine:
@@ -158,9 +159,14 @@ class GPT2Engine:
                 off += n
                 if decay:
                     seg.n_decay = off - seg.off
+            seg.nd_n = off - (seg.off + seg.n_decay)
             off = _round_up(off, SEG_ALIGN)
             seg.n = off - seg.off
         self.P = off
+        nd = 0
+        for seg in self.segments:
+            seg.nd_off = nd
+            nd += seg.nd_n
         self.p32 = torch.zeros(self.P, dtype=torch.float32, device=dev)
         self.m = torch.zeros(self.P, dtype=torch.float32, device=dev)
         self.v = torch.zeros(self.P, dtype=torch.float32, device=dev)
@@ -183,6 +189,9 @@ class GPT2Engine:
             self.pg_pub = torch.zeros(G, self.world, 2, dtype=torch.int64, device=dev)       # what every owner published
             self.pg_flags = torch.zeros(self.world, dtype=torch.int32, device=dev)           # 1 = shard of that rank mismatched
             self.param_attack = torch.zeros(1, dtype=torch.float32, device=dev)              # fault injection: noise on my shard
+            # ZeRO-1 publishes parameters in bf16, LayerNorm gains and biases included: every rank (the owner too, so the
+            # replicas stay identical) feeds the fp32-consuming kernels from an fp32 view of the gathered bf16 values
+            self.nd32 = torch.zeros(max(nd, 8), dtype=torch.float32, device=dev)
         else:
             self.p16 = torch.zeros(self.P, dtype=torch.bfloat16, device=dev)
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
@@ -210,9 +219,31 @@ class GPT2Engine:
         for nm in ("wte", "lm_head"):
             if nm in self.offsets and self.Vp > self.V:
                 self.w32(nm)[self.V:].zero_()
+        self._refresh_working_copies()
+
+    def _refresh_working_copies(self) -> None:
+        """bf16 working parameters (and, under ZeRO-1, the fp32 view of the 1-D tensors) from the fp32 master."""
         K.cast_f32_bf16(self.p32, self.p16)
         if self.zero:
             self.p16_prev.copy_(self.p16)
+            for seg in self.segments:
+                self._refresh_nd(seg)
+
+    def _refresh_nd(self, seg) -> None:
+        if seg.nd_n:
+            a = seg.off + seg.n_decay
+            K.cast_bf16_f32(self.p16[a:a + seg.nd_n], self.nd32[seg.nd_off:seg.nd_off + seg.nd_n])
+
+    def wf(self, name: str) -> torch.Tensor:
+        """fp32 view of a 1-D tensor for the kernels that consume fp32 (LayerNorm gain / bias, GEMM bias)."""
+        if not self.zero:
+            return self.w32(name)
+        o, shape = self.offsets[name]
+        for seg in self.segments:
+            if seg.off <= o < seg.off + seg.n:
+                a = seg.nd_off + o - (seg.off + seg.n_decay)
+                return self.nd32[a:a + math.prod(shape)].view(shape)
+        raise KeyError(name)
 
     def _canonical_order(self):
         """(name, shape) of every tensor of the *whole* model in a fixed order (initialisation stream)."""
@@ -277,16 +308,29 @@ class GPT2Engine:
     def load_from_module(self, module) -> None:
         for name, t in self._module_tensors(module).items():
             self.w32(name).copy_(t.detach().to(self.device, torch.float32))
-        K.cast_f32_bf16(self.p32, self.p16)
-        if self.zero:
-            self.p16_prev.copy_(self.p16)
+        self._refresh_working_copies()
+
+    @torch.no_grad()
+    def sync_master(self) -> None:
+        """ZeRO-1: every rank holds only its slice of the fp32 master weights and Adam moments; assemble the full buffers
+        on every rank (NCCL all-gather, off the step path: checkpoints, export, validation on the nn.Module)."""
+        if not self.zero or self.world == 1:
+            return
+        import torch.distributed as dist
+        for seg in self.segments:
+            per = seg.n // self.world
+            lo = seg.off + self.reducer.rank * per
+            for buf in (self.p32, self.m, self.v):
+                dist.all_gather_into_tensor(buf[seg.off:seg.off + seg.n], buf[lo:lo + per].clone())
 
     @torch.no_grad()
     def export_to_module(self, module) -> None:
+        self.sync_master()
         for name, t in self._module_tensors(module).items():
             t.copy_(self.w32(name).to(t.device, t.dtype))
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
+        self.sync_master()
         return {"p32": self.p32.clone(), "m": self.m.clone(), "v": self.v.clone(), "hyper": self.hyper.clone(),
                 "step": torch.tensor(self.step_count), "trust": self.reducer.trust.clone(),
                 "status": self.reducer.status.clone()}
@@ -295,9 +339,7 @@ class GPT2Engine:
         self.p32.copy_(sd["p32"]); self.m.copy_(sd["m"]); self.v.copy_(sd["v"]); self.hyper.copy_(sd["hyper"])
         self.step_count = int(sd["step"])
         self.reducer.trust.copy_(sd["trust"]); self.reducer.status.copy_(sd["status"])
-        K.cast_f32_bf16(self.p32, self.p16)
-        if self.zero:
-            self.p16_prev.copy_(self.p16)
+        self._refresh_working_copies()
 
     # ---- stage migration (trust-driven reassignment): everything a new owner needs to continue bit-identically ----
     def migration_tensors(self) -> List[torch.Tensor]:
@@ -306,7 +348,7 @@ class GPT2Engine:
         return [self.p32, self.m, self.v, self.hyper, self.reducer.epochs]
 
     def after_migration(self) -> None:
-        K.cast_f32_bf16(self.p32, self.p16)
+        self._refresh_working_copies()
 
     # ------------------------------------------------------------------ activations
     def _build_activations(self) -> None:
@@ -362,20 +404,20 @@ class GPT2Engine:
         L, eps = self.L, self.cfg.layer_norm_eps
         for j in range(L):
             p = f"h{self.l0 + j}."
-            K.layernorm_fwd(self.res[s, j], self.w32(p + "ln1_w"), self.w32(p + "ln1_b"), self.ln1[s, j],
+            K.layernorm_fwd(self.res[s, j], self.wf(p + "ln1_w"), self.wf(p + "ln1_b"), self.ln1[s, j],
                             self.ln_mean[s, 2 * j], self.ln_rstd[s, 2 * j], eps)
-            K.linear_fwd(self.ln1[s, j], self.w16(p + "qkv_w"), self.qkv[s, j], bias=self.w32(p + "qkv_b"))
+            K.linear_fwd(self.ln1[s, j], self.w16(p + "qkv_w"), self.qkv[s, j], bias=self.wf(p + "qkv_b"))
             K.attention_fwd(self.qkv[s, j], self.atty[s, j], self.lse[s, j], self.B, self.T, self.H)
-            K.linear_fwd(self.atty[s, j], self.w16(p + "o_w"), self.x2[s, j], bias=self.w32(p + "o_b"),
+            K.linear_fwd(self.atty[s, j], self.w16(p + "o_w"), self.x2[s, j], bias=self.wf(p + "o_b"),
                          epilogue=K.EPI_RESIDUAL, aux_in=self.res[s, j])
-            K.layernorm_fwd(self.x2[s, j], self.w32(p + "ln2_w"), self.w32(p + "ln2_b"), self.ln2[s, j],
+            K.layernorm_fwd(self.x2[s, j], self.wf(p + "ln2_w"), self.wf(p + "ln2_b"), self.ln2[s, j],
                             self.ln_mean[s, 2 * j + 1], self.ln_rstd[s, 2 * j + 1], eps)
-            K.linear_fwd(self.ln2[s, j], self.w16(p + "fc_w"), self.fcg[s, j], bias=self.w32(p + "fc_b"),
+            K.linear_fwd(self.ln2[s, j], self.w16(p + "fc_w"), self.fcg[s, j], bias=self.wf(p + "fc_b"),
                          epilogue=K.EPI_GELU_DG, aux_out=self.fch[s, j])     # fch holds gelu'(pre): backward multiplies
-            K.linear_fwd(self.fcg[s, j], self.w16(p + "proj_w"), self.res[s, j + 1], bias=self.w32(p + "proj_b"),
+            K.linear_fwd(self.fcg[s, j], self.w16(p + "proj_w"), self.res[s, j + 1], bias=self.wf(p + "proj_b"),
                          epilogue=K.EPI_RESIDUAL, aux_in=self.x2[s, j])
         if self.has_head:
-            K.layernorm_fwd(self.res[s, L], self.w32("lnf_w"), self.w32("lnf_b"), self.lnf[s], self.ln_mean[s, 2 * L],
+            K.layernorm_fwd(self.res[s, L], self.wf("lnf_w"), self.wf("lnf_b"), self.lnf[s], self.ln_mean[s, 2 * L],
                             self.ln_rstd[s, 2 * L], eps)
 
     def _head_forward(self, s: int) -> None:
@@ -414,7 +456,7 @@ class GPT2Engine:
             dx = self.dx_a
             # every LayerNorm backward also emits the column sums of the dx it writes = the bias gradient of the linear
             # layer below it (MLP down-projection under ln_f / ln_1, attention output projection under ln_2)
-            K.layernorm_bwd(self.dln, self.res[s, L], self.w32("lnf_w"), self.ln_mean[s, 2 * L], self.ln_rstd[s, 2 * L], None, dx,
+            K.layernorm_bwd(self.dln, self.res[s, L], self.wf("lnf_w"), self.ln_mean[s, 2 * L], self.ln_rstd[s, 2 * L], None, dx,
                             self.grad32("lnf_w"), self.grad32("lnf_b"), dxsum=self.grad32(top + "proj_b"))
         else:
             dx = self.dy_in[k]
@@ -429,7 +471,7 @@ class GPT2Engine:
             K.linear_wgrad(self.dfch, self.ln2[s, j], self.grad32(p + "fc_w"), split_k=self._split_k(4 * C, C))
             K.linear_dgrad(self.dfch, self.w16(p + "fc_w"), self.dln)
             nxt = scratch_other(dx)
-            K.layernorm_bwd(self.dln, self.x2[s, j], self.w32(p + "ln2_w"), self.ln_mean[s, 2 * j + 1], self.ln_rstd[s, 2 * j + 1],
+            K.layernorm_bwd(self.dln, self.x2[s, j], self.wf(p + "ln2_w"), self.ln_mean[s, 2 * j + 1], self.ln_rstd[s, 2 * j + 1],
                             dx, nxt, self.grad32(p + "ln2_w"), self.grad32(p + "ln2_b"), dxsum=self.grad32(p + "o_b"))
             dx = nxt
             # ---- attention ----
@@ -440,7 +482,7 @@ class GPT2Engine:
             K.linear_wgrad(self.dqkv, self.ln1[s, j], self.grad32(p + "qkv_w"), split_k=self._split_k(3 * C, C))
             K.linear_dgrad(self.dqkv, self.w16(p + "qkv_w"), self.dln)
             nxt = self.dx_out[k] if (j == 0 and not self.has_embed) else scratch_other(dx)
-            K.layernorm_bwd(self.dln, self.res[s, j], self.w32(p + "ln1_w"), self.ln_mean[s, 2 * j], self.ln_rstd[s, 2 * j],
+            K.layernorm_bwd(self.dln, self.res[s, j], self.wf(p + "ln1_w"), self.ln_mean[s, 2 * j], self.ln_rstd[s, 2 * j],
                             dx, nxt, self.grad32(p + "ln1_w"), self.grad32(p + "ln1_b"),
                             dxsum=self.grad32(f"h{l - 1}.proj_b") if j > 0 else None)
             dx = nxt
@@ -508,6 +550,7 @@ class GPT2Engine:
                   ptr(self.p16_prev[seg.off:seg.off + seg.n]), i64(per), ptr(self.pg_sums[i]), ptr(self.pg_drift[i]),
                   stream_ptr())
         _lib.call("tdl_integrity_compare", ptr(self.pg_sums[i]), ptr(self.pg_pub[i]), i32(W), ptr(self.pg_flags), stream_ptr())
+        self._refresh_nd(seg)
         r.barrier(0)                                  # nobody overwrites a slice that a peer is still pulling
 
     # ------------------------------------------------------------------ step pieces
@@ -548,7 +591,13 @@ class GPT2Engine:
                     ev.record(main)
                     self.side.wait_event(ev)
                     with torch.cuda.stream(self.side):
-                        self._reduce_segment(i, overlapped=i < last)
+                        # blocks small enough to sit beside the resident GEMM / attention CTAs of the backward pass; the last
+                        # segment has the GPU to itself
+                        _lib.lib().tdl_set_small_footprint(1 if i < last else 0)
+                        try:
+                            self._reduce_segment(i, overlapped=i < last)
+                        finally:
+                            _lib.lib().tdl_set_small_footprint(0)
 
                 self._backward(0, 0, seg_done)
                 main.wait_stream(self.side)

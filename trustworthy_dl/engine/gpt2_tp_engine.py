@@ -27,6 +27,7 @@ injects poisoned gradients is caught — and rescaled by W (the aggregate is a w
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -217,8 +218,13 @@ class GPT2TPEngine:
         self.logits = torch.empty(Ms, self.Vp, **bf)
         self.row_loss = torch.empty(Ms, **f32)
         self.loss_sum = torch.zeros(1, **f32)
-        self.full_a = torch.empty(M, C, **bf)           # gathered operand of a wgrad (pulled beside the critical path)
+        # gathered operands: the K8 pull lands every [M, C] activation / gradient here once; the forward copies are kept per
+        # layer because the wgrads of the backward pass consume them again (no second trip over NVLink)
+        self.k8_flags = os.environ.get("TDL_K8", "flags") != "tma"
+        self.ln_full = torch.empty(L, 2, M, C, **bf) if self.k8_flags else None
+        self.full_a = torch.empty(M, C, **bf)
         self.full_b = torch.empty(M, C, **bf)
+        self.flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
         self.dln_s = torch.empty(Ms, C, **bf)
         self.dfch = torch.empty(M, Fl, **bf)
         self.datty = torch.empty(M, Cl, **bf)
@@ -239,16 +245,48 @@ class GPT2TPEngine:
             _lib.call("tdl_exchange", self.pad.ptr_array(), i32(self.rank), i32(self.world), i32(0), ptr(self._nothing), i32(0),
                       ptr(self.epochs), i32(0), stream_ptr())
 
-    def _col_parallel(self, off: int, w, out, **kw) -> None:
-        """K8: out [M, N_local] = AG(shards at arena offset ``off``) @ w (see tp_ops.allgather_gemm)."""
+    def _col_parallel(self, off: int, w, out, full: Optional[torch.Tensor] = None, **kw) -> None:
+        """K8: out [M, N_local] = AG(shards at arena offset ``off``) @ w.
+
+        Default form (tile-arrival flags): a small-footprint pull kernel on the copy stream brings the peer shards into the
+        local buffer ``full`` 16 rows at a time and raises a flag per 128-row block; the tcgen05 GEMM runs at the same time
+        on the compute stream and its TMA producer waits for the flag of each tile, own shard first.  Every remote byte
+        crosses NVLink once and ``full`` stays for the wgrad.  ``TDL_K8=tma``: the TMA producer reads the peer shards
+        directly (re-fetching an A tile once per n-block)."""
         self.barrier()                                               # every rank's shard is written
-        tp_ops.allgather_gemm(self._peers(off), self.rank, self.Ms, w, out, **kw)
+        if full is None or not self.k8_flags:
+            tp_ops.allgather_gemm(self._peers(off), self.rank, self.Ms, w, out, **kw)
+            if full is not None:
+                tp_ops.gather_rows(self._peers(off), self.Ms * self.C, full.view(-1))
+            return
+        self.flags.zero_()
+        main = torch.cuda.current_stream()
+        ev0 = torch.cuda.Event(); ev0.record(main)
+        self.copy_stream.wait_event(ev0)
+        with torch.cuda.stream(self.copy_stream):
+            tp_ops.gather_rows_flagged(self._peers(off), self.rank, self.Ms, self.C, full, self.flags)
+            ev1 = torch.cuda.Event(); ev1.record(self.copy_stream)
+        tp_ops.gemm_flagged(full, self.flags, self.world, self.rank, self.Ms, w, out, **kw)
+        main.wait_event(ev1)
 
     def _row_parallel(self, a, w, out_s, bias=None, residual=None, b_mn: bool = False) -> None:
         """K7 + slot sum: out_s [Ms, C] = RS(a @ w^T) (+ bias) (+ residual)."""
         tp_ops.gemm_scatter(a, w, self._peers(self._off_slots), self.rank, self.Ms, b_mn=b_mn)
         self.barrier()                                               # every partial tile has landed in its owner's slots
         tp_ops.reduce_slots(self.slots, self.world, out_s, residual=residual, bias=bias)
+
+    def _gathered_ln(self, l: int, j: int) -> torch.Tensor:
+        """The full [M, C] LayerNorm output of block ``l`` (j = 0: ln_1, 1: ln_2) for a wgrad: kept from the forward K8, or
+        (TDL_K8=tma) pulled again from the per-layer symmetric shards."""
+        if self.ln_full is not None:
+            return self.ln_full[l, j]
+        dst = self.full_a if j == 1 else self.full_b     # not in use at that point of the block's backward
+        tmp = torch.empty_like(dst)
+        tp_ops.gather_rows(self._peers(self._off_ln[l][j]), self.Ms * self.C, tmp.view(-1))
+        return tmp
+
+    def _lnf(self, l: int, j: int) -> Optional[torch.Tensor]:
+        return self.ln_full[l, j] if self.ln_full is not None else None
 
     def _pull(self, off: int, dst: torch.Tensor, side: bool = True):
         """Gathered copy [M, C] of the shards at ``off`` for a wgrad.  Issued on the copy stream (beside the GEMMs of the
@@ -275,14 +313,14 @@ class GPT2TPEngine:
             K.layernorm_fwd(self.res[l], self.w32(p + "ln1_w"), self.w32(p + "ln1_b"), self.sym_ln[l][0],
                             self.ln_mean[2 * l], self.ln_rstd[2 * l], eps)
             # 256-wide tiles even when 3C/W is not a multiple of 256: every A tile crosses NVLink once per n-block
-            self._col_parallel(self._off_ln[l][0], self.w16(p + "qkv_w"), self.qkv[l], bias=self.w32(p + "qkv_b"),
-                               block_n=256 if 3 * self.Cl > 128 else 0)
+            self._col_parallel(self._off_ln[l][0], self.w16(p + "qkv_w"), self.qkv[l], full=self._lnf(l, 0),
+                               bias=self.w32(p + "qkv_b"), block_n=256 if 3 * self.Cl > 128 else 0)
             K.attention_fwd(self.qkv[l], self.atty[l], self.lse[l], self.B, self.T, self.Hl)
             self._row_parallel(self.atty[l], self.w16(p + "o_w"), self.x2[l], bias=self.w32(p + "o_b"), residual=self.res[l])
             K.layernorm_fwd(self.x2[l], self.w32(p + "ln2_w"), self.w32(p + "ln2_b"), self.sym_ln[l][1],
                             self.ln_mean[2 * l + 1], self.ln_rstd[2 * l + 1], eps)
-            self._col_parallel(self._off_ln[l][1], self.w16(p + "fc_w"), self.fcg[l], bias=self.w32(p + "fc_b"),
-                               epilogue=K.EPI_GELU_DG, aux_out=self.fch[l])
+            self._col_parallel(self._off_ln[l][1], self.w16(p + "fc_w"), self.fcg[l], full=self._lnf(l, 1),
+                               bias=self.w32(p + "fc_b"), epilogue=K.EPI_GELU_DG, aux_out=self.fch[l])
             self._row_parallel(self.fcg[l], self.w16(p + "proj_w"), self.res[l + 1], bias=self.w32(p + "proj_b"),
                                residual=self.x2[l])
         K.layernorm_fwd(self.res[L], self.w32("lnf_w"), self.w32("lnf_b"), self.lnf, self.ln_mean[2 * L], self.ln_rstd[2 * L], eps)
@@ -300,30 +338,22 @@ class GPT2TPEngine:
         main = torch.cuda.current_stream()
         for l in reversed(range(L)):
             p = f"h{l}."
-            # ---- MLP: d(fc out) = (AG(dx) @ Wproj_r) * gelu' ; the gathered dx / ln2 arrive beside it for the wgrads ----
-            self._col_parallel(self._off_dx[cur], self.w16(p + "proj_w"), self.dfch, b_mn=True, epilogue=K.EPI_MUL,
-                               aux_in=self.fch[l], colsum=self.grad32(p + "fc_b"))
-            ev_dx = self._pull(self._off_dx[cur], self.full_a)
-            ev_ln = self._pull(self._off_ln[l][1], self.full_b)
-            main.wait_event(ev_dx)
+            # ---- MLP: d(fc out) = (AG(dx) @ Wproj_r) * gelu'; the gathered dx lands in full_a on the way and feeds the wgrad
+            self._col_parallel(self._off_dx[cur], self.w16(p + "proj_w"), self.dfch, full=self.full_a, b_mn=True,
+                               epilogue=K.EPI_MUL, aux_in=self.fch[l], colsum=self.grad32(p + "fc_b"))
             K.linear_wgrad(self.full_a, self.fcg[l], self.grad32(p + "proj_w"), split_k=0)
-            main.wait_event(ev_ln)
-            K.linear_wgrad(self.dfch, self.full_b, self.grad32(p + "fc_w"), split_k=0)
+            K.linear_wgrad(self.dfch, self._gathered_ln(l, 1), self.grad32(p + "fc_w"), split_k=0)
             self._row_parallel(self.dfch, self.w16(p + "fc_w"), self.dln_s, b_mn=True)
             K.layernorm_bwd(self.dln_s, self.x2[l], self.w32(p + "ln2_w"), self.ln_mean[2 * l + 1], self.ln_rstd[2 * l + 1],
                             self.sym_dx[cur], self.sym_dx[cur ^ 1], self.grad32(p + "ln2_w"), self.grad32(p + "ln2_b"),
                             dxsum=self.grad32(p + "o_b"))
             cur ^= 1
             # ---- attention ----
-            self._col_parallel(self._off_dx[cur], self.w16(p + "o_w"), self.datty, b_mn=True)
-            ev_dx = self._pull(self._off_dx[cur], self.full_a)
-            ev_ln = self._pull(self._off_ln[l][0], self.full_b)
-            main.wait_event(ev_dx)
-            K.linear_wgrad(self.full_a, self.atty[l], self.grad32(p + "o_w"), split_k=0)
+            self._col_parallel(self._off_dx[cur], self.w16(p + "o_w"), self.datty, full=self.full_b, b_mn=True)
+            K.linear_wgrad(self.full_b, self.atty[l], self.grad32(p + "o_w"), split_k=0)
             K.attention_bwd(self.qkv[l], self.atty[l], self.datty, self.lse[l], self.delta, self.dqkv, self.B, self.T, self.Hl,
                             dbias=self.grad32(p + "qkv_b"))
-            main.wait_event(ev_ln)
-            K.linear_wgrad(self.dqkv, self.full_b, self.grad32(p + "qkv_w"), split_k=0)
+            K.linear_wgrad(self.dqkv, self._gathered_ln(l, 0), self.grad32(p + "qkv_w"), split_k=0)
             self._row_parallel(self.dqkv, self.w16(p + "qkv_w"), self.dln_s, b_mn=True)
             K.layernorm_bwd(self.dln_s, self.res[l], self.w32(p + "ln1_w"), self.ln_mean[2 * l], self.ln_rstd[2 * l],
                             self.sym_dx[cur], self.sym_dx[cur ^ 1], self.grad32(p + "ln1_w"), self.grad32(p + "ln1_b"),
@@ -420,5 +450,5 @@ class GPT2TPEngine:
         W, L = self.world, self.L
         shard = self.Ms * self.C * 2
         ag = (W - 1) * shard                       # one all-gather / reduce-scatter of a [M, C] bf16 tensor
-        return {"k8_allgather_gemm": 4 * L * ag, "k7_gemm_scatter": 4 * L * ag, "wgrad_pulls": 4 * L * ag,
+        return {"k8_allgather_gemm": 4 * L * ag, "k7_gemm_scatter": 4 * L * ag, "wgrad_pulls": 0 if self.k8_flags else 4 * L * ag,
                 "replicated_grad_allreduce": 2 * (W - 1) / W * self.n_rep * 2}

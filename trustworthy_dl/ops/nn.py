@@ -111,3 +111,7 @@ def pack_norm(src32, dst16, sumsq, scale=None):
 
 def cast_f32_bf16(src, dst):
     _lib.call("tdl_cast_f32_bf16", ptr(src), ptr(dst), i64(src.numel()), stream_ptr())
+
+
+def cast_bf16_f32(src, dst):
+    _lib.call("tdl_cast_bf16_f32", ptr(src), ptr(dst), i64(src.numel()), stream_ptr())

@@ -130,10 +130,14 @@ class SymmetricTrustReducer:
         params = list(TRUST_PARAM_DEFAULTS)
         params[1], params[6], params[7], params[8] = trust_threshold, clip_ratio, norm_ratio_max, cosine_min
         self.params = (ctypes.c_float * 12)(*params)
-        # NVLS write-back (one multimem.st instead of W peer stores) only for whole-world groups: the multicast object
-        # spans every rank of the allocation.  TDL_TR_MULTIMEM=0 keeps the P2P stores.
-        self.use_multimem = (self.bucket.multicast_ptr != 0 and W == gworld and W > 1
-                             and os.environ.get("TDL_TR_MULTIMEM", "1") != "0")
+        # NVLS (multimem) paths exist only for whole-world groups: the multicast object spans every rank of the allocation.
+        # K4 (plain mean all-reduce) goes through the switch whenever it can (TDL_K4_MULTIMEM=0: P2P).  K2's write-back
+        # keeps W peer stores by default: the reduction already RECEIVES (W-1)/W of the bucket as load responses, and a
+        # multicast store loops the own slice back through the switch on top of that (RX (2W-1)/W vs 2(W-1)/W of the
+        # bucket), which measured slower at W = 2; TDL_TR_MULTIMEM=1 selects the single multimem.st.
+        has_mc = self.bucket.multicast_ptr != 0 and W == gworld and W > 1
+        self.use_multimem = has_mc and os.environ.get("TDL_TR_MULTIMEM", "0") == "1"
+        self.k4_multimem = has_mc and os.environ.get("TDL_K4_MULTIMEM", "1") != "0"
         self.set_group(self.ranks)
 
     # ---- group membership ------------------------------------------------------------------------
@@ -147,7 +151,9 @@ class SymmetricTrustReducer:
         self._bucket_ptrs = self.bucket.ptr_array(idx, self.arena_offset)
         self._pad_ptrs = self.pad.ptr_array(idx, self.pad_index * self.pad_words)
         self._my_pad = ctypes.c_void_p(self.pad.peer_ptrs[idx[self.rank]] + self.pad_index * self.pad_words * 8)
-        self._mc = ctypes.c_void_p(self.bucket.multicast_ptr + self.arena_offset * self.bucket.itemsize) if self.use_multimem else None
+        mc = ctypes.c_void_p(self.bucket.multicast_ptr + self.arena_offset * self.bucket.itemsize) if self.bucket.multicast_ptr else None
+        self._mc = mc if self.use_multimem else None
+        self._mc_k4 = mc if self.k4_multimem else None
         nvec = self.padded // self.vec
         per = nvec // self.world
         self.vec_begin, self.vec_end = self.rank * per, (self.rank + 1) * per
@@ -213,7 +219,7 @@ class SymmetricTrustReducer:
         numel = self.padded if numel is None else numel
         vb, ve = self.slice_of(begin, numel)
         self.barrier(0)                                               # every rank's bucket is packed
-        _lib.call("tdl_sum_allreduce", self._bucket_ptrs, self._mc, i32(W), i32(_lib.DTYPE_CODES[self.dtype]), i64(vb), i64(ve),
+        _lib.call("tdl_sum_allreduce", self._bucket_ptrs, self._mc_k4, i32(W), i32(_lib.DTYPE_CODES[self.dtype]), i64(vb), i64(ve),
                   f32(1.0 / W if scale is None else scale), i32(0), stream_ptr())
         self.barrier(1)
 

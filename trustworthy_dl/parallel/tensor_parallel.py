@@ -289,7 +289,9 @@ class TensorParallelStrategy:
         dtype = torch.bfloat16 if (c.dtype == "bf16" and self.device.type == "cuda") else torch.float32
         self.model = TPGPT2(base, self.rank, self.world).to(self.device, dtype)
         t.model_partitions[0] = self.model
-        if self.device.type == "cuda" and self.world > 1 and dist.get_backend() == "nccl" and dtype == torch.bfloat16:
+        import os
+        if (self.device.type == "cuda" and self.world > 1 and dist.get_backend() == "nccl" and dtype == torch.bfloat16
+                and os.environ.get("TDL_TP_FUSED", "1") != "0"):
             T = c.seq_len or base.config.n_positions
             rows = c.batch_size * T // self.world
             _FUSED = _FusedTP(rows, 4 * base.config.n_embd, self.device)
