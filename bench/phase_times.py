@@ -31,6 +31,7 @@ def main() -> int:
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--model", default="gpt2-medium")
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--zero", type=int, default=0, help="1 = ZeRO-1: sharded AdamW + integrity-checked parameter all-gather (K9)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -39,7 +40,7 @@ def main() -> int:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     cfg = GPT2Config(**GPT2_PRESETS[args.model])
     T = min(1024, cfg.n_positions)
-    eng = GPT2Engine(cfg, batch_size=args.batch, seq_len=T, lr=5e-5, device=dev, security=True, use_graph=False)
+    eng = GPT2Engine(cfg, batch_size=args.batch, seq_len=T, lr=5e-5, device=dev, security=True, use_graph=False, zero=args.zero)
     g = torch.Generator().manual_seed(rank)
     idx = torch.randint(0, cfg.vocab_size, (args.batch, T), generator=g).to(dev)
     eng.idx[0].copy_(idx); eng.tgt[0].copy_(idx)
@@ -80,7 +81,7 @@ def main() -> int:
                 K.pack_norm(eng.g32[seg.off:seg.off + seg.n], eng.bucket[seg.off:seg.off + seg.n], r.sumsq, eng.attack_scale)
                 sync()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(); r.enqueue_bucket(seg.off, seg.n); e1.record(); torch.cuda.synchronize()
+                e0.record(); r.enqueue_bucket(seg.off, seg.n, owner_only=bool(args.zero)); e1.record(); torch.cuda.synchronize()
                 ts.append(e0.elapsed_time(e1))
             red[i] = min(ts)
         r.enqueue_finalize(update_trust=False)
@@ -100,16 +101,17 @@ def main() -> int:
     if rank == 0:
         nk = len(keys)
         serial = sum(out[:nk])
-        print(f"world {world}, {args.model}, batch {args.batch} x {T}: ms, max over ranks, eager launches")
+        print(f"world {world}, {args.model}, batch {args.batch} x {T}, zero={args.zero}: ms, max over ranks, eager launches")
         for n, v in zip(keys, out[:nk]):
             print(f"  {n:64s} {v:8.3f}")
         print(f"  {'serial total':64s} {serial:8.3f}")
         print(f"  {'overlapped schedule, whole step':64s} {out[-1]:8.3f}   (hidden: {serial - out[-1]:.3f} ms)")
         if world > 1:
-            print("  trust-weighted reduction alone (exchange + coefficients + K2 + barrier), NVLink bytes per direction:")
+            print("  trust-weighted reduction alone (exchange + coefficients + K2 + barrier); NVLink bytes RECEIVED per rank =")
+            print("  load responses for its slice from W-1 peers" + ("" if args.zero else " + the W-1 reduced slices its peers store into it") + ":")
             tot_b, tot_t = 0.0, 0.0
             for i, seg in enumerate(eng.segments):
-                b = seg.n * 2 * (world - 1) / world
+                b = seg.n * 2 * (world - 1) / world * (1 if args.zero else 2)
                 t = out[nk + i] / 1e3
                 tot_b += b; tot_t += t
                 print(f"    seg{i}: {b / 1e6:8.1f} MB in {t * 1e3:7.3f} ms = {b / t / 1e9:6.1f} GB/s = {b / t / LINK_BYTES_PER_S:.2f} of link rate")

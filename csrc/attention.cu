@@ -20,7 +20,6 @@
 //   Roles inside a CTA: one TMA warp, one MMA-issue warp (elect.sync, precomputed descriptor words), 8 warps that only
 //   turn S into P (exp2), 8 warps that turn (P, dP) into dS and write finished tiles out through TMA stores (and add
 //   the qkv bias gradient).  S is double-buffered in TMEM; P / dS are written back into the S buffer they came from.
-//   (attn_bwd_kernel / attn_bwd_ws_kernel are the earlier generations, selectable with TDL_ATTN_BWD_WS=0 / 1.)
 // The reference reaches attention only through torch/HF eager ops.
 #include "common.cuh"
 #include <cstdlib>
@@ -279,659 +278,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p
     if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
 }
 
-// ---- variant with two threads per query row (256 threads, still 2 CTAs per SM) -------------------------------
-__global__ void __launch_bounds__(256, 2)
-attn_fwd_t2_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sQ = smem;
-    uint8_t* sK = smem + TILE_BYTES;              // 2 buffers
-    uint8_t* sV = smem + 3 * TILE_BYTES;          // 2 buffers
-    uint8_t* sP = smem + 5 * TILE_BYTES;          // [128 x 128] = 2 sub-tiles
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * TILE_BYTES);
-    uint64_t* bar_q = bars;
-    uint64_t* bar_kv = bars + 1;                  // [2]
-    uint64_t* bar_s = bars + 3;
-    uint64_t* bar_o = bars + 4;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
-    __half* s_max = reinterpret_cast<__half*>(bars + 6);  // [2 halves][128 rows] partial row maxima (fp16: 512 B keeps 2 CTAs/SM)
-    float* s_sum = reinterpret_cast<float*>(sP);          // epilogue only: P tile is dead by then
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    // heaviest (longest causal row) tiles first
-    const int qb = (gridDim.x - 1) - blockIdx.x;
-    const int h = blockIdx.y, b = blockIdx.z;
-    const int row0 = b * p.T;
-    const int n_kv = qb + 1;
-
-    if (tid == 0) {
-        if (smem_u32(smem) & 1023u) __trap();
-        tma_prefetch_desc(&tmap_qkv);
-        mbar_init(bar_q, 1); mbar_init(&bar_kv[0], 1); mbar_init(&bar_kv[1], 1);
-        mbar_init(bar_s, 1); mbar_init(bar_o, 1);
-        fence_barrier_init();
-    }
-    if (warp == 0) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-    const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
-    // 256 threads: two threads per query row.  Warp w reads TMEM lane quarter (w & 3); `half` = w >> 2 selects which
-    // 64 of the 128 score columns (and which 32 of the 64 output columns) the thread owns.  The only cross-thread
-    // quantity is the row maximum (exchanged through smem once per key block); the row sum is combined at the end.
-    const int quarter = warp & 3, half = warp >> 2;
-    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
-    const int r = quarter * 32 + lane;               // query row inside the tile
-
-    if (tid == 0) {
-        mbar_arrive_expect_tx(bar_q, TILE_BYTES);
-        tma_load_2d(sQ, &tmap_qkv, bar_q, h * D, row0 + qb * BQ);
-        mbar_arrive_expect_tx(&bar_kv[0], 2 * TILE_BYTES);
-        tma_load_2d(sK, &tmap_qkv, &bar_kv[0], p.C + h * D, row0);
-        tma_load_2d(sV, &tmap_qkv, &bar_kv[0], 2 * p.C + h * D, row0);
-    }
-
-    const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-    const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-    float o_acc[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) o_acc[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
-
-    // S(j+1) = Q K_{j+1}^T is queued on the tensor pipe right behind P_j V_j (the S accumulator is already in
-    // registers by then), so the next block's scores are ready when the softmax warps come back for them.
-    auto issue_s = [&](int jj) {                     // thread 0 only
-        const int b2 = jj & 1;
-        mbar_wait(&bar_kv[b2], (jj >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-            umma_bf16_ss(tmem_s, desc_kmajor(sQ, k), desc_kmajor(sK + b2 * TILE_BYTES, k), idesc_s, k > 0);
-        umma_commit(bar_s);
-    };
-    if (tid == 0) { mbar_wait(bar_q, 0); issue_s(0); }
-    for (int j = 0; j < n_kv; ++j) {
-        const int buf = j & 1;
-        if (tid == 0 && j + 1 < n_kv) {              // prefetch next K/V into the other buffer
-            mbar_arrive_expect_tx(&bar_kv[buf ^ 1], 2 * TILE_BYTES);
-            tma_load_2d(sK + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], p.C + h * D, row0 + (j + 1) * BK);
-            tma_load_2d(sV + (buf ^ 1) * TILE_BYTES, &tmap_qkv, &bar_kv[buf ^ 1], 2 * p.C + h * D, row0 + (j + 1) * BK);
-        }
-        mbar_wait(bar_s, j & 1);
-        __syncwarp();
-        tc_fence_after();
-
-        // ---- online softmax: this thread's 64 columns of its row, held in registers ----------------
-        const bool diag = (j == qb);
-        uint32_t sraw[64];
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-            tmem_ld_32x32(tmem_s + lane_base + half * 64 + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
-        tmem_ld_wait();
-        if (diag) {                                  // causal mask only in the diagonal block (warp-uniform branch)
-#pragma unroll
-            for (int i = 0; i < 64; ++i) if (half * 64 + i > r) sraw[i] = 0xff800000u;     // -inf
-        }
-        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-        for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-        // both threads of a row must use the SAME maximum: each rounds its partial up to fp16 and both take the max
-        // of the two rounded values (softmax is shift-invariant, so the rounding itself is harmless)
-        const __half mh = __float2half_ru(fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
-        s_max[half * 128 + r] = mh;
-        __syncthreads();                             // (also: everyone has pulled S out of TMEM)
-        const float mraw = fmaxf(__half2float(mh), __half2float(s_max[(half ^ 1) * 128 + r]));
-        const float mx = fmaxf(m_run, mraw * p.scale_log2);
-        const float alpha = exp2f(m_run - mx);
-        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            float pv[32];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float e = exp2f(fmaf(__uint_as_float(sraw[c * 32 + i]), p.scale_log2, -mx));   // exp2(-inf) = 0 under the mask
-                pv[i] = e;
-                rs4[i & 3] += e;
-            }
-            store_p_chunk(sP, r, half * 64 + c * 32, pv);
-        }
-        l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
-        m_run = mx;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[i] *= alpha;
-
-        fence_proxy_async_smem();                    // P (generic proxy) -> visible to the tensor core
-        tc_fence_before();
-        __syncthreads();
-        if (tid == 0) {
-            tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-                umma_bf16_ss(tmem_o, desc_kmajor(sP + (k >> 2) * TILE_BYTES, k & 3),
-                             desc_mnmajor(sV + buf * TILE_BYTES, k, TILE_BYTES), idesc_o, k > 0);
-            umma_commit(bar_o);
-            if (j + 1 < n_kv) issue_s(j + 1);
-        }
-        mbar_wait(bar_o, j & 1);
-        __syncwarp();
-        tc_fence_after();
-        {
-            uint32_t raw[32];
-            tmem_ld_32x32(tmem_o + lane_base + half * 32, raw);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) o_acc[i] += __uint_as_float(raw[i]);
-        }
-        tc_fence_before();
-    }
-
-    // ---- epilogue: combine the two half-row sums, normalise, store ---------------------------------
-    __syncthreads();
-    s_sum[half * 128 + r] = l_run;
-    __syncthreads();
-    const float l_tot = l_run + s_sum[(half ^ 1) * 128 + r];
-    const float inv = 1.0f / l_tot;
-    const long long grow = (long long)(row0 + qb * BQ + r);
-    __nv_bfloat16* orow = p.out + grow * p.C + h * D + half * 32;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint4 u;
-        u.x = pack_bf16x2(o_acc[q * 8 + 0] * inv, o_acc[q * 8 + 1] * inv); u.y = pack_bf16x2(o_acc[q * 8 + 2] * inv, o_acc[q * 8 + 3] * inv);
-        u.z = pack_bf16x2(o_acc[q * 8 + 4] * inv, o_acc[q * 8 + 5] * inv); u.w = pack_bf16x2(o_acc[q * 8 + 6] * inv, o_acc[q * 8 + 7] * inv);
-        *reinterpret_cast<uint4*>(orow + q * 8) = u;
-    }
-    if (half == 0) p.lse[((long long)b * p.H + h) * p.T + qb * BQ + r] = (m_run + log2f(l_tot)) * 0.6931471805599453f;
-
-    __syncthreads();
-    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
-}
-
-// =================================================================================================
-// forward, warp-specialised ping-pong version (used when T/128 is even)
-//
-// One CTA (320 threads, 1 per SM) owns TWO adjacent query tiles of one head (blocks 2i and 2i+1): both tiles share
-// every K/V block the CTA loads and have nearly equal causal work, so the two warpgroups stay busy together.
-//   warps 0-3  softmax warpgroup of tile A          warps 4-7  softmax warpgroup of tile B
-//   warp 8     MMA issuer (one lane)                warp 9     TMA producer (one lane)
-// While one warpgroup runs exp on its scores the tensor core computes the other tile's S = QK^T and PV, and
-// S_t(j+1) is issued as soon as the warpgroup has pulled S_t(j) into registers.  O accumulates in TMEM across
-// key blocks (tcgen05.mma accumulate); the running max is only refreshed when it grows by more than 2^8
-// ("lazy rescale"), in which case the warpgroup scales its O tile in TMEM (tcgen05.ld / st) before the next PV.
-// TMEM: S_A [0,128) S_B [128,256) O_A [256,320) O_B [320,384).  smem: Q x2, 3 K/V stages, P x2 = 192 KB.
-// =================================================================================================
-constexpr int WS_NST = 3;
-constexpr int WS_THREADS = 384;                // 2 softmax warpgroups + 1 helper warpgroup (MMA warp, TMA warp, 2 idle)
-
-__global__ void __launch_bounds__(WS_THREADS, 1)
-attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnParams p) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sQ = smem;                                   // [2] tiles
-    uint8_t* sKV = smem + 2 * TILE_BYTES;                 // [WS_NST][K | V]
-    uint8_t* sP = smem + (2 + 2 * WS_NST) * TILE_BYTES;   // [2][128 x 128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 + 2 * WS_NST + 4) * TILE_BYTES);
-    uint64_t* q_full = bars;
-    uint64_t* kv_full = bars + 1;
-    uint64_t* kv_empty = bars + 1 + WS_NST;
-    uint64_t* s_full = bars + 1 + 2 * WS_NST;
-    uint64_t* s_free = s_full + 2;
-    uint64_t* p_full = s_free + 2;
-    uint64_t* o_done = p_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nblk = p.T / 128;
-    // adjacent query blocks share a CTA: both warpgroups then have (almost) the same number of key blocks, so neither
-    // idles while the other finishes; CTAs differ in length instead and are launched longest-first
-    const int pi = (gridDim.x - 1) - blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-    const int qblk0 = 2 * pi, qblk1 = 2 * pi + 1;         // tile A / tile B query blocks
-    const int nkv0 = qblk0 + 1, nkv1 = qblk1 + 1;         // causal key-block counts
-    const int nmax = nkv1;
-    (void)nblk;
-    const int row0 = b * p.T;
-
-    if (tid == 0) {
-        if (smem_u32(smem) & 1023u) __trap();
-        tma_prefetch_desc(&tmap_qkv);
-        mbar_init(q_full, 1);
-        for (int s2 = 0; s2 < WS_NST; ++s2) { mbar_init(&kv_full[s2], 1); mbar_init(&kv_empty[s2], 1); }
-        for (int t = 0; t < 2; ++t) { mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 4); mbar_init(&p_full[t], 4); mbar_init(&o_done[t], 1); }
-        fence_barrier_init();
-    }
-    if (warp == 8) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-    // Register redistribution: the helper warpgroup gives most of its registers to the two softmax warpgroups,
-    // which can then keep a whole 128-column score row in registers (single TMEM pass, early release of S).
-    if (warp >= 8) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
-    if (warp == 9) {
-        // ===================================== TMA producer =====================================
-        if (lane == 0) {
-            mbar_arrive_expect_tx(q_full, 2 * TILE_BYTES);
-            tma_load_2d(sQ, &tmap_qkv, q_full, h * D, row0 + qblk0 * 128);
-            tma_load_2d(sQ + TILE_BYTES, &tmap_qkv, q_full, h * D, row0 + qblk1 * 128);
-            for (int j = 0; j < nmax; ++j) {
-                const int st = j % WS_NST;
-                mbar_wait(&kv_empty[st], ((j / WS_NST) & 1) ^ 1);
-                mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
-                tma_load_2d(sKV + st * 2 * TILE_BYTES, &tmap_qkv, &kv_full[st], p.C + h * D, row0 + j * 128);
-                tma_load_2d(sKV + st * 2 * TILE_BYTES + TILE_BYTES, &tmap_qkv, &kv_full[st], 2 * p.C + h * D, row0 + j * 128);
-            }
-        }
-    } else if (warp == 8) {
-        // ===================================== MMA issuer ========================================
-        if (lane == 0) {
-            const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-            const uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-            auto issue_s = [&](int t, int j) {
-                const uint8_t* kt = sKV + (j % WS_NST) * 2 * TILE_BYTES;
-#pragma unroll
-                for (int k = 0; k < D / 16; ++k)
-                    umma_bf16_ss(tmem + t * 128, desc_kmajor(sQ + t * TILE_BYTES, k), desc_kmajor(kt, k), idesc_s, k > 0);
-                umma_commit(&s_full[t]);
-            };
-            auto issue_pv = [&](int t, int j) {
-                const uint8_t* vt = sKV + (j % WS_NST) * 2 * TILE_BYTES + TILE_BYTES;
-                const uint8_t* pt = sP + t * 2 * TILE_BYTES;
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_bf16_ss(tmem + 256 + t * 64, desc_kmajor(pt + (k >> 2) * TILE_BYTES, k & 3),
-                                 desc_mnmajor(vt, k, TILE_BYTES), idesc_o, (j > 0 || k > 0));
-                umma_commit(&o_done[t]);
-            };
-            mbar_wait(q_full, 0);
-            mbar_wait(&kv_full[0], 0);
-            tc_fence_after();
-            issue_s(0, 0);
-            issue_s(1, 0);
-            // Event-driven issue: whichever tile has something ready (its S row has been pulled out of TMEM, or its
-            // P tile has been written) is served first, so the two warpgroups genuinely alternate instead of marching
-            // in lock-step behind one blocking wait.
-            int js[2] = {1, 1};                                  // next S block to issue per tile
-            int jp[2] = {0, 0};                                  // next PV block to issue per tile
-            const int nt[2] = {nkv0, nkv1};
-            int kv_ready = 1;                                    // K/V blocks known to have landed
-            while (jp[0] < nt[0] || jp[1] < nt[1]) {
-#pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    if (js[t] < nt[t]) {
-                        const int j = js[t];
-                        if (kv_ready <= j && mbar_try_wait(&kv_full[j % WS_NST], (j / WS_NST) & 1)) kv_ready = j + 1;
-                        if (kv_ready > j && mbar_try_wait(&s_free[t], (j - 1) & 1)) {
-                            tc_fence_after();
-                            issue_s(t, j);
-                            ++js[t];
-                        }
-                    }
-                    if (jp[t] < nt[t] && mbar_try_wait(&p_full[t], jp[t] & 1)) {
-                        const int j = jp[t];
-                        tc_fence_after();
-                        issue_pv(t, j);
-                        ++jp[t];
-                        const int o = t ^ 1;
-                        if (jp[o] > j || nt[o] <= j) umma_commit(&kv_empty[j % WS_NST]);   // both tiles are past block j
-                    }
-                }
-            }
-        }
-    }
-    } else {
-        // ===================================== softmax warpgroups ================================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;" ::: "memory");
-        const int t = warp >> 2;
-        const int r = (warp & 3) * 32 + lane;
-        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-        const uint32_t tmem_s = tmem + t * 128, tmem_o = tmem + 256 + t * 64;
-        uint8_t* myP = sP + t * 2 * TILE_BYTES;
-        float m_ref = -INFINITY, l_run = 0.f;
-        const int n = t == 0 ? nkv0 : nkv1;
-        const int my_qblk = t == 0 ? qblk0 : qblk1;
-        for (int j = 0; j < n; ++j) {
-            const bool diag = (j == n - 1);
-            mbar_wait(&s_full[t], j & 1);
-            __syncwarp();
-            tc_fence_after();
-            // whole S row -> registers in one round of TMEM loads, then hand S back to the tensor core at once
-            uint32_t sraw[128];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) tmem_ld_32x32(tmem_s + lane_base + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_free[t]);              // S_t(j+1) may be issued while we do the exponentials
-            if (diag) {
-#pragma unroll
-                for (int i = 0; i < 128; ++i) if (i > r) sraw[i] = 0xff800000u;
-            }
-            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-            for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(sraw[i]));
-            const float m_blk = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2;
-            float alpha = 1.f;
-            if (m_blk > m_ref + 8.f) { alpha = exp2f(m_ref - m_blk); m_ref = m_blk; }   // lazy: p stays <= 2^8 otherwise
-            const bool any_rescale = __any_sync(0xffffffffu, alpha != 1.f);
-            float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-            for (int i = 0; i < 128; ++i) {
-                const float e = exp2f(fmaf(__uint_as_float(sraw[i]), p.scale_log2, -m_ref));
-                sraw[i] = __float_as_uint(e);
-                rs4[i & 3] += e;
-            }
-            l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
-            if (j > 0) {                                         // PV_t(j-1) must be done before P / O are touched
-                mbar_wait(&o_done[t], (j - 1) & 1);
-                __syncwarp();
-                tc_fence_after();
-                if (any_rescale) {
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t o[32];
-                        tmem_ld_32x32(tmem_o + lane_base + c * 32, o);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                        tmem_st_32x32(tmem_o + lane_base + c * 32, o);
-                    }
-                    tmem_st_wait();
-                }
-            }
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float pv[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) pv[i] = __uint_as_float(sraw[c * 32 + i]);
-                store_p_chunk(myP, r, c * 32, pv);
-            }
-            fence_proxy_async_smem();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[t]);
-        }
-        // ---- epilogue: O_t / l -> bf16, logsumexp ------------------------------------------------
-        mbar_wait(&o_done[t], (n - 1) & 1);
-        __syncwarp();
-        tc_fence_after();
-        const float inv = 1.0f / l_run;
-        const long long grow = (long long)(row0 + my_qblk * 128 + r);
-        __nv_bfloat16* orow = p.out + grow * p.C + h * D;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            uint32_t o[32];
-            tmem_ld_32x32(tmem_o + lane_base + c * 32, o);
-            tmem_ld_wait();
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint4 u;
-                u.x = pack_bf16x2(__uint_as_float(o[q * 8 + 0]) * inv, __uint_as_float(o[q * 8 + 1]) * inv);
-                u.y = pack_bf16x2(__uint_as_float(o[q * 8 + 2]) * inv, __uint_as_float(o[q * 8 + 3]) * inv);
-                u.z = pack_bf16x2(__uint_as_float(o[q * 8 + 4]) * inv, __uint_as_float(o[q * 8 + 5]) * inv);
-                u.w = pack_bf16x2(__uint_as_float(o[q * 8 + 6]) * inv, __uint_as_float(o[q * 8 + 7]) * inv);
-                *reinterpret_cast<uint4*>(orow + c * 32 + q * 8) = u;
-            }
-        }
-        p.lse[((long long)b * p.H + h) * p.T + my_qblk * 128 + r] = (m_ref + log2f(l_run)) * 0.6931471805599453f;
-        tc_fence_before();
-    }
-    __syncthreads();
-    if (warp == 8) { tc_fence_after(); tmem_dealloc(tmem, 512); }
-}
-
-// =================================================================================================
-// backward preprocess: delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]
-// =================================================================================================
-__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
-                                                         float* __restrict__ delta, int B, int T, int H) {
-    // 8 threads per (row, head): each handles 8 of the 64 elements
-    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long item = gid >> 3;
-    const int part = gid & 7;
-    const long long total = (long long)B * T * H;
-    float acc = 0.f;
-    if (item < total) {
-        const long long row = item / H;
-        const int h = item % H;
-        const long long off = row * (long long)(H * D) + h * D + part * 8;
-        const uint4 a = *reinterpret_cast<const uint4*>(o + off), g = *reinterpret_cast<const uint4*>(d_o + off);
-        const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
-        const float2 g0 = unpack_bf16x2(g.x), g1 = unpack_bf16x2(g.y), g2 = unpack_bf16x2(g.z), g3 = unpack_bf16x2(g.w);
-        acc = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y + a2.x * g2.x + a2.y * g2.y + a3.x * g3.x + a3.y * g3.y;
-    }
-    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-    if (item < total && part == 0) {
-        const long long row = item / H;
-        const int h = item % H;
-        const int b = row / T, t = row % T;
-        delta[((long long)b * H + h) * T + t] = acc;
-    }
-}
-
-// =================================================================================================
-// backward main kernels.  MODE 0: dK/dV (outer tile = key block, inner loop over query blocks)
-//                         MODE 1: dQ    (outer tile = query block, inner loop over key blocks)
-// smem: fixed pair (2 tiles) | streamed pair x2 (4 tiles) | P (2 tiles) | dS (2 tiles)  = 160 KB
-// TMEM: S [0,128) dP [128,256) acc0 [256,320) acc1 [320,384)
-// =================================================================================================
-template <int MODE>
-__global__ void __launch_bounds__(256, 1)
-attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const AttnParams p) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sFix0 = smem;                         // MODE0: K   MODE1: Q
-    uint8_t* sFix1 = smem + TILE_BYTES;            // MODE0: V   MODE1: dO
-    uint8_t* sStr = smem + 2 * TILE_BYTES;         // [buf][2] : MODE0: Q,dO   MODE1: K,V
-    uint8_t* sP = smem + 6 * TILE_BYTES;
-    uint8_t* sdS = smem + 8 * TILE_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 10 * TILE_BYTES);
-    uint64_t* bar_fix = bars;
-    uint64_t* bar_str = bars + 1;                  // [2]
-    uint64_t* bar_s = bars + 3;
-    uint64_t* bar_acc = bars + 4;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
-
-    const int tid = threadIdx.x, warp = tid >> 5;
-    const int nblk = p.T / 128;
-    const int ob = MODE == 0 ? blockIdx.x : (gridDim.x - 1) - blockIdx.x;      // outer block index
-    const int h = blockIdx.y, b = blockIdx.z;
-    const int row0 = b * p.T;
-    const int i_begin = MODE == 0 ? ob : 0;
-    const int i_end = MODE == 0 ? nblk : ob + 1;
-
-    if (tid == 0) {
-        if (smem_u32(smem) & 1023u) __trap();
-        tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do);
-        mbar_init(bar_fix, 1); mbar_init(&bar_str[0], 1); mbar_init(&bar_str[1], 1);
-        mbar_init(bar_s, 1); mbar_init(bar_acc, 1);
-        fence_barrier_init();
-    }
-    if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-    const uint32_t tmem_s = tmem, tmem_dp = tmem + 128, tmem_a0 = tmem + 256, tmem_a1 = tmem + 320;
-    // 256 threads: two threads per tile row — warp w reads TMEM lane quarter (w & 3) and owns column half
-    // (w >> 2) of the 128-wide S / dP rows (P and dS are element-wise, so no cross-thread reduction).
-    const int quarter = warp & 3, half = warp >> 2;
-    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
-
-    auto load_stream = [&](int i, int buf) {      // called by thread 0
-        uint8_t* s0 = sStr + buf * 2 * TILE_BYTES;
-        mbar_arrive_expect_tx(&bar_str[buf], 2 * TILE_BYTES);
-        if (MODE == 0) {
-            tma_load_2d(s0, &tmap_qkv, &bar_str[buf], h * D, row0 + i * 128);                  // Q_i
-            tma_load_2d(s0 + TILE_BYTES, &tmap_do, &bar_str[buf], h * D, row0 + i * 128);      // dO_i
-        } else {
-            tma_load_2d(s0, &tmap_qkv, &bar_str[buf], p.C + h * D, row0 + i * 128);            // K_i
-            tma_load_2d(s0 + TILE_BYTES, &tmap_qkv, &bar_str[buf], 2 * p.C + h * D, row0 + i * 128);   // V_i
-        }
-    };
-    if (tid == 0) {
-        mbar_arrive_expect_tx(bar_fix, 2 * TILE_BYTES);
-        if (MODE == 0) {
-            tma_load_2d(sFix0, &tmap_qkv, bar_fix, p.C + h * D, row0 + ob * 128);              // K
-            tma_load_2d(sFix1, &tmap_qkv, bar_fix, 2 * p.C + h * D, row0 + ob * 128);          // V
-        } else {
-            tma_load_2d(sFix0, &tmap_qkv, bar_fix, h * D, row0 + ob * 128);                    // Q
-            tma_load_2d(sFix1, &tmap_do, bar_fix, h * D, row0 + ob * 128);                     // dO
-        }
-        load_stream(i_begin, 0);
-    }
-
-    const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
-    const uint32_t idesc_kv = umma_idesc_bf16(128, 64, 1, 1);       // dV, dK: MN-major A x MN-major B
-    const uint32_t idesc_dq = umma_idesc_bf16(128, 64, 0, 1);       // dQ    : K-major A x MN-major B
-    const int r = quarter * 32 + (tid & 31);
-    // MODE 1: this thread's query row is fixed for the whole kernel
-    float lse2_fix = 0.f, delta_fix = 0.f;
-    if (MODE == 1) {
-        const long long idx = ((long long)b * p.H + h) * p.T + ob * 128 + r;
-        lse2_fix = p.lse[idx] * 1.4426950408889634f;
-        delta_fix = p.delta[idx];
-    }
-
-    // S and dP of iteration it+1 are queued right behind the accumulate-MMAs of iteration it (thread 0 only)
-    auto issue_sdp = [&](int it2) {
-        const int b2 = it2 & 1;
-        uint8_t* q0 = sStr + b2 * 2 * TILE_BYTES;
-        const uint8_t* xQ = MODE == 0 ? q0 : sFix0;
-        const uint8_t* xdO = MODE == 0 ? q0 + TILE_BYTES : sFix1;
-        const uint8_t* xK = MODE == 0 ? sFix0 : q0;
-        const uint8_t* xV = MODE == 0 ? sFix1 : q0 + TILE_BYTES;
-        mbar_wait(&bar_str[b2], (it2 >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_s, desc_kmajor(xQ, k), desc_kmajor(xK, k), idesc_s, k > 0);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_bf16_ss(tmem_dp, desc_kmajor(xdO, k), desc_kmajor(xV, k), idesc_s, k > 0);
-        umma_commit(bar_s);
-    };
-    int it = 0;
-    for (int i = i_begin; i < i_end; ++i, ++it) {
-        const int buf = it & 1;
-        uint8_t* s0 = sStr + buf * 2 * TILE_BYTES;
-        uint8_t* s1 = s0 + TILE_BYTES;
-        // operand roles for this iteration
-        const uint8_t* tQ = MODE == 0 ? s0 : sFix0;
-        const uint8_t* tdO = MODE == 0 ? s1 : sFix1;
-        const uint8_t* tK = MODE == 0 ? sFix0 : s0;
-        const uint8_t* tV = MODE == 0 ? sFix1 : s1;
-        if (tid == 0 && it == 0) { mbar_wait(bar_fix, 0); issue_sdp(0); }
-        // the previous iteration's accumulate-MMAs must be done before P/dS (and the other stream
-        // buffer) are overwritten
-        if (it > 0) { mbar_wait(bar_acc, (it - 1) & 1); tc_fence_after(); }
-        if (tid == 0 && i + 1 < i_end) load_stream(i + 1, buf ^ 1);
-
-        const int qblk = MODE == 0 ? i : ob, kblk = MODE == 0 ? ob : i;
-        const bool diag = (qblk == kblk);
-        float lse2 = lse2_fix, dlt = delta_fix;
-        if (MODE == 0) {
-            const long long idx = ((long long)b * p.H + h) * p.T + i * 128 + r;
-            lse2 = p.lse[idx] * 1.4426950408889634f;
-            dlt = p.delta[idx];
-        }
-        mbar_wait(bar_s, it & 1);
-        __syncwarp();
-        tc_fence_after();
-#pragma unroll
-        for (int c = half * 2; c < half * 2 + 2; ++c) {
-            uint32_t rs_[32], rd_[32];
-            tmem_ld_32x32(tmem_s + lane_base + c * 32, rs_);
-            tmem_ld_32x32(tmem_dp + lane_base + c * 32, rd_);
-            tmem_ld_wait();
-            if (diag) {                                   // causal mask only in the diagonal block (warp-uniform)
-#pragma unroll
-                for (int k = 0; k < 32; ++k) if ((c * 32 + k) > r) rs_[k] = 0xff800000u;   // -inf -> P = 0
-            }
-            float pv[32], dsv[32];
-#pragma unroll
-            for (int k = 0; k < 32; ++k) {
-                const float e = exp2f(fmaf(__uint_as_float(rs_[k]), p.scale_log2, -lse2));
-                pv[k] = e;
-                dsv[k] = e * (__uint_as_float(rd_[k]) - dlt);
-            }
-            if (MODE == 0) store_p_chunk(sP, r, c * 32, pv);
-            store_p_chunk(sdS, r, c * 32, dsv);
-        }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        __syncthreads();
-        if (tid == 0) {
-            tc_fence_after();
-            if (MODE == 0) {
-                // dV[k, d] += sum_q P[q, k] dO[q, d] ;  dK[k, d] += sum_q dS[q, k] Q[q, d]   (K dim = 128 queries)
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_bf16_ss(tmem_a0, desc_mnmajor(sP, k, TILE_BYTES), desc_mnmajor(tdO, k, TILE_BYTES), idesc_kv, (it > 0 || k > 0));
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_bf16_ss(tmem_a1, desc_mnmajor(sdS, k, TILE_BYTES), desc_mnmajor(tQ, k, TILE_BYTES), idesc_kv, (it > 0 || k > 0));
-            } else {
-                // dQ[q, d] += sum_k dS[q, k] K[k, d]     (K dim = 128 keys)
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_bf16_ss(tmem_a0, desc_kmajor(sdS + (k >> 2) * TILE_BYTES, k & 3), desc_mnmajor(tK, k, TILE_BYTES), idesc_dq, (it > 0 || k > 0));
-            }
-            umma_commit(bar_acc);
-            if (i + 1 < i_end) issue_sdp(it + 1);
-        }
-    }
-    // ---- write the accumulators ------------------------------------------------------------------
-    mbar_wait(bar_acc, (it - 1) & 1);
-    __syncwarp();
-    tc_fence_after();
-    const long long grow = (long long)(row0 + ob * 128 + r);
-    auto write_acc = [&](uint32_t taddr, __nv_bfloat16* dst, float mul, float* dbias) {
-        {
-            const int c = half;                    // each of the two row threads writes 32 of the 64 columns
-            uint32_t raw[32];
-            tmem_ld_32x32(taddr + lane_base + c * 32, raw);
-            tmem_ld_wait();
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint4 u;
-                u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
-                u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
-                u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
-                u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
-                *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
-            }
-            if (dbias != nullptr) {
-                // qkv bias gradient: column sums of the (bf16-rounded) tile.  Transposing butterfly over the warp's
-                // 32 rows: after the 5 rounds lane l holds the sum of column l of this thread's 32-column half.
-                const int lane = threadIdx.x & 31;
-                float v[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j]) * mul));
-#pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) {
-                    const bool up = (lane & off) != 0;
-#pragma unroll
-                    for (int j = 0; j < off; ++j) {
-                        const float send = up ? v[j] : v[j + off];
-                        const float keep = up ? v[j + off] : v[j];
-                        v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-                    }
-                }
-                atomicAdd(dbias + c * 32 + lane, v[0]);
-            }
-        }
-    };
-    __nv_bfloat16* base = p.dqkv + grow * (3LL * p.C) + h * D;
-    float* db = p.dbias != nullptr ? p.dbias + h * D : nullptr;
-    if (MODE == 0) {
-        write_acc(tmem_a1, base + p.C, p.scale, db ? db + p.C : nullptr);          // dK
-        write_acc(tmem_a0, base + 2 * p.C, 1.0f, db ? db + 2 * p.C : nullptr);     // dV
-    } else {
-        write_acc(tmem_a0, base, p.scale, db);                                     // dQ
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
-}
-
 // =================================================================================================
 // backward: persistent, software-pipelined, P / dS kept in tensor memory (default).
 // Same math as attn_bwd_kernel, restructured around what bounded it there:
@@ -977,432 +323,6 @@ __device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[8]
 
 __device__ __forceinline__ void named_bar_math(int id) {          // barrier among the math warps only
     asm volatile("bar.sync %0, %1;" :: "r"(id), "n"(BWD_WS_MATH) : "memory");
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(BWD_WS_THREADS, 1)
-attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
-                   const __grid_constant__ CUtensorMap tmap_dqkv, const __grid_constant__ CUtensorMap tmap_o, const AttnParams p) {
-    constexpr int NSTR = BWD_WS_NSTR, NFIX = BWD_WS_NFIX;
-    constexpr int CW = 128 / BWD_WS_NCG;           // S / dP columns per math thread
-    TRACE_DECL;
-    extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sFix = smem;                                   // [NFIX][2] : MODE0: K,V   MODE1: Q,dO
-    uint8_t* sStr = smem + 2 * NFIX * TILE_BYTES;           // [NSTR][2] : MODE0: Q,dO  MODE1: K,V
-    uint8_t* sOut = smem + (2 * NFIX + 2 * NSTR) * TILE_BYTES;                                  // [2] finished dK,dV / dQ tiles
-    float* sStat = reinterpret_cast<float*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES);     // [2][2][128]: lse*log2e, delta (MODE 0)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 * NFIX + 2 * NSTR + 2) * TILE_BYTES + 2048);
-    uint64_t* fix_full = bars;                     // [<= 3]
-    uint64_t* fix_empty = bars + 3;                // [<= 3]
-    uint64_t* str_full = bars + 6;                 // [4]
-    uint64_t* str_empty = bars + 10;               // [4]
-    uint64_t* s_full = bars + 14;                  // [2]
-    uint64_t* dp_full = bars + 16;
-    uint64_t* dp_free = bars + 17;
-    uint64_t* p_full = bars + 18;                  // [2]
-    uint64_t* acc_done = bars + 20;                // [2]
-    uint64_t* acc_free = bars + 22;
-    uint64_t* o_full = bars + 23;                  // MODE 1: the tile's O rows landed (for delta = rowsum(dO * O))
-    uint64_t* o_free = bars + 24;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nblk = p.T / 128;
-    const int BH = p.B * p.H;
-    const int total = nblk * BH;
-    // Tile order: (batch, head) pairs in chunks of p.bwd_chunk whose Q/K/V/dO fit in L2; inside a chunk longest tiles
-    // first.  CTA c takes tiles c, c + gridDim.x, ...: the chunk size is not a multiple of the grid, so which CTA gets
-    // the long tiles rotates from chunk to chunk.
-    const int CH = p.bwd_chunk;
-    auto fdiv = [](int n, unsigned long long magic) { return (int)(((unsigned long long)(unsigned)n * magic) >> 40); };
-    auto cur_decode = [&](BwdCursor& c) {                     // runs when a cursor enters a new tile; no hardware division
-        if (c.t >= total) { c.n = 0; return; }
-        const int chunk = fdiv(c.t, p.mg_tile);               // t / (nblk * CH); CH divides B*H
-        const int tl = c.t - chunk * nblk * CH;
-        const int rank = fdiv(tl, p.mg_chunk);                // tl / CH
-        const int bh = chunk * CH + tl - rank * CH;
-        c.ob = MODE == 0 ? rank : nblk - 1 - rank;
-        c.n = MODE == 0 ? nblk - c.ob : c.ob + 1;
-        c.b = fdiv(bh, p.mg_head);                            // bh / H
-        c.h = bh - c.b * p.H;
-    };
-    auto cur_init = [&]() {
-        BwdCursor c; c.t = blockIdx.x; c.k = 0; c.it = 0; c.j = 0; c.ob = c.h = c.b = 0;
-        cur_decode(c);
-        return c;
-    };
-    auto cur_next = [&](BwdCursor& c) {
-        ++c.j;
-        if (++c.it == c.n) { c.it = 0; c.t += gridDim.x; ++c.k; cur_decode(c); }
-    };
-
-    if (tid == 0) {
-        if (smem_u32(smem) & 1023u) __trap();
-        tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); tma_prefetch_desc(&tmap_dqkv);
-        for (int s = 0; s < NFIX; ++s) { mbar_init(&fix_full[s], 1); mbar_init(&fix_empty[s], 1); }
-        for (int s = 0; s < NSTR; ++s) { mbar_init(&str_full[s], 1); mbar_init(&str_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], BWD_WS_MATH / 32); mbar_init(&acc_done[s], 1); }
-        mbar_init(dp_full, 1); mbar_init(dp_free, BWD_WS_MATH / 32); mbar_init(acc_free, BWD_WS_MATH / 32);
-        mbar_init(o_full, 1); mbar_init(o_free, BWD_WS_MATH / 32);
-        fence_barrier_init();
-    }
-    if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-    const uint32_t tmem_dp = tmem + 256, tmem_a0 = tmem + 384, tmem_a1 = tmem + 448;
-    pdl_enter();                                     // global memory is touched only below
-
-    if (warp == BWD_WS_MATH / 32 + 1) {
-        // ======================================= TMA producer ====================================
-        if (lane == 0) {
-            for (BwdCursor c = cur_init(); c.t < total; cur_next(c)) {
-                const int ob = c.ob, h = c.h;
-                const int row0 = c.b * p.T;
-                if (c.it == 0) {
-                    const int fb = c.k % NFIX;
-                    if (c.k >= NFIX) mbar_wait(&fix_empty[fb], ((c.k / NFIX) - 1) & 1);
-                    uint8_t* f0 = sFix + fb * 2 * TILE_BYTES;
-                    mbar_arrive_expect_tx(&fix_full[fb], 2 * TILE_BYTES);
-                    if (MODE == 0) {
-                        tma_load_2d(f0, &tmap_qkv, &fix_full[fb], p.C + h * D, row0 + ob * 128);                  // K
-                        tma_load_2d(f0 + TILE_BYTES, &tmap_qkv, &fix_full[fb], 2 * p.C + h * D, row0 + ob * 128); // V
-                    } else {
-                        tma_load_2d(f0, &tmap_qkv, &fix_full[fb], h * D, row0 + ob * 128);                        // Q
-                        tma_load_2d(f0 + TILE_BYTES, &tmap_do, &fix_full[fb], h * D, row0 + ob * 128);            // dO
-                        // O rows of the tile -> the staging tile MODE 1 does not use for output (single buffer)
-                        if (c.k >= 1) mbar_wait(o_free, (c.k - 1) & 1);
-                        mbar_arrive_expect_tx(o_full, TILE_BYTES);
-                        tma_load_2d(sOut + TILE_BYTES, &tmap_o, o_full, h * D, row0 + ob * 128);
-                    }
-                }
-                const int st = c.j % NSTR;
-                const int i = (MODE == 0 ? ob : 0) + c.it;
-                if (c.j >= NSTR) mbar_wait(&str_empty[st], ((c.j / NSTR) - 1) & 1);
-                uint8_t* s0 = sStr + st * 2 * TILE_BYTES;
-                mbar_arrive_expect_tx(&str_full[st], 2 * TILE_BYTES);
-                if (MODE == 0) {
-                    tma_load_2d(s0, &tmap_qkv, &str_full[st], h * D, row0 + i * 128);                  // Q_i
-                    tma_load_2d(s0 + TILE_BYTES, &tmap_do, &str_full[st], h * D, row0 + i * 128);      // dO_i
-                } else {
-                    tma_load_2d(s0, &tmap_qkv, &str_full[st], p.C + h * D, row0 + i * 128);            // K_i
-                    tma_load_2d(s0 + TILE_BYTES, &tmap_qkv, &str_full[st], 2 * p.C + h * D, row0 + i * 128);   // V_i
-                }
-            }
-        }
-        __syncwarp();
-    } else if (warp == BWD_WS_MATH / 32) {
-        // ======================================= MMA issue =======================================
-        // the whole warp walks the schedule and waits; one elected lane issues
-        {
-            const uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);       // S, dP : K-major x K-major
-            const uint32_t idesc_ts = umma_idesc_bf16(128, 64, 0, 1);       // acc   : A from TMEM (K along columns) x MN-major B
-            // K-slice k (16 values = 8 packed columns) of P lives in the S columns of the thread group that owns them
-            auto a_col = [](int k) { return (uint32_t)((k * 16 / CW) * CW + ((k * 16) % CW) / 2); };
-            // MODE 0: S^T = K Q_i^T, dP^T = V dO_i^T (keys on the lanes); MODE 1: S = Q K_i^T, dP = dO V_i^T
-            auto issue_s = [&](const BwdCursor& c) {
-                if (c.it == 0) mbar_wait(&fix_full[c.k % NFIX], (c.k / NFIX) & 1);
-                mbar_wait(&str_full[c.j % NSTR], (c.j / NSTR) & 1);
-                tc_fence_after();
-                const uint32_t a_lo = umma_desc_lo(smem_u32(sFix + (c.k % NFIX) * 2 * TILE_BYTES), 16);
-                const uint32_t b_lo = umma_desc_lo(smem_u32(sStr + (c.j % NSTR) * 2 * TILE_BYTES), 16);
-                if (elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < D / 16; ++k)      // K-major operands: 32 bytes (2 descriptor units) per K slice
-                        umma_bf16_ss_lo(tmem + (c.j & 1) * 128, a_lo + 2 * k, b_lo + 2 * k, idesc_s, k > 0);
-                    umma_commit(&s_full[c.j & 1]);
-                }
-                __syncwarp();
-            };
-            auto issue_dp = [&](const BwdCursor& c) {       // its fixed pair and stream stage were waited for by issue_s
-                const uint32_t a_lo = umma_desc_lo(smem_u32(sFix + (c.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES), 16);
-                const uint32_t b_lo = umma_desc_lo(smem_u32(sStr + (c.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES), 16);
-                if (elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < D / 16; ++k) umma_bf16_ss_lo(tmem_dp, a_lo + 2 * k, b_lo + 2 * k, idesc_s, k > 0);
-                    umma_commit(dp_full);
-                }
-                __syncwarp();
-            };
-            BwdCursor cs = cur_init(), cd = cur_init(), ca = cur_init();
-            if (cs.t < total) { issue_s(cs); cur_next(cs); }
-            if (cd.t < total) { issue_dp(cd); cur_next(cd); }
-            if (cs.t < total) { issue_s(cs); cur_next(cs); }
-            for (; ca.t < total; cur_next(ca)) {
-                const int bb = ca.j & 1;
-                const uint8_t* q0 = sStr + (ca.j % NSTR) * 2 * TILE_BYTES;
-                const uint32_t ts = tmem + bb * 128;
-                TRACE_AT(30);
-                mbar_wait(&p_full[bb], (ca.j >> 1) & 1);                // P / dS of this iteration sit in S[bb]
-                if (ca.it == 0 && ca.k > 0) mbar_wait(acc_free, (ca.k - 1) & 1);   // previous tile's accumulators were read out
-                const bool next_dp = cd.t < total;
-                if (next_dp) mbar_wait(dp_free, ca.j & 1);              // dP(j) has left TMEM (arrived before p_full)
-                tc_fence_after();
-                TRACE_AT(32);
-                // Back-to-back MMAs into the SAME accumulator are paced by the accumulate latency (~95 clk measured for
-                // N = 64), not by throughput, so the independent chains of this step -- dV, dK and the next block's dP --
-                // are issued round-robin.
-                const uint32_t accum = ca.it > 0;
-                // MN-major B tiles: 2048 bytes (128 descriptor units) per K slice; K-major dP operands: 32 bytes (2 units)
-                const uint32_t bq_lo = umma_desc_lo(smem_u32(q0), TILE_BYTES);                  // MODE 0: Q_i    MODE 1: K_i
-                const uint32_t bo_lo = umma_desc_lo(smem_u32(q0 + TILE_BYTES), TILE_BYTES);     // MODE 0: dO_i
-                const uint32_t pa_lo = umma_desc_lo(smem_u32(sFix + (cd.k % NFIX) * 2 * TILE_BYTES + TILE_BYTES), 16);
-                const uint32_t pb_lo = umma_desc_lo(smem_u32(sStr + (cd.j % NSTR) * 2 * TILE_BYTES + TILE_BYTES), 16);
-                if (elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        if (MODE == 0) {
-                            // dV[k, d] += sum_q P^T[k, q] dO[q, d] ;  dK[k, d] += sum_q dS^T[k, q] Q[q, d]
-                            umma_bf16_ts_lo(tmem_a0, ts + a_col(k), bo_lo + 128 * k, idesc_ts, (accum || k > 0));
-                            umma_bf16_ts_lo(tmem_a1, ts + a_col(k) + CW / 2, bq_lo + 128 * k, idesc_ts, (accum || k > 0));
-                        } else {
-                            // dQ[q, d] += sum_k dS[q, k] K[k, d]
-                            umma_bf16_ts_lo(tmem_a0, ts + a_col(k) + CW / 2, bq_lo + 128 * k, idesc_ts, (accum || k > 0));
-                        }
-                        if (next_dp && k < D / 16) {                    // dP(j+1): its operands were waited for by issue_s(j+1)
-                            umma_bf16_ss_lo(tmem_dp, pa_lo + 2 * k, pb_lo + 2 * k, idesc_s, k > 0);
-                            if (k == D / 16 - 1) umma_commit(dp_full);
-                        }
-                    }
-                    umma_commit(&acc_done[bb]);
-                    umma_commit(&str_empty[ca.j % NSTR]);               // the stream stage can be refilled
-                    if (ca.it == ca.n - 1) umma_commit(&fix_empty[ca.k % NFIX]);
-                }
-                __syncwarp();
-                if (next_dp) cur_next(cd);
-                TRACE_AT(33);
-                if (cs.t < total) {
-                    mbar_wait(&acc_done[bb], (ca.j >> 1) & 1);          // acc(j) is done with S[bb]
-                    TRACE_AT(34);
-                    issue_s(cs); cur_next(cs);
-                }
-                TRACE_AT(35);
-            }
-        }
-        __syncwarp();
-    } else {
-        // ===================================== math warps =========================================
-        // NCG threads per tile row: warp w reads TMEM lane quarter (w & 3) and owns the CW columns of group (w >> 2).
-        // More, narrower threads (4 x 32 columns) keep four warps per scheduler, which is what hides the tcgen05.ld /
-        // barrier latencies between the MUFU-bound stretches.
-        const int quarter = warp & 3, cg = warp >> 2;
-        const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
-        const int r = quarter * 32 + lane;
-        // MODE 0: the query block's statistics run along the columns: thread tid fetches lse (tid < 128) or delta
-        // (tid < 256) of one query of the NEXT block at the top of an iteration and parks it in shared memory at the end
-        auto fetch_stat = [&](const BwdCursor& c) {
-            const long long idx = (long long)(c.b * p.H + c.h) * p.T + (long long)(c.ob + c.it) * 128 + (tid & 127);
-            return tid < 128 ? p.lse[idx] : p.delta[idx];      // raw: scaled when parked, so nothing waits on the load here
-        };
-        const float stat_mul = tid < 128 ? 1.4426950408889634f : 1.0f;
-        // ---- finished tile: accumulators -> bf16 -> swizzled staging tiles -> TMA store.  It runs AFTER the math of the
-        //      next tile's first block, so the tensor core finishes the last acc MMAs under useful work, and the
-        //      accumulators are released (acc_free) as soon as they are in registers.
-        bool pend = false;
-        int pend_ob = 0, pend_h = 0, pend_b = 0, pend_bar = 0, pend_par = 0;
-        auto write_tile = [&]() {
-            mbar_wait(&acc_done[pend_bar], pend_par);
-            __syncwarp();
-            tc_fence_after();
-            TRACE_AT(27);
-            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile's stores have read the staging
-            named_bar_math(2);
-            float* db = p.dbias != nullptr ? p.dbias + pend_h * D : nullptr;
-            constexpr int AW = D / BWD_WS_NCG;         // accumulator columns per thread (32 or 16)
-            auto stage_acc = [&](uint32_t taddr, uint8_t* tile, float mul, float* dbias) {
-                uint32_t raw[AW];
-                tmem_ld_n(taddr + lane_base + cg * AW, raw);
-                tmem_ld_wait();
-#pragma unroll
-                for (int q = 0; q < AW / 8; ++q) {
-                    uint4 u;
-                    u.x = pack_bf16x2(__uint_as_float(raw[q * 8 + 0]) * mul, __uint_as_float(raw[q * 8 + 1]) * mul);
-                    u.y = pack_bf16x2(__uint_as_float(raw[q * 8 + 2]) * mul, __uint_as_float(raw[q * 8 + 3]) * mul);
-                    u.z = pack_bf16x2(__uint_as_float(raw[q * 8 + 4]) * mul, __uint_as_float(raw[q * 8 + 5]) * mul);
-                    u.w = pack_bf16x2(__uint_as_float(raw[q * 8 + 6]) * mul, __uint_as_float(raw[q * 8 + 7]) * mul);
-                    *reinterpret_cast<uint4*>(tile + swz(r, cg * (AW / 8) + q)) = u;
-                }
-                if (dbias != nullptr) {
-                    // qkv bias gradient: column sums of the bf16-rounded tile.  Transposing butterfly over the warp's 32
-                    // rows: each round halves the values a lane carries; lane l ends with the sum of column l % AW.
-                    float v[AW];
-#pragma unroll
-                    for (int j2 = 0; j2 < AW; ++j2) v[j2] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(raw[j2]) * mul));
-#pragma unroll
-                    for (int off = AW / 2; off >= 1; off >>= 1) {
-                        const bool up = (lane & off) != 0;
-#pragma unroll
-                        for (int j2 = 0; j2 < off; ++j2) {
-                            const float send = up ? v[j2] : v[j2 + off];
-                            const float keep = up ? v[j2 + off] : v[j2];
-                            v[j2] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-                        }
-                    }
-                    if constexpr (AW == 16) v[0] += __shfl_xor_sync(0xffffffffu, v[0], 16);
-                    if (lane < AW) atomicAdd(dbias + cg * AW + lane, v[0]);
-                }
-            };
-            // (measured: routing these sums through shared-memory atomics + a bulk reduction costs more, +47 vs +33 us)
-            if (MODE == 0) {
-                stage_acc(tmem_a1, sOut, p.scale, db ? db + p.C : nullptr);                    // dK
-                stage_acc(tmem_a0, sOut + TILE_BYTES, 1.0f, db ? db + 2 * p.C : nullptr);      // dV
-            } else {
-                stage_acc(tmem_a0, sOut, p.scale, db);                                         // dQ
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(acc_free);              // the accumulators are in registers / shared memory
-            fence_proxy_async_smem();
-            named_bar_math(2);
-            if (tid == 0) {
-                const int grow = pend_b * p.T + pend_ob * 128;
-                if (MODE == 0) {
-                    tma_store_2d_tile(&tmap_dqkv, sOut, p.C + pend_h * D, grow);
-                    tma_store_2d_tile(&tmap_dqkv, sOut + TILE_BYTES, 2 * p.C + pend_h * D, grow);
-                } else {
-                    tma_store_2d_tile(&tmap_dqkv, sOut, pend_h * D, grow);
-                }
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-            TRACE_AT(28);
-            pend = false;
-        };
-        BwdCursor c = cur_init(), cn = cur_init();
-        if (cn.t < total) cur_next(cn);
-        if (MODE == 0 && c.t < total) {
-            if (tid < 256) sStat[tid] = fetch_stat(c) * stat_mul;
-            named_bar_math(1);
-        }
-        float lse2 = 0.f, dlt = 0.f;
-        for (; c.t < total; cur_next(c)) {
-            const int ob = c.ob, h = c.h, b = c.b;
-            if (MODE == 1 && c.it == 0) {                      // this thread's query row is fixed for the whole tile
-                const long long idx = (long long)(b * p.H + h) * p.T + ob * 128 + r;
-                lse2 = p.lse[idx] * 1.4426950408889634f;
-                // delta = rowsum(dO * O) from the two tiles in shared memory (this used to be a separate kernel and a
-                // separate pass over O and dO); written out for the dK/dV kernel, which runs after this one
-                const int fb = c.k % NFIX;
-                mbar_wait(&fix_full[fb], (c.k / NFIX) & 1);
-                mbar_wait(o_full, c.k & 1);
-                const uint8_t* tdo = sFix + fb * 2 * TILE_BYTES + TILE_BYTES;
-                const uint8_t* to = sOut + TILE_BYTES;
-                float part = 0.f;
-#pragma unroll
-                for (int q = 0; q < 8 / BWD_WS_NCG; ++q) {
-                    const uint32_t piece = cg * (8 / BWD_WS_NCG) + q;
-                    const uint4 ua = *reinterpret_cast<const uint4*>(to + swz(r, piece));
-                    const uint4 ug = *reinterpret_cast<const uint4*>(tdo + swz(r, piece));
-                    const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wg[4] = {ug.x, ug.y, ug.z, ug.w};
-#pragma unroll
-                    for (int j2 = 0; j2 < 4; ++j2) {
-                        const float2 fa = unpack_bf16x2(wa[j2]), fg = unpack_bf16x2(wg[j2]);
-                        part = fmaf(fa.x, fg.x, part);
-                        part = fmaf(fa.y, fg.y, part);
-                    }
-                }
-                sStat[cg * 128 + r] = part;
-                __syncwarp();
-                if (lane == 0) mbar_arrive(o_free);
-                named_bar_math(1);
-                dlt = 0.f;
-#pragma unroll
-                for (int q = 0; q < BWD_WS_NCG; ++q) dlt += sStat[q * 128 + r];
-                if (cg == 0) const_cast<float*>(p.delta)[idx] = dlt;
-            }
-            const int bb = c.j & 1;
-            const bool diag = MODE == 0 ? (c.it == 0) : (c.it == c.n - 1);
-            const uint32_t ts = tmem + bb * 128 + lane_base + cg * CW;
-            const float4* st_l = reinterpret_cast<const float4*>(sStat + bb * 256 + cg * CW);
-            const float4* st_d = reinterpret_cast<const float4*>(sStat + bb * 256 + 128 + cg * CW);
-            float stat_next = 0.f;
-            if (MODE == 0 && tid < 256 && cn.t < total) stat_next = fetch_stat(cn);
-            // exp first (needs only S(j), which has been ready for a while), dS when dP(j) lands: dP(j) is issued together
-            // with acc(j-1), i.e. it completes while this block's exponentials are being computed.
-            float e[CW];
-            TRACE_AT(20);
-            mbar_wait(&s_full[bb], (c.j >> 1) & 1);
-            tc_fence_after();
-            TRACE_AT(21);
-            {
-                uint32_t rs_[CW];
-#pragma unroll
-                for (int q = 0; q < CW / 32; ++q) tmem_ld_32x32(ts + q * 32, *reinterpret_cast<uint32_t(*)[32]>(&rs_[q * 32]));
-                tmem_ld_wait();
-                if (diag) {                                    // causal mask only in the diagonal block (warp-uniform branch)
-#pragma unroll
-                    for (int k = 0; k < CW; ++k) {
-                        const int cc = cg * CW + k;            // MODE 0: row = key, column = query; MODE 1: the transpose
-                        if (MODE == 0 ? (cc < r) : (cc > r)) rs_[k] = 0xff800000u;   // -inf -> P = 0
-                    }
-                }
-#pragma unroll
-                for (int k4 = 0; k4 < CW / 4; ++k4) {
-                    float4 l4 = make_float4(lse2, lse2, lse2, lse2);
-                    if (MODE == 0) l4 = st_l[k4];
-                    e[k4 * 4 + 0] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 0]), p.scale_log2, -l4.x));
-                    e[k4 * 4 + 1] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 1]), p.scale_log2, -l4.y));
-                    e[k4 * 4 + 2] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 2]), p.scale_log2, -l4.z));
-                    e[k4 * 4 + 3] = exp2f(fmaf(__uint_as_float(rs_[k4 * 4 + 3]), p.scale_log2, -l4.w));
-                }
-            }
-            TRACE_AT(22);
-            if (MODE == 0) {                                   // P (bf16 pairs along the K index) -> first half of this thread's S columns
-                uint32_t pk[CW / 2];
-#pragma unroll
-                for (int k = 0; k < CW / 2; ++k) pk[k] = pack_bf16x2(e[2 * k], e[2 * k + 1]);
-                tmem_st_n(ts, pk);
-            }
-            mbar_wait(dp_full, c.j & 1);
-            tc_fence_after();
-            TRACE_AT(23);
-            {
-                uint32_t rd_[CW];
-#pragma unroll
-                for (int q = 0; q < CW / 32; ++q) tmem_ld_32x32(tmem_dp + lane_base + cg * CW + q * 32, *reinterpret_cast<uint32_t(*)[32]>(&rd_[q * 32]));
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(dp_free);           // dP(j) is in registers: the tensor core may overwrite it
-#pragma unroll
-                for (int k4 = 0; k4 < CW / 4; ++k4) {
-                    float4 d4 = make_float4(dlt, dlt, dlt, dlt);
-                    if (MODE == 0) d4 = st_d[k4];
-                    e[k4 * 4 + 0] *= (__uint_as_float(rd_[k4 * 4 + 0]) - d4.x);
-                    e[k4 * 4 + 1] *= (__uint_as_float(rd_[k4 * 4 + 1]) - d4.y);
-                    e[k4 * 4 + 2] *= (__uint_as_float(rd_[k4 * 4 + 2]) - d4.z);
-                    e[k4 * 4 + 3] *= (__uint_as_float(rd_[k4 * 4 + 3]) - d4.w);
-                }
-            }
-            {                                                  // dS -> second half of this thread's S columns
-                uint32_t pk[CW / 2];
-#pragma unroll
-                for (int k = 0; k < CW / 2; ++k) pk[k] = pack_bf16x2(e[2 * k], e[2 * k + 1]);
-                tmem_st_n(ts + CW / 2, pk);
-            }
-            TRACE_AT(24);
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[bb]);
-            TRACE_AT(25);
-            if (pend) write_tile();                            // previous tile's accumulators (its last MMAs ran under this block)
-            // stage the next block's statistics (other buffer); everyone is done reading this block's after the barrier
-            if (MODE == 0) {
-                if (tid < 256) sStat[(bb ^ 1) * 256 + tid] = stat_next * stat_mul;
-                named_bar_math(1);
-            }
-            TRACE_AT(26);
-            if (cn.t < total) cur_next(cn);
-
-            if (c.it == c.n - 1) { pend = true; pend_ob = ob; pend_h = h; pend_b = b; pend_bar = bb; pend_par = (c.j >> 1) & 1; }
-        }
-        if (pend) write_tile();
-        if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // staging tiles are read before the CTA exits
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
 // =================================================================================================
@@ -1886,31 +806,10 @@ extern "C" int tdl_attention_fwd(const void* qkv, void* out, float* lse, int64_t
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.out = (__nv_bfloat16*)out; p.lse = lse;
     const int smem = 5 * TILE_BYTES + 64;                 // Q, 2 x K, 2 x V (P lives in tensor memory)
-    const int smem_ws = (2 + 2 * WS_NST + 4) * TILE_BYTES + 256;
     static bool configured = false;
-    static int use_ws = 0;                 // the simple 2-CTA/SM kernel measured faster (profiles/README.md); TDL_ATTN_WS=1 selects ping-pong
     if (!configured) {
         TDL_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        TDL_CHECK(cudaFuncSetAttribute(attn_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
-        const char* e = getenv("TDL_ATTN_WS");
-        if (e) use_ws = atoi(e);
         configured = true;
-    }
-    static int fwd_variant = -1;
-    if (fwd_variant < 0) { const char* e = getenv("TDL_ATTN_FWD"); fwd_variant = e ? atoi(e) : 1; }
-    if (fwd_variant == 2) {
-        static bool cfg2 = false;
-        const int smem2 = 7 * TILE_BYTES + 64 + 512;
-        if (!cfg2) { TDL_CHECK(cudaFuncSetAttribute(attn_fwd_t2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2)); cfg2 = true; }
-        attn_fwd_t2_kernel<<<dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), 256, smem2, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
-        TDL_LAUNCH_CHECK();
-        return 0;
-    }
-    if (use_ws && (T / 128) % 2 == 0) {
-        attn_fwd_ws_kernel<<<dim3((unsigned)(T / 256), (unsigned)H, (unsigned)B), WS_THREADS, smem_ws,
-                             reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
-        TDL_LAUNCH_CHECK();
-        return 0;
     }
     TDL_CHECK(tdl_launch_pdl(attn_fwd_kernel, dim3((unsigned)(T / 128), (unsigned)H, (unsigned)B), dim3(128), smem,
                              reinterpret_cast<cudaStream_t>(stream), tm, p));
@@ -1934,52 +833,29 @@ extern "C" int tdl_attention_bwd_dbias(const void* qkv, const void* out, const v
     p.scale_log2 = p.scale * 1.4426950408889634f;
     p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = (__nv_bfloat16*)dqkv; p.dbias = dbias;
     TDL_REQUIRE((reinterpret_cast<uintptr_t>(dbias) & 15) == 0, "attention backward: dbias must be 16-byte aligned");
-    const int smem = 10 * TILE_BYTES + 64;
     const int smem_ws = BWD_WS_SMEM;
     static bool configured = false;
-    static int use_ws = 2;                       // TDL_ATTN_BWD_WS: 2 = phase-specialised (default), 1 = column-split math warps, 0 = non-pipelined kernels
     if (!configured) {
-        if (const char* e = getenv("TDL_ATTN_BWD_WS")) use_ws = atoi(e);
-        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ws_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
-        TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ws_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
         TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ps_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
         TDL_CHECK(cudaFuncSetAttribute(attn_bwd_ps_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
         configured = true;
     }
-    const dim3 grid((unsigned)(T / 128), (unsigned)H, (unsigned)B);
-    if (!use_ws) {                               // the pipelined dQ kernel computes delta itself
-        const long long items = B * T * H * 8;
-        attn_delta_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)d_out,
-                                                                        delta, (int)B, (int)T, (int)H);
-    }
-    if (use_ws) {
-        const long long tiles = (T / 128) * B * H;
-        long long ch = (96 * 1024) / T;                      // 4 tensors x T x 64 x 2 B per pair: keep a chunk under ~48 MB
-        ch = ch < 1 ? 1 : (ch > B * H ? B * H : ch);
-        while ((B * H) % ch) --ch;                           // chunks are all the same size
-        p.bwd_chunk = (int)ch;
-        TDL_REQUIRE(tiles < (1 << 20) && H < (1 << 20), "attention backward: too many tiles for the persistent schedule");
-        auto magic = [](long long d) { return (unsigned long long)(((1ull << 40) + d - 1) / d); };
-        p.mg_tile = magic((T / 128) * ch); p.mg_chunk = magic(ch); p.mg_head = magic(H);
-        const unsigned ctas = (unsigned)(tiles < tdl_num_sms() ? tiles : tdl_num_sms());      // persistent: one CTA per SM
-        CUtensorMap tdq;
-        if (int rc = tdl_make_tmap_2d_bf16(&tdq, dqkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
-        CUtensorMap to;
-        if (int rc = tdl_make_tmap_2d_bf16(&to, out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
-        // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
-        if (use_ws == 2) {                                   // phase-specialised math warps
-            TDL_CHECK(tdl_launch_pdl(attn_bwd_ps_kernel<1>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
-            TDL_CHECK(tdl_launch_pdl(attn_bwd_ps_kernel<0>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
-        } else {
-            TDL_CHECK(tdl_launch_pdl(attn_bwd_ws_kernel<1>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
-            TDL_CHECK(tdl_launch_pdl(attn_bwd_ws_kernel<0>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
-        }
-    } else {
-        attn_bwd_kernel<0><<<grid, 256, smem, s>>>(tq, tdo, p);
-        attn_bwd_kernel<1><<<grid, 256, smem, s>>>(tq, tdo, p);
-    }
+    const long long tiles = (T / 128) * B * H;
+    long long ch = (96 * 1024) / T;                      // 4 tensors x T x 64 x 2 B per pair: keep a chunk under ~48 MB
+    ch = ch < 1 ? 1 : (ch > B * H ? B * H : ch);
+    while ((B * H) % ch) --ch;                           // chunks are all the same size
+    p.bwd_chunk = (int)ch;
+    TDL_REQUIRE(tiles < (1 << 20) && H < (1 << 20), "attention backward: too many tiles for the persistent schedule");
+    auto magic = [](long long d) { return (unsigned long long)(((1ull << 40) + d - 1) / d); };
+    p.mg_tile = magic((T / 128) * ch); p.mg_chunk = magic(ch); p.mg_head = magic(H);
+    const unsigned ctas = (unsigned)(tiles < tdl_num_sms() ? tiles : tdl_num_sms());      // persistent: one CTA per SM
+    CUtensorMap tdq;
+    if (int rc = tdl_make_tmap_2d_bf16(&tdq, dqkv, 3ull * C, (uint64_t)(B * T), 3ull * C, 64, 128)) return rc;
+    CUtensorMap to;
+    if (int rc = tdl_make_tmap_2d_bf16(&to, out, (uint64_t)C, (uint64_t)(B * T), (uint64_t)C, 64, 128)) return rc;
+    // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
+    TDL_CHECK(tdl_launch_pdl(attn_bwd_ps_kernel<1>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
+    TDL_CHECK(tdl_launch_pdl(attn_bwd_ps_kernel<0>, dim3(ctas), dim3(BWD_WS_THREADS), smem_ws, s, tq, tdo, tdq, to, p));
     TDL_LAUNCH_CHECK();
     return 0;
 }

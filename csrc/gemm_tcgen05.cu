@@ -870,7 +870,7 @@ int tdl_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t inner, ui
 }
 
 template <int BLOCK_N, int STAGES_>
-static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream) {
+static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream, int sm_reserve = 0) {
     using C = Cfg<BLOCK_N, STAGES_>;
     static bool configured = false;
     if (!configured) {
@@ -879,7 +879,8 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
         configured = true;
     }
     const int work = p.m_blocks * p.n_blocks * p.split_k;
-    const int grid = work < tdl_num_sms() ? work : tdl_num_sms();
+    const int sms = tdl_num_sms() - sm_reserve;
+    const int grid = work < sms ? work : sms;
     gemm_bf16_tcgen05_kernel<BLOCK_N, STAGES_><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
     TDL_LAUNCH_CHECK();
     return 0;
@@ -887,7 +888,7 @@ static int launch_gemm(const TmapArray& ta, const CUtensorMap& tb, GemmParams& p
 
 template <int BLOCK_N, int STAGES_, bool AUX, bool COLSUM = false>
 static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const EpiMaps& em, const TmapArray& cm, GemmParams& p,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, int sm_reserve = 0) {
     using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     static bool configured = false;
     if (!configured) {
@@ -897,7 +898,7 @@ static int launch_gemm_2cta(const TmapArray& ta, const CUtensorMap& tb, const Ep
     }
     const int m_blocks2 = (p.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
     const int work = m_blocks2 * p.n_blocks * p.split_k;
-    const int max_clusters = tdl_num_sms() / 2;
+    const int max_clusters = (tdl_num_sms() - sm_reserve) / 2;
     const int clusters = work < max_clusters ? work : max_clusters;
     TDL_CHECK(tdl_launch_pdl(gemm_bf16_tcgen05_2cta_kernel<BLOCK_N, STAGES_, AUX, COLSUM>, dim3(2 * clusters), dim3(NUM_THREADS),
                              C::SMEM_BYTES, stream, ta, tb, em, cm, p));
@@ -1013,19 +1014,31 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         }
         const bool fuse_colsum = colsum != nullptr && staged && (reinterpret_cast<uintptr_t>(colsum) & 15) == 0;
         if (fuse_colsum) p.colsum = colsum;             // column sums leave from the staged epilogue panels
+        // With tile-arrival flags the pull kernel that feeds A has to make progress WHILE this grid is resident, whatever the
+        // launch order: the persistent grid leaves `reserve` SMs to it (TDL_K8_PULL_SMS, default 16 = 8 TPCs, ~11 % of the
+        // tensor throughput of a GEMM that is NVLink-bound anyway), and runs one pipeline stage less so that the pull's
+        // 128-thread blocks can additionally sit beside resident GEMM CTAs (~32 KB of shared memory stays free per SM).
+        const bool flagged = a_flags != nullptr;
+        static int pull_sms = -1;
+        if (pull_sms < 0) { const char* e = getenv("TDL_K8_PULL_SMS"); pull_sms = e ? atoi(e) : 16; if (pull_sms < 2) pull_sms = 2; }
+        const int rsv = flagged ? pull_sms : 0;
         if (fuse_colsum)
-            rc = needs_aux ? launch_gemm_2cta<256, 5, true, true>(ta, tb, em, cm, p, s)
-                           : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, cm, p, s);
+            rc = needs_aux ? (flagged ? launch_gemm_2cta<256, 4, true, true>(ta, tb, em, cm, p, s, rsv)
+                                      : launch_gemm_2cta<256, 5, true, true>(ta, tb, em, cm, p, s))
+                           : (flagged ? launch_gemm_2cta<256, 5, false, true>(ta, tb, em, cm, p, s, rsv)
+                                      : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, cm, p, s));
+        else if (staged && needs_aux)
+            rc = flagged ? launch_gemm_2cta<256, 4, true>(ta, tb, em, cm, p, s, rsv) : launch_gemm_2cta<256, 5, true>(ta, tb, em, cm, p, s);
         else
-            rc = (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, cm, p, s)
-                                       : launch_gemm_2cta<256, 6, false>(ta, tb, em, cm, p, s);
+            rc = flagged ? launch_gemm_2cta<256, 5, false>(ta, tb, em, cm, p, s, rsv) : launch_gemm_2cta<256, 6, false>(ta, tb, em, cm, p, s);
         if (!rc && colsum != nullptr && !fuse_colsum) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
         return rc;
     }
     static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
     if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
-    if (block_n == 256) rc = exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
-    else                rc = exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s) : launch_gemm<128, 6>(ta, tb, p, s);
+    const int rsv1 = a_flags != nullptr ? 16 : 0;           // see the 2-CTA path: SMs left to the pull kernel
+    if (block_n == 256) rc = exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s, rsv1) : launch_gemm<256, 4>(ta, tb, p, s, rsv1);
+    else                rc = exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s, rsv1) : launch_gemm<128, 6>(ta, tb, p, s, rsv1);
     // the 1-CTA kernel has no fused column sums: follow with the stand-alone reduction over the output
     if (!rc && colsum != nullptr) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
     return rc;

@@ -118,6 +118,13 @@ extern "C" int tdl_gather_rows_flagged(const void* const* shard_ptrs, int W, int
     const int total = (int)(shard_rows / GF_ROWS) * W;
     int grid = max_blocks > 0 ? max_blocks : 2 * tdl_num_sms();
     if (grid > total) grid = total;
+    static bool configured = false;
+    if (!configured) {
+        // SMs switch their L1 / shared-memory split only when idle: ask for the split of the tensor-core kernels this copy
+        // is meant to run beside, so its blocks are not kept off an SM that holds a GEMM CTA
+        cudaFuncSetAttribute(gather_rows_flagged_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured = true;
+    }
     gather_rows_flagged_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ps, W, my_rank, (int)shard_rows,
                                                                                          (int)(row_elems * 2 / 16),
                                                                                          reinterpret_cast<uint4*>(dst), flags);

@@ -409,7 +409,9 @@ extern "C" int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, 
     if (per_sm < 0) { const char* e = getenv("TDL_TR_BLOCKS"); per_sm = e ? atoi(e) : 4; if (per_sm < 1) per_sm = 1; }
     const long long cap = max_blocks > 0 ? max_blocks : (long long)tdl_num_sms() * per_sm;
     const int grid = (int)(blocks > cap ? cap : blocks);
-#define LAUNCH(T, WW) do { if (threads == 256) trust_reduce_kernel<T, WW, 256><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); \
+    // the 64-thread variant is meant to sit beside tensor-core CTAs: same L1 / shared-memory split as theirs (see param_gather.cu)
+#define LAUNCH(T, WW) do { if (threads == 64) cudaFuncSetAttribute(trust_reduce_kernel<T, WW, 64>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+                           if (threads == 256) trust_reduce_kernel<T, WW, 256><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); \
                            else trust_reduce_kernel<T, WW, 64><<<grid, 64, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); } while (0)
 #define BY_W(T) switch (W) { case 1: LAUNCH(T, 1); break; case 2: LAUNCH(T, 2); break; case 3: LAUNCH(T, 3); break; \
     case 4: LAUNCH(T, 4); break; case 5: LAUNCH(T, 5); break; case 6: LAUNCH(T, 6); break; case 7: LAUNCH(T, 7); break; \

