@@ -85,6 +85,29 @@ def main() -> int:
                 ts.append(e0.elapsed_time(e1))
             red[i] = min(ts)
         r.enqueue_finalize(update_trust=False)
+    # the same bucket through K4 (plain mean all-reduce: multimem through the switch, or P2P) and through NCCL
+    cmp_ms = {}
+    if world > 1:
+        r = eng.reducer
+
+        def timeit(fn, reps=args.reps):
+            ts = []
+            for _ in range(reps):
+                sync()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            return min(ts)
+
+        def k2_all():
+            for seg in eng.segments:
+                r.enqueue_bucket(seg.off, seg.n, owner_only=bool(args.zero))
+        eng.bucket.normal_()
+        cmp_ms["K2 trust-weighted all-reduce + median/cosine statistics (all segments)"] = timeit(k2_all)
+        r.enqueue_finalize(update_trust=False)
+        cmp_ms["K4 plain mean all-reduce (" + ("multimem.ld_reduce + multimem.st" if r.k4_multimem else "P2P") + ")"] = \
+            timeit(lambda: r.enqueue_sum_allreduce(0, eng.P))
+        cmp_ms["NCCL all_reduce (bf16, same bucket)"] = timeit(lambda: dist.all_reduce(eng.bucket))
     # overlapped schedule: whole step
     whole = []
     for _ in range(args.reps):
@@ -116,7 +139,11 @@ def main() -> int:
                 tot_b += b; tot_t += t
                 print(f"    seg{i}: {b / 1e6:8.1f} MB in {t * 1e3:7.3f} ms = {b / t / 1e9:6.1f} GB/s = {b / t / LINK_BYTES_PER_S:.2f} of link rate")
             print(f"    all : {tot_b / 1e6:8.1f} MB in {tot_t * 1e3:7.3f} ms = {tot_b / tot_t / 1e9:6.1f} GB/s = {tot_b / tot_t / LINK_BYTES_PER_S:.2f} of link rate")
-        print(json.dumps({"world": world, "serial_ms": serial, "overlapped_ms": out[-1],
+        if cmp_ms:
+            print(f"  same {eng.P * 2 / 1e6:.0f} MB bf16 bucket, whole (this rank's timings):")
+            for k, v in cmp_ms.items():
+                print(f"    {k:80s} {v:7.3f} ms")
+        print(json.dumps({"world": world, "serial_ms": serial, "overlapped_ms": out[-1], "allreduce_ms": cmp_ms,
                           "phases": dict(zip(keys, out[:nk])), "reduce_ms": out[nk:nk + len(eng.segments)]}))
     if world > 1:
         dist.barrier(); dist.destroy_process_group()

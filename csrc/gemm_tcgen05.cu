@@ -412,7 +412,11 @@ template <int BLOCK_N, int STAGES_, bool AUX> struct Cfg2 {
     static constexpr int STAGING_BYTES = (AUX ? 4 : 2) * PANEL_BYTES;
     static constexpr int COLSUM_BYTES = 8 * 16 * 4;                       // per epilogue warp: 16 column sums
     static constexpr int BIAS_BYTES = 2 * (BLOCK_N / 2) * 4;              // per column half: this tile's bias as fp32
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + COLSUM_BYTES + BIAS_BYTES + 1024 + 256;
+    // No alignment slack: the kernel has no static shared memory, so the dynamic window starts 1024-aligned (checked at
+    // kernel start).  The KB saved is what lets one small block of another stream (the 64-thread trust-reduce, the
+    // 128-thread pack / AdamW helpers: <= 256 B of shared memory, < 12 K registers) become resident beside a GEMM CTA:
+    // 231,168 B here + 1 KB system reservation per block leaves 1,280 B of the SM's 233,472 B.
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + COLSUM_BYTES + BIAS_BYTES + 256;
 };
 
 struct EpiMaps { CUtensorMap c, aux; };
@@ -451,8 +455,8 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                               const __grid_constant__ GemmParams p) {
     using C = Cfg2<BLOCK_N, STAGES_, AUX>;
     const CUtensorMap& tmap_a = tmaps_a.m[0];
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) __trap();          // swizzled TMA tiles need the 1024-byte alignment
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
     uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;                 // [half][out | aux] panels

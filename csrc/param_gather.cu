@@ -87,14 +87,14 @@ __global__ void __launch_bounds__(128) gather_rows_flagged_kernel(Ptrs shards, i
         const int row0 = (it % items_per_shard) * GF_ROWS;
         const uint4* src = reinterpret_cast<const uint4*>(shards.p[sh]) + (long long)row0 * row_vecs;
         uint4* out = dst + ((long long)sh * shard_rows + row0) * row_vecs;
-        for (int v = threadIdx.x; v < vecs; v += 128 * 4) {
-            uint4 u[4];
+        for (int v = threadIdx.x; v < vecs; v += 128 * 8) {              // 8 x 16 B in flight per thread (NVLink latency)
+            uint4 u[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < 8; ++j)
                 if (v + j * 128 < vecs)
                     asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u[j].x), "=r"(u[j].y), "=r"(u[j].z), "=r"(u[j].w) : "l"(src + v + j * 128) : "memory");
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < 8; ++j)
                 if (v + j * 128 < vecs) out[v + j * 128] = u[j];
         }
         __syncthreads();
@@ -116,7 +116,7 @@ extern "C" int tdl_gather_rows_flagged(const void* const* shard_ptrs, int W, int
     Ptrs ps{};
     for (int i = 0; i < W; ++i) ps.p[i] = shard_ptrs[i];
     const int total = (int)(shard_rows / GF_ROWS) * W;
-    int grid = max_blocks > 0 ? max_blocks : 2 * tdl_num_sms();
+    int grid = max_blocks > 0 ? max_blocks : 4 * tdl_num_sms();
     if (grid > total) grid = total;
     static bool configured = false;
     if (!configured) {

@@ -183,3 +183,94 @@ def test_gemm_gelu_with_saved_derivative(M):
     ref = (dy.float() @ w2.float()) * dg.float()
     assert torch.allclose(dpre.float(), ref, atol=5e-2, rtol=3e-2)
     assert torch.allclose(cs, dpre.float().sum(0), atol=2e-3 * (M ** 0.5), rtol=1e-4)
+
+
+def test_gemm_lm_head_two_cta_grouped_rasterisation():
+    """N = 50304 with M >= 512: the 2-CTA kernel with grouped tile order (197 n-blocks, the LM-head fast path)."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(11)
+    M, C, Vp = 4096, 256, 50304                    # 16 m-pairs x 197 n-blocks: one full rasterisation group and change
+    x, wte = _mk((M, C), dev), _mk((Vp, C), dev, 0.05)
+    logits = torch.empty(M, Vp, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, wte, logits)
+    ref = x.float() @ wte.float().t()
+    assert (logits.float() - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+    d = _mk((M, Vp), dev, 0.01)
+    dx = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+    Kk.linear_dgrad(d, wte, dx)                    # K = 50304 (786 k-blocks) through the 2-CTA kernel
+    ref = d.float() @ wte.float()
+    assert (dx.float() - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+
+
+@pytest.mark.parametrize("N,Kin", [(1024, 4096), (4096, 1024), (3072, 1024), (1024, 1024)])
+def test_gemm_wgrad_auto_split_k_on_gpt2_medium_shapes(N, Kin):
+    """split_k = 0: the library picks the split that fills whole waves (what the engine always passes)."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(N + Kin)
+    M = 8192                                       # tokens (the reduction dimension): 128 k-blocks
+    dy, x = _mk((M, N), dev, 0.5), _mk((M, Kin), dev, 0.5)
+    dw = torch.full((N, Kin), 0.5, device=dev)
+    Kk.linear_wgrad(dy, x, dw, split_k=0)
+    ref = dy.float().t() @ x.float() + 0.5
+    assert (dw - ref).abs().max().item() <= 2e-3 * (ref.abs().max().item() + 1)
+
+
+def test_gemm_full_lm_head_bench_shape_sampled_rows():
+    """The shape bench.py runs (32768 x 50304 x 1024), checked on 64 random rows against fp32."""
+    from trustworthy_dl.ops import nn as Kk
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(12)
+    M, C, Vp = 32768, 1024, 50304
+    x, wte = _mk((M, C), dev), _mk((Vp, C), dev, 0.03)
+    logits = torch.empty(M, Vp, device=dev, dtype=torch.bfloat16)
+    Kk.linear_fwd(x, wte, logits)
+    rows = torch.randint(0, M, (64,), device=dev)
+    ref = x[rows].float() @ wte.float().t()
+    got = logits[rows].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
+    del logits
+    torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("W", [2, 8])
+def test_flagged_allgather_gemm_emulated_ranks(W):
+    """K8 with tile-arrival flags, all "ranks" on one GPU: the pull kernel fills the local operand while the GEMM consumes it."""
+    from trustworthy_dl.ops import nn as Kk, tp_ops
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(20 + W)
+    shard_rows, Kd, N = 512, 512, 768
+    M = shard_rows * W
+    shards = [_mk((shard_rows, Kd), dev) for _ in range(W)]
+    w = _mk((N, Kd), dev, 0.2)
+    bias = torch.randn(N, device=dev)
+    ref = torch.cat(shards).float() @ w.float().t() + bias
+    side = torch.cuda.Stream()
+    for rank in (0, W - 1):
+        full = torch.zeros(M, Kd, device=dev, dtype=torch.bfloat16)
+        flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
+        out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):
+            tp_ops.gather_rows_flagged([s.data_ptr() for s in shards], rank, shard_rows, Kd, full, flags)
+        tp_ops.gemm_flagged(full, flags, W, rank, shard_rows, w, out, bias=bias)
+        torch.cuda.synchronize()
+        assert int(flags.min().item()) == tp_ops.FLAG_TARGET and int(flags.max().item()) == tp_ops.FLAG_TARGET
+        assert torch.equal(full, torch.cat(shards))
+        assert torch.allclose(out.float(), ref, atol=8e-2, rtol=2e-2), (out.float() - ref).abs().max().item()
+    # dgrad form: weight stored [K, N], GELU' multiply and the bias gradient in the epilogue
+    w2 = _mk((Kd, N), dev, 0.2)
+    aux = _mk((M, N), dev)
+    cs = torch.zeros(N, device=dev)
+    full = torch.zeros(M, Kd, device=dev, dtype=torch.bfloat16)
+    flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
+    out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        tp_ops.gather_rows_flagged([s.data_ptr() for s in shards], 1, shard_rows, Kd, full, flags)
+    tp_ops.gemm_flagged(full, flags, W, 1, shard_rows, w2, out, b_mn=True, epilogue=Kk.EPI_MUL, aux_in=aux, colsum=cs)
+    torch.cuda.synchronize()
+    ref2 = (torch.cat(shards).float() @ w2.float()) * aux.float()
+    assert torch.allclose(out.float(), ref2, atol=0.12, rtol=3e-2), (out.float() - ref2).abs().max().item()
+    assert torch.allclose(cs, out.float().sum(0), atol=2e-3 * (M ** 0.5) + 0.05, rtol=1e-3)

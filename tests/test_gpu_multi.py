@@ -411,3 +411,33 @@ def test_fused_pipeline_stages_with_reassignment():
             a, b = owner[s], owner[S + s]
             assert res[a]["psum"][s] == pytest.approx(res[b]["psum"][s], rel=1e-6)
     assert res[0]["val"] == pytest.approx(res[-1]["val"], rel=1e-6) and res[0]["val"] < L[0]
+
+
+def _trainer_zero_worker(rank, world):
+    """Public API, ``zero: 1``: the parameter monitor runs inside the parameter all-gather of every step; a rank that
+    publishes a corrupted shard is marked MODEL_POISONING the same step."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    att = AdversarialAttacker(AttackConfig(attack_types=["model_poisoning"], target_nodes=[1], intensity=0.5, start_step=5, end_step=6))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=2 * world, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, parallelism="data", engine="fused", dtype="bf16", seq_len=128, zero=1,
+                         model_kwargs={"n_positions": 128, "n_embd": 128, "n_head": 2, "vocab_size": 512, "padded_vocab_size": 512})
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("tiny-tokens", "train", 2 * world, num_batches=8, seq_len=128)]
+    return {"losses": losses, "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+            "status": [t.trust_manager.get_node_status(n).value for n in range(world)],
+            "events": [e["reason"] for e in t.parameter_monitor.events]}
+
+
+def test_trainer_zero1_flags_model_poisoning_in_the_same_step():
+    world = torch.cuda.device_count()
+    if world & (world - 1):
+        pytest.skip("ZeRO-1 slices need a power-of-two world")
+    res = _run(_trainer_zero_worker, world)
+    for r in res:
+        assert r["attacks"] and r["attacks"][0] == (1, 5, "model_poisoning"), r["attacks"]
+        assert r["status"][1] == "compromised" and r["status"][0] == "trusted"
+        assert "checksum_mismatch" in r["events"]
+    assert all(r["attacks"] == res[0]["attacks"] for r in res)

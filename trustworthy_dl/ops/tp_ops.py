@@ -100,3 +100,16 @@ def gemm_flagged(a_full: torch.Tensor, flags: torch.Tensor, W: int, rank: int, s
     _lib.call("tdl_gemm_bf16_flagged", ptr(a_full), ptr(flags), i32(FLAG_TARGET), i32(W), i32(rank), i64(shard_rows), ptr(w), ptr(out),
               i64(N), i64(K), i64(K), i64(w.shape[1]), i64(N), i32(b_mn), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in),
               ptr(aux_out), i64(N), i32(block_n), ptr(colsum), stream_ptr())
+
+
+def local_gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, bias: Optional[torch.Tensor] = None, epilogue: int = 0,
+               aux_in=None, aux_out=None, block_n: int = 0, b_mn: bool = False, colsum: Optional[torch.Tensor] = None):
+    """Plain tcgen05 GEMM on an already gathered operand, same keyword surface as the fused forms."""
+    from . import nn as K
+    M = a.shape[0]
+    if b_mn:
+        Kd, N = w.shape
+    else:
+        N, Kd = w.shape
+    K.gemm(a, w, out, M, N, Kd, lda=Kd, ldb=w.shape[1], ldc=N, b_mn=b_mn, bias=bias, epilogue=epilogue, aux_in=aux_in,
+           aux_out=aux_out, ld_aux=N, block_n=block_n, colsum=colsum)

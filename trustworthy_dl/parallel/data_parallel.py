@@ -197,6 +197,11 @@ class DataParallelStrategy:
             i = t.attacker.config.intensity
             scale = -(1.0 + 4.0 * i) if t.attacker.config.gradient_mode == "sign_flip" else 1.0 + 20.0 * i
             t.attacker._record("gradient_poisoning", step, self.rank, mode=t.attacker.config.gradient_mode)
+        if self.engine.zero and t.attacker is not None:
+            armed = t.attacker._armed("model_poisoning", step, self.rank)
+            self.engine.param_attack.fill_(float(t.attacker.config.intensity) / 10.0 if armed else 0.0)
+            if armed:
+                t.attacker._record("model_poisoning", step, self.rank)
         loss = self.engine.train_step(local["input"], local["target"], attack_scale=scale)
         ts = time.perf_counter()
         snap = self.engine.security_snapshot()
@@ -221,6 +226,30 @@ class DataParallelStrategy:
             res = t.attack_detector.observe_stats(snap["act_stats"].numpy(), self.rank, step)
             if res.is_attack:
                 t.metrics_collector.record_event("output_anomaly", node_id=self.rank, step=step)
+        if "param_flags" in snap:
+            # ZeRO-1: the parameter monitor ("Param Monitor", reference README.md:22) runs inside the parameter all-gather
+            # of every step: a shard whose checksum differs from the one its owner published, or whose drift norm jumps,
+            # marks the owner MODEL_POISONING in the same step
+            pflags, pdrift = snap["param_flags"].tolist(), snap["param_drift"].tolist()
+            for node in range(self.world):
+                bad = bool(pflags[node])
+                if bad:
+                    t.parameter_monitor.report_mismatch(node, step)
+                elif t.parameter_monitor.observe_drift(node, float(pdrift[node]), step)["poisoned"]:
+                    bad = True
+                if bad and tm.get_node_status(node) is not NodeStatus.COMPROMISED:
+                    t.attack_history.append({"node_id": node, "timestamp": time.time(), "step": step,
+                                             "attack_type": "model_poisoning",
+                                             "parameter_stats": {"checksum_mismatch": bool(pflags[node]), "drift": float(pdrift[node])}})
+                    tm.mark_compromised(node, "model_poisoning")
+                    # the device-resident trust vector is authoritative on this path: demote the rank there too (every
+                    # rank takes the same decision from the same flags, so the replicas stay identical)
+                    self.engine.reducer.trust[node] = float(tm.get_trust_score(node))
+                    self.engine.reducer.status[node] = 2
+                    t.metrics_collector.record_event("attack", node_id=node, type="model_poisoning", step=step)
+                    self.reassign(node)
+                    from ..core.distributed_trainer import TrainingState
+                    t.training_state = TrainingState.UNDER_ATTACK
         self._sec_s += time.perf_counter() - ts
         self._step_s += time.perf_counter() - t0
         t.metrics_collector.collect_batch_metrics({

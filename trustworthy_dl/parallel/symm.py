@@ -239,6 +239,7 @@ class SymmetricTrustReducer:
 
 
 def _overlap_blocks() -> int:
-    """Grid of the reduction variant that runs under the backward pass (TDL_TR_OVERLAP_BLOCKS, default 2 per SM)."""
+    """Grid of the reduction variant that runs under the backward pass (TDL_TR_OVERLAP_BLOCKS, default 1 per SM: beside
+    a resident GEMM CTA there is shared memory for exactly one small block)."""
     v = os.environ.get("TDL_TR_OVERLAP_BLOCKS")
-    return int(v) if v else 2 * int(_lib.lib().tdl_device_sm_count())
+    return int(v) if v else int(_lib.lib().tdl_device_sm_count())

@@ -78,6 +78,25 @@ class ParameterMonitor:
             hist.append(drift)
         return {"drift": drift, "expected": expected, "poisoned": poisoned}
 
+    def observe_drift(self, shard_id: int, drift: float, step: int) -> Dict:
+        """Same rule as :meth:`observe` for a drift norm that was measured elsewhere -- the parameter all-gather kernel
+        (csrc/param_gather.cu) folds ``||theta - theta_prev||^2`` per shard into the copy, so the monitor never touches
+        the parameters themselves on that path."""
+        hist = self._drifts[shard_id]
+        expected = float(np.median(hist)) if len(hist) >= self.warmup else None
+        poisoned = (not np.isfinite(drift)) or (expected is not None and expected > 0
+                                                and drift > self.drift_ratio_max * expected)
+        if poisoned:
+            self.events.append({"shard": shard_id, "step": step, "reason": "drift", "drift": drift, "expected": expected})
+        else:
+            hist.append(drift)
+        return {"drift": drift, "expected": expected, "poisoned": poisoned}
+
+    def report_mismatch(self, shard_id: int, step: int) -> None:
+        """A receiver's checksum of shard ``shard_id`` differed from the one its owner published (K9 verdict)."""
+        self.events.append({"shard": shard_id, "step": step, "reason": "checksum_mismatch"})
+        logger.error("parameter shard %d failed its integrity check at step %d", shard_id, step)
+
     def detect_parameter_poisoning(self, shard_id: int, params: Iterable[torch.Tensor], step: int) -> bool:
         return bool(self.observe(shard_id, params, step)["poisoned"])
 
