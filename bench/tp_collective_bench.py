@@ -47,7 +47,6 @@ def main() -> int:
     e.atty[0].normal_(); e.fcg[0].normal_(); e.dfch.normal_(); e.dqkv.normal_(); e.fch[0].fill_(1.0)
     p = "h0."
     mode = {"pull": "P2P pull into the local operand, then the tcgen05 GEMM on local memory (operand kept for the wgrad)",
-            "flags": "tile-arrival flags (small-footprint pull kernel concurrent with a local-A tcgen05 GEMM)",
             "tma": "TMA reads of the peer shards"}[e.k8_mode]
     ag_bytes = (W - 1) * Ms * C * 2            # what one rank pulls (K8) or pushes (K7), one direction
     cases = [
@@ -61,16 +60,6 @@ def main() -> int:
         ("K7 bwd  dln1  dqkv_r[M,3C/W] @ Wqkv_r -> RS", lambda: e._row_parallel(e.dqkv, e.w16(p + "qkv_w"), e.dln_s, b_mn=True), 2.0 * M * C * 3 * Cl, ag_bytes),
         ("pull    AG copy of a [M,C] operand for a wgrad (K9 kernel)", lambda: e._pull(e._off_dx[0], e.full_a, side=False), 0.0, ag_bytes),
     ]
-    if e.k8_mode == "flags":
-        def pull_only():
-            e.flags.zero_()
-            tp_ops.gather_rows_flagged(e._peers(e._off_ln[0][0]), e.rank, Ms, C, e.full_a, e.flags)
-
-        def gemm_only():          # flags left complete by pull_only: the GEMM never waits
-            tp_ops.gemm_flagged(e.full_a, e.flags, W, e.rank, Ms, e.w16(p + "fc_w"), e.fcg[0], bias=e.w32(p + "fc_b"),
-                                epilogue=K.EPI_GELU_DG, aux_out=e.fch[0])
-        cases += [("      flagged pull alone (small-footprint blocks, whole GPU free)", pull_only, 0.0, ag_bytes),
-                  ("      flagged fc GEMM alone (flags already complete)", gemm_only, 2.0 * M * Fl * C, 0.0)]
     rows = []
     for name, fn, flops, nbytes in cases:
         for _ in range(3):

@@ -54,29 +54,7 @@ struct GemmParams {
     // into that rank's staging buffer c_ptrs[owner] at slot `c_src_slot` (P2P stores from the epilogue).
     int c_scatter, c_shard_rows, c_src_slot;
     void* c_ptrs[8];
-    // K8 with tile-arrival flags: A is a LOCAL [M, K] buffer that a concurrent pull kernel fills from the peers 128 rows
-    // at a time; a_flags[r / 128] reaches a_flag_target once rows [r, r + 128) have landed.  The TMA producer waits for the
-    // flag of the tile it is about to load, so each remote byte crosses NVLink exactly once (and stays for the wgrad).
-    const int* a_flags; int a_flag_target;
 };
-
-__device__ __forceinline__ void wait_rows_ready(const int* flags, int m_idx, int target) {
-    const int* f = flags + (m_idx >> 7);
-    int v;
-    long long t0 = 0;
-    unsigned spins = 0;
-    do {
-        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-        if (v < target) {
-            __nanosleep(64);
-            if ((++spins & 0xFFFFu) == 0) {                    // watchdog: the pull kernel never delivered these rows
-                if (t0 == 0) t0 = clock64();
-                else if (clock64() - t0 > 20000000000ll) { printf("tdl: gemm: rows %d never arrived (flag %d < %d)\n", m_idx, v, target); __trap(); }
-            }
-        }
-    } while (v < target);
-    asm volatile("fence.proxy.async.global;" ::: "memory");    // generic-proxy writes of the pull -> visible to the TMA load
-}
 
 struct TmapArray { CUtensorMap m[8]; };
 
@@ -240,7 +218,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapArray tmaps_a, const __grid
                 }
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
-                if (p.a_flags != nullptr) wait_rows_ready(p.a_flags, m_idx, p.a_flag_target);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
@@ -527,7 +504,6 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                 }
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, total_k_blocks);
-                if (p.a_flags != nullptr && m_idx < p.M) wait_rows_ready(p.a_flags, m_idx, p.a_flag_target);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
@@ -914,8 +890,7 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
                        const void* B, void* Cout, void* const* c_ptrs, int c_scatter, int64_t c_shard_rows, int c_src_slot,
                        int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
                        const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux,
-                       int out_f32_atomic, int split_k, int block_n, float* colsum, void* stream,
-                       const int* a_flags = nullptr, int a_flag_target = 0) {
+                       int out_f32_atomic, int split_k, int block_n, float* colsum, void* stream) {
     TDL_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
     TDL_REQUIRE(colsum == nullptr || (!out_f32_atomic && !c_scatter), "column sums need the bf16 output");
     TDL_REQUIRE(N % 32 == 0, "N (%lld) must be a multiple of 32", (long long)N);
@@ -955,8 +930,6 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
     TDL_REQUIRE(!(epilogue == EPI_RESIDUAL || epilogue == EPI_DGELU || epilogue == EPI_MUL) || aux_in != nullptr, "epilogue needs aux_in");
     p.a_shards = a_shards; p.a_shard_rows = (int)a_shard_rows; p.m_block_offset = m_block_offset % p.m_blocks;
     p.c_scatter = c_scatter; p.c_shard_rows = (int)c_shard_rows; p.c_src_slot = c_src_slot;
-    p.a_flags = a_flags; p.a_flag_target = a_flag_target;
-    TDL_REQUIRE(a_flags == nullptr || (!a_mn_major && M % BLOCK_M == 0), "tile-arrival flags need a K-major A with whole 128-row blocks");
     if (a_shards > 1) {
         TDL_REQUIRE(!a_mn_major && a_shards <= 8 && a_shard_rows % BLOCK_M == 0 && a_shard_rows * a_shards == M,
                     "sharded A needs K-major layout, <= 8 shards and shard rows that are a multiple of %d", BLOCK_M);
@@ -1018,31 +991,19 @@ static int gemm_common(const void* const* a_shard_ptrs, int a_shards, int64_t a_
         }
         const bool fuse_colsum = colsum != nullptr && staged && (reinterpret_cast<uintptr_t>(colsum) & 15) == 0;
         if (fuse_colsum) p.colsum = colsum;             // column sums leave from the staged epilogue panels
-        // With tile-arrival flags the pull kernel that feeds A has to make progress WHILE this grid is resident, whatever the
-        // launch order: the persistent grid leaves `reserve` SMs to it (TDL_K8_PULL_SMS, default 16 = 8 TPCs, ~11 % of the
-        // tensor throughput of a GEMM that is NVLink-bound anyway), and runs one pipeline stage less so that the pull's
-        // 128-thread blocks can additionally sit beside resident GEMM CTAs (~32 KB of shared memory stays free per SM).
-        const bool flagged = a_flags != nullptr;
-        static int pull_sms = -1;
-        if (pull_sms < 0) { const char* e = getenv("TDL_K8_PULL_SMS"); pull_sms = e ? atoi(e) : 16; if (pull_sms < 2) pull_sms = 2; }
-        const int rsv = flagged ? pull_sms : 0;
         if (fuse_colsum)
-            rc = needs_aux ? (flagged ? launch_gemm_2cta<256, 4, true, true>(ta, tb, em, cm, p, s, rsv)
-                                      : launch_gemm_2cta<256, 5, true, true>(ta, tb, em, cm, p, s))
-                           : (flagged ? launch_gemm_2cta<256, 5, false, true>(ta, tb, em, cm, p, s, rsv)
-                                      : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, cm, p, s));
-        else if (staged && needs_aux)
-            rc = flagged ? launch_gemm_2cta<256, 4, true>(ta, tb, em, cm, p, s, rsv) : launch_gemm_2cta<256, 5, true>(ta, tb, em, cm, p, s);
+            rc = needs_aux ? launch_gemm_2cta<256, 5, true, true>(ta, tb, em, cm, p, s)
+                           : launch_gemm_2cta<256, 6, false, true>(ta, tb, em, cm, p, s);
         else
-            rc = flagged ? launch_gemm_2cta<256, 5, false>(ta, tb, em, cm, p, s, rsv) : launch_gemm_2cta<256, 6, false>(ta, tb, em, cm, p, s);
+            rc = (staged && needs_aux) ? launch_gemm_2cta<256, 5, true>(ta, tb, em, cm, p, s)
+                                       : launch_gemm_2cta<256, 6, false>(ta, tb, em, cm, p, s);
         if (!rc && colsum != nullptr && !fuse_colsum) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
         return rc;
     }
     static int exp_stages = -1;                  // TDL_GEMM_STAGES=3 selects the shallow pipeline (experiments only)
     if (exp_stages < 0) { const char* e = getenv("TDL_GEMM_STAGES"); exp_stages = e ? atoi(e) : 0; }
-    const int rsv1 = a_flags != nullptr ? 16 : 0;           // see the 2-CTA path: SMs left to the pull kernel
-    if (block_n == 256) rc = exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s, rsv1) : launch_gemm<256, 4>(ta, tb, p, s, rsv1);
-    else                rc = exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s, rsv1) : launch_gemm<128, 6>(ta, tb, p, s, rsv1);
+    if (block_n == 256) rc = exp_stages == 3 ? launch_gemm<256, 3>(ta, tb, p, s) : launch_gemm<256, 4>(ta, tb, p, s);
+    else                rc = exp_stages == 3 ? launch_gemm<128, 3>(ta, tb, p, s) : launch_gemm<128, 6>(ta, tb, p, s);
     // the 1-CTA kernel has no fused column sums: follow with the stand-alone reduction over the output
     if (!rc && colsum != nullptr) rc = tdl_bias_grad(Cout, colsum, M, N, ldc, stream);
     return rc;
@@ -1091,20 +1052,6 @@ extern "C" int tdl_allgather_gemm_bf16_ex(const void* const* a_shard_ptrs, int W
     const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
     return gemm_common(a_shard_ptrs, W, shard_rows, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, b_mn_major, bias,
                        bias_f32, epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, colsum, stream);
-}
-
-// K8, second form: A is the LOCAL gathered buffer [W * shard_rows, K] that tdl_gather_rows_flagged is filling from the
-// peers while this GEMM runs; the TMA producer waits on the tile-arrival flag of each 128-row block (flags[M / 128],
-// ready when >= flag_target).  Tiles are visited own shard first, then in the order the pull delivers them.
-extern "C" int tdl_gemm_bf16_flagged(const void* A_full, const int* flags, int flag_target, int W, int my_rank, int64_t shard_rows,
-                                     const void* B, void* Cout, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
-                                     int b_mn_major, const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out,
-                                     int64_t ld_aux, int block_n, float* colsum, void* stream) {
-    const int64_t M = shard_rows * W;
-    const void* a1[1] = {A_full};
-    const int offset = (int)((shard_rows / BLOCK_M) * my_rank);
-    return gemm_common(a1, 1, M, offset, B, Cout, nullptr, 0, 0, 0, M, N, K, lda, ldb, ldc, 0, b_mn_major, bias, bias_f32,
-                       epilogue, aux_in, aux_out, ld_aux, 0, 1, block_n, colsum, stream, flags, flag_target);
 }
 
 // K7: GEMM -> reduce-scatter (first half).  The partial product tile for rows owned by rank o is stored from

@@ -72,65 +72,7 @@ __global__ void __launch_bounds__(256) param_gather_kernel(Ptrs shards, T* __res
     }
 }
 
-// Pull for the flagged all-gather -> GEMM: copies the W row shards into the local [W * shard_rows, row_bytes] buffer in the
-// order the GEMM consumes them (own shard first, then rank+1, ...), 16 rows per work item, and bumps flags[row / 128] after
-// every item (release): a 128-row block is complete at 8 arrivals.  128 threads and ~40 registers per block, so the blocks
-// fit beside a resident GEMM CTA and the copy can never be starved by the kernel that waits for it.
-constexpr int GF_ROWS = 16;
-__global__ void __launch_bounds__(128) gather_rows_flagged_kernel(Ptrs shards, int W, int my_rank, int shard_rows, int row_vecs /*16-byte*/,
-                                                                  uint4* __restrict__ dst, int* __restrict__ flags) {
-    const int items_per_shard = shard_rows / GF_ROWS;
-    const int total = items_per_shard * W;
-    const int vecs = GF_ROWS * row_vecs;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        const int sh = (my_rank + it / items_per_shard) % W;
-        const int row0 = (it % items_per_shard) * GF_ROWS;
-        const uint4* src = reinterpret_cast<const uint4*>(shards.p[sh]) + (long long)row0 * row_vecs;
-        uint4* out = dst + ((long long)sh * shard_rows + row0) * row_vecs;
-        for (int v = threadIdx.x; v < vecs; v += 128 * 8) {              // 8 x 16 B in flight per thread (NVLink latency)
-            uint4 u[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (v + j * 128 < vecs)
-                    asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u[j].x), "=r"(u[j].y), "=r"(u[j].z), "=r"(u[j].w) : "l"(src + v + j * 128) : "memory");
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (v + j * 128 < vecs) out[v + j * 128] = u[j];
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            asm volatile("red.release.gpu.global.add.s32 [%0], 1;" :: "l"(flags + (sh * shard_rows + row0) / 128) : "memory");
-        }
-    }
-}
-
 }  // namespace
-
-// dst [W * shard_rows, row_elems] (bf16) <- the W peer shards, with tile-arrival flags (int32 [W * shard_rows / 128], zeroed by
-// the caller before the call; a block is complete at TDL_GATHER_FLAG_TARGET).  max_blocks <= 0: 2 per SM.
-extern "C" int tdl_gather_rows_flagged(const void* const* shard_ptrs, int W, int my_rank, int64_t shard_rows, int64_t row_elems,
-                                       void* dst, int* flags, int max_blocks, void* stream) {
-    TDL_REQUIRE(W >= 1 && W <= MAX_W, "world size %d unsupported", W);
-    TDL_REQUIRE(shard_rows % 128 == 0 && (row_elems * 2) % 16 == 0, "shards must be whole 128-row blocks of 16-byte aligned rows");
-    Ptrs ps{};
-    for (int i = 0; i < W; ++i) ps.p[i] = shard_ptrs[i];
-    const int total = (int)(shard_rows / GF_ROWS) * W;
-    int grid = max_blocks > 0 ? max_blocks : 4 * tdl_num_sms();
-    if (grid > total) grid = total;
-    static bool configured = false;
-    if (!configured) {
-        // SMs switch their L1 / shared-memory split only when idle: ask for the split of the tensor-core kernels this copy
-        // is meant to run beside, so its blocks are not kept off an SM that holds a GEMM CTA
-        cudaFuncSetAttribute(gather_rows_flagged_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        configured = true;
-    }
-    gather_rows_flagged_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ps, W, my_rank, (int)shard_rows,
-                                                                                         (int)(row_elems * 2 / 16),
-                                                                                         reinterpret_cast<uint4*>(dst), flags);
-    TDL_LAUNCH_CHECK();
-    return 0;
-}
 
 // shard_ptrs: W device pointers (peer-mapped) to each rank's shard of `shard_elems` elements.
 // dst: full buffer [W * shard_elems]; prev: optional snapshot of the same size (refreshed in place).

@@ -58,17 +58,6 @@ int tdl_gemm_bf16_colsum(const void* A, const void* B, void* C, int64_t M, int64
 int tdl_allgather_gemm_bf16(const void* const* a_shard_ptrs, int W, int my_rank, int64_t shard_rows, const void* B, void* C,
                             int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, const void* bias, int bias_f32,
                             int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux, int block_n, void* stream);
-/* K8 with tile-arrival flags: tdl_gather_rows_flagged pulls the W peer shards into a LOCAL [W*shard_rows, row_elems] bf16
- * buffer (own shard first; flags[row/128] += 1 per 16 rows, a 128-row block is complete at TDL_GATHER_FLAG_TARGET; the caller
- * zeroes the flags); tdl_gemm_bf16_flagged consumes that buffer while it fills, its TMA producer waiting on the flag of each
- * row block.  Every remote byte crosses NVLink once and the gathered operand stays for the wgrad of the backward pass. */
-#define TDL_GATHER_FLAG_TARGET 8
-int tdl_gather_rows_flagged(const void* const* shard_ptrs, int W, int my_rank, int64_t shard_rows, int64_t row_elems, void* dst,
-                            int* flags, int max_blocks, void* stream);
-int tdl_gemm_bf16_flagged(const void* A_full, const int* flags, int flag_target, int W, int my_rank, int64_t shard_rows,
-                          const void* B, void* C, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major,
-                          const void* bias, int bias_f32, int epilogue, const void* aux_in, void* aux_out, int64_t ld_aux,
-                          int block_n, float* colsum, void* stream);
 /* GEMM -> reduce-scatter: partial tiles are stored from the epilogue into the owner rank's staging slots */
 int tdl_gemm_scatter_bf16(const void* A, const void* B, void* const* c_ptrs, int W, int my_rank, int64_t shard_rows,
                           int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major, int block_n,

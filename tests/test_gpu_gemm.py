@@ -232,45 +232,3 @@ def test_gemm_full_lm_head_bench_shape_sampled_rows():
     assert (got - ref).abs().max().item() <= 2e-2 * (ref.abs().max().item() + 1)
     del logits
     torch.cuda.empty_cache()
-
-
-@pytest.mark.parametrize("W", [2, 8])
-def test_flagged_allgather_gemm_emulated_ranks(W):
-    """K8 with tile-arrival flags, all "ranks" on one GPU: the pull kernel fills the local operand while the GEMM consumes it."""
-    from trustworthy_dl.ops import nn as Kk, tp_ops
-    dev = torch.device("cuda", 0)
-    torch.manual_seed(20 + W)
-    shard_rows, Kd, N = 512, 512, 768
-    M = shard_rows * W
-    shards = [_mk((shard_rows, Kd), dev) for _ in range(W)]
-    w = _mk((N, Kd), dev, 0.2)
-    bias = torch.randn(N, device=dev)
-    ref = torch.cat(shards).float() @ w.float().t() + bias
-    side = torch.cuda.Stream()
-    for rank in (0, W - 1):
-        full = torch.zeros(M, Kd, device=dev, dtype=torch.bfloat16)
-        flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
-        out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
-        torch.cuda.synchronize()
-        with torch.cuda.stream(side):
-            tp_ops.gather_rows_flagged([s.data_ptr() for s in shards], rank, shard_rows, Kd, full, flags)
-        tp_ops.gemm_flagged(full, flags, W, rank, shard_rows, w, out, bias=bias)
-        torch.cuda.synchronize()
-        assert int(flags.min().item()) == tp_ops.FLAG_TARGET and int(flags.max().item()) == tp_ops.FLAG_TARGET
-        assert torch.equal(full, torch.cat(shards))
-        assert torch.allclose(out.float(), ref, atol=8e-2, rtol=2e-2), (out.float() - ref).abs().max().item()
-    # dgrad form: weight stored [K, N], GELU' multiply and the bias gradient in the epilogue
-    w2 = _mk((Kd, N), dev, 0.2)
-    aux = _mk((M, N), dev)
-    cs = torch.zeros(N, device=dev)
-    full = torch.zeros(M, Kd, device=dev, dtype=torch.bfloat16)
-    flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
-    out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
-    torch.cuda.synchronize()
-    with torch.cuda.stream(side):
-        tp_ops.gather_rows_flagged([s.data_ptr() for s in shards], 1, shard_rows, Kd, full, flags)
-    tp_ops.gemm_flagged(full, flags, W, 1, shard_rows, w2, out, b_mn=True, epilogue=Kk.EPI_MUL, aux_in=aux, colsum=cs)
-    torch.cuda.synchronize()
-    ref2 = (torch.cat(shards).float() @ w2.float()) * aux.float()
-    assert torch.allclose(out.float(), ref2, atol=0.12, rtol=3e-2), (out.float() - ref2).abs().max().item()
-    assert torch.allclose(cs, out.float().sum(0), atol=2e-3 * (M ** 0.5) + 0.05, rtol=1e-3)

@@ -220,13 +220,12 @@ class GPT2TPEngine:
         self.loss_sum = torch.zeros(1, **f32)
         # gathered operands: the K8 pull lands every [M, C] activation / gradient here once; the forward copies are kept per
         # layer because the wgrads of the backward pass consume them again (no second trip over NVLink)
-        self.k8_mode = os.environ.get("TDL_K8", "pull")            # pull | flags | tma  (see _col_parallel)
-        assert self.k8_mode in ("pull", "flags", "tma")
+        self.k8_mode = os.environ.get("TDL_K8", "pull")            # pull | tma  (see _col_parallel)
+        assert self.k8_mode in ("pull", "tma")
         self.k8_flags = self.k8_mode != "tma"                      # the gathered operand is kept locally
         self.ln_full = torch.empty(L, 2, M, C, **bf) if self.k8_flags else None
         self.full_a = torch.empty(M, C, **bf)
         self.full_b = torch.empty(M, C, **bf)
-        self.flags = torch.zeros(M // 128, dtype=torch.int32, device=dev)
         self.dln_s = torch.empty(Ms, C, **bf)
         self.dfch = torch.empty(M, Fl, **bf)
         self.datty = torch.empty(M, Cl, **bf)
@@ -248,36 +247,28 @@ class GPT2TPEngine:
                       ptr(self.epochs), i32(0), stream_ptr())
 
     def _col_parallel(self, off: int, w, out, full: Optional[torch.Tensor] = None, **kw) -> None:
-        """K8: out [M, N_local] = AG(shards at arena offset ``off``) @ w.  Three forms (``TDL_K8``):
+        """K8: out [M, N_local] = AG(shards at arena offset ``off``) @ w.  Two forms (``TDL_K8``):
 
         * ``pull`` (default): one P2P pull brings the W-1 remote shards into the local buffer ``full`` (each remote byte
           crosses NVLink exactly once, at the copy kernel's ~0.5 TB/s), then the tcgen05 GEMM runs on local memory at full
           tile rate; ``full`` stays for the wgrad of the backward pass, so no operand is ever fetched twice.
-        * ``flags``: the same pull issued as a small-footprint kernel on the copy stream with a tile-arrival flag per
-          128-row block, the GEMM running concurrently and waiting per tile.  Measured slower on B200 (2 GPUs, fc shape:
-          373 us against 68 us pull + 151 us GEMM back to back): while a persistent tensor-core grid is resident the
-          copy blocks only get the SMs reserved for them.
-        * ``tma``: the GEMM's TMA producer reads the peer shards directly; an A tile crosses NVLink once per n-block
-          (2-6x the bytes at GPT-2 medium shapes) and the wgrads pull again."""
+        * ``tma``: the GEMM's TMA producer reads the peer shards directly (plain per-CTA loads, own shard first); the
+          transfer is spread over the main loop, but an A tile crosses NVLink once per n-block (2-6x the bytes at GPT-2
+          medium shapes) and the wgrads pull the operand again.
+
+        A third form was built and measured and then removed: the pull as a small-footprint kernel on a second stream with
+        a tile-arrival flag per 128-row block, the GEMM running at the same time and waiting per tile.  On B200 (2 GPUs,
+        fc shape) it took 373 us against 68 us (pull) + 151 us (GEMM) back to back -- while a persistent tensor-core grid
+        is resident the copy blocks only ran on the SMs held back for them -- and two launches of which one spins on the
+        other have no co-scheduling guarantee on one GPU."""
         self.barrier()                                               # every rank's shard is written
         if full is None or self.k8_mode == "tma":
             tp_ops.allgather_gemm(self._peers(off), self.rank, self.Ms, w, out, **kw)
             if full is not None:
                 tp_ops.gather_rows(self._peers(off), self.Ms * self.C, full.view(-1))
             return
-        if self.k8_mode == "pull":
-            tp_ops.gather_rows(self._peers(off), self.Ms * self.C, full.view(-1))
-            tp_ops.local_gemm(full, w, out, **kw)
-            return
-        self.flags.zero_()
-        main = torch.cuda.current_stream()
-        ev0 = torch.cuda.Event(); ev0.record(main)
-        self.copy_stream.wait_event(ev0)
-        with torch.cuda.stream(self.copy_stream):
-            tp_ops.gather_rows_flagged(self._peers(off), self.rank, self.Ms, self.C, full, self.flags)
-            ev1 = torch.cuda.Event(); ev1.record(self.copy_stream)
-        tp_ops.gemm_flagged(full, self.flags, self.world, self.rank, self.Ms, w, out, **kw)
-        main.wait_event(ev1)
+        tp_ops.gather_rows(self._peers(off), self.Ms * self.C, full.view(-1))
+        tp_ops.local_gemm(full, w, out, **kw)
 
     def _row_parallel(self, a, w, out_s, bias=None, residual=None, b_mn: bool = False) -> None:
         """K7 + slot sum: out_s [Ms, C] = RS(a @ w^T) (+ bias) (+ residual)."""

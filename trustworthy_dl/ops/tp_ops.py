@@ -76,32 +76,6 @@ def gather_rows(shard_ptrs: List[int], shard_elems: int, dst: torch.Tensor):
               ptr(sums), ptr(drift), stream_ptr())
 
 
-FLAG_TARGET = 8          # TDL_GATHER_FLAG_TARGET: 16-row items per 128-row block
-
-
-def gather_rows_flagged(shard_ptrs: List[int], rank: int, shard_rows: int, row_elems: int, dst: torch.Tensor, flags: torch.Tensor,
-                        max_blocks: int = 0):
-    """Pull the W peer shards into the local ``dst [W*shard_rows, row_elems]`` (own shard first), raising ``flags[row // 128]``
-    as rows land; ``flags`` (int32, zeroed by the caller) is what :func:`gemm_flagged` waits on."""
-    W = len(shard_ptrs)
-    _lib.call("tdl_gather_rows_flagged", _arr(shard_ptrs), i32(W), i32(rank), i64(shard_rows), i64(row_elems), ptr(dst), ptr(flags),
-              i32(max_blocks), stream_ptr())
-
-
-def gemm_flagged(a_full: torch.Tensor, flags: torch.Tensor, W: int, rank: int, shard_rows: int, w: torch.Tensor, out: torch.Tensor, *,
-                 bias: Optional[torch.Tensor] = None, epilogue: int = 0, aux_in=None, aux_out=None, block_n: int = 0,
-                 b_mn: bool = False, colsum: Optional[torch.Tensor] = None):
-    """K8 with tile-arrival flags: ``out = a_full @ w^T`` (or ``@ w`` with ``b_mn``) while ``a_full`` is still being filled."""
-    if b_mn:
-        K, N = w.shape
-    else:
-        N, K = w.shape
-    bias_f32 = 1 if (bias is not None and bias.dtype == torch.float32) else 0
-    _lib.call("tdl_gemm_bf16_flagged", ptr(a_full), ptr(flags), i32(FLAG_TARGET), i32(W), i32(rank), i64(shard_rows), ptr(w), ptr(out),
-              i64(N), i64(K), i64(K), i64(w.shape[1]), i64(N), i32(b_mn), ptr(bias), i32(bias_f32), i32(epilogue), ptr(aux_in),
-              ptr(aux_out), i64(N), i32(block_n), ptr(colsum), stream_ptr())
-
-
 def local_gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, bias: Optional[torch.Tensor] = None, epilogue: int = 0,
                aux_in=None, aux_out=None, block_n: int = 0, b_mn: bool = False, colsum: Optional[torch.Tensor] = None):
     """Plain tcgen05 GEMM on an already gathered operand, same keyword surface as the fused forms."""
