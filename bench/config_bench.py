@@ -55,11 +55,11 @@ def build(name: str, world: int, args):
         data = ("openwebtext", {"seq_len": 1024})
         unit = "tokens/s"
     elif name == "gpt2_pp4dp2":
-        dp = 2 if world % 2 == 0 and world >= 4 else 1
+        dp = args.dp if args.dp else (2 if world % 2 == 0 and world >= 4 else 1)
         cfg = TrainingConfig(model_name="gpt2", model_size="medium", dataset_name="openwebtext", batch_size=args.batch or 128 * dp,
                              num_nodes=world, learning_rate=5e-5, checkpoint_interval=0, parallelism="pipeline", pp_size=world // dp,
                              dp_size=dp, micro_batches=args.micro, dtype="bf16", seq_len=1024, optimizer="adamw", migration_model="nvlink",
-                             engine=eng, **sec)
+                             engine=eng, pp_virtual=args.pp_virtual, **sec)
         att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[min(2, world - 1)], intensity=0.5,
                                                start_step=args.attack_step))
         data = ("openwebtext", {"seq_len": 1024})
@@ -129,6 +129,8 @@ def main() -> int:
     p.add_argument("--attack-step", type=int, default=8)
     p.add_argument("--micro", type=int, default=8, help="micro-batches per step of the pipeline configurations")
     p.add_argument("--no-attack", action="store_true")
+    p.add_argument("--dp", type=int, default=0, help="data-parallel replicas of the pipeline configuration (default: 2 from 4 GPUs up)")
+    p.add_argument("--pp-virtual", type=int, default=1, help="stages per pipeline rank (interleaved)")
     p.add_argument("--impl", default="ours", choices=["ours", "baseline"],
                    help="baseline = BASELINE.md baseline A: stock kernels (torch eager, cuBLAS/cuDNN/SDPA) + NCCL collectives, "
                         "security off, same box, same model/config")

@@ -100,6 +100,7 @@ class TrainingConfig:
     pp_size: int = 1
     dp_size: int = 1
     micro_batches: int = 1
+    pp_virtual: int = 1                        # stages per pipeline rank (interleaved: stage s starts on rank s % pp_size)
     device: str = "auto"
     dtype: str = "fp32"                        # fp32 | bf16 (autocast on CUDA)
     optimizer: str = "adamw"

@@ -25,6 +25,7 @@ GPT-2 in bf16 on NCCL:
 from __future__ import annotations
 
 import logging
+import os
 import time
 from typing import Any, Dict, List, Optional, Tuple
 
@@ -94,7 +95,8 @@ class FusedPipelineStrategy(PipelineStrategy):
         self.gcfg = cfg
         if self.pp > 1:
             model.untie_head()
-        self.S = S = min(self.pp, cfg.n_layer)
+        # stages: one per pipeline rank, or `pp_virtual` per rank (interleaved, stage s starts on rank s % pp)
+        self.S = S = min(self.pp * max(1, int(getattr(c, "pp_virtual", 1))), cfg.n_layer)
         self.ranges = split_layers(cfg.n_layer, S)
         kind = "1f1b" if c.parallelism == "pipeline" else "gpipe"
         self.micro = max(1, c.micro_batches if c.parallelism == "pipeline" else 1)
@@ -129,10 +131,15 @@ class FusedPipelineStrategy(PipelineStrategy):
             t.model_partitions[sid] = self.stages[sid]
             if self._owner(sid) == self.rank:
                 self.engines[sid] = self._make_engine(sid, load=True)
-        # ---- one communicator per (sender, receiver) pair and direction: a communicator carries messages one way only,
-        #      in micro-batch order, so no send can wait behind an unmatched receive.  Created for the pairs the current
-        #      stage map needs (every rank walks the same list); a reassignment adds the pairs it introduces.
-        self._pair_groups: Dict[Tuple[int, int, int], Any] = {}
+        # ---- one communicator per FLOW = (sender rank, receiver rank, direction, stage boundary): a communicator carries the
+        #      messages of one stage boundary one way only, in micro-batch order, so no send can wait behind an unmatched
+        #      receive and two flows between the same pair of ranks can never be matched against each other.  Created for
+        #      the flows the current stage map needs (every rank walks the same list); a reassignment adds its own.
+        self._pair_groups: Dict[Tuple[int, int, int, int], Any] = {}
+        self._trace = None
+        if os.environ.get("TDL_PP_TRACE"):
+            os.makedirs("gpurun_out", exist_ok=True)
+            self._trace = open(f"gpurun_out/pp_trace_rank{self.rank}.txt", "w")
         self._ensure_groups()
         self._stats_buf = torch.zeros(S, NUM_STATS, dtype=torch.float64, device=self.device)
         self._have_buf = torch.zeros(S, dtype=torch.float64, device=self.device)
@@ -144,7 +151,7 @@ class FusedPipelineStrategy(PipelineStrategy):
             for sid in range(self.S - 1):
                 a, b = self._owner(sid, d), self._owner(sid + 1, d)
                 if a != b:
-                    need.add((a, b, 0)); need.add((b, a, 1))
+                    need.add((a, b, 0, sid)); need.add((b, a, 1, sid))
         for key in sorted(need):
             if key not in self._pair_groups:
                 self._pair_groups[key] = dist.new_group([key[0], key[1]])
@@ -171,11 +178,19 @@ class FusedPipelineStrategy(PipelineStrategy):
         return eng
 
     # ------------------------------------------------------------------ transport
-    def _send(self, tensor: torch.Tensor, dst: int, direction: int):
-        return dist.isend(tensor, dst, group=self._pair_groups[(self.rank, dst, direction)])
+    def _send(self, tensor: torch.Tensor, dst: int, direction: int, boundary: int):
+        """``boundary`` = index of the lower stage of the stage boundary the message crosses."""
+        self._log(f"isend dir{direction} b{boundary} -> {dst}")
+        return dist.isend(tensor, dst, group=self._pair_groups[(self.rank, dst, direction, boundary)])
 
-    def _recv(self, tensor: torch.Tensor, src: int, direction: int):
-        return dist.irecv(tensor, src, group=self._pair_groups[(src, self.rank, direction)])
+    def _recv(self, tensor: torch.Tensor, src: int, direction: int, boundary: int):
+        self._log(f"irecv dir{direction} b{boundary} <- {src}")
+        return dist.irecv(tensor, src, group=self._pair_groups[(src, self.rank, direction, boundary)])
+
+    def _log(self, msg: str) -> None:
+        if self._trace is not None:
+            self._trace.write(f"{time.perf_counter():.4f} step {self.t.global_step} {msg}\n")
+            self._trace.flush()
 
     # ------------------------------------------------------------- one step
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
@@ -217,9 +232,9 @@ class FusedPipelineStrategy(PipelineStrategy):
             kind, s, m = op
             eng = self.engines[s]
             if kind == "F" and s > 0 and self._owner(s - 1) != self.rank:
-                pending[op] = self._recv(eng.res[m % eng.slots, 0], self._owner(s - 1), 0)
+                pending[op] = self._recv(eng.res[m % eng.slots, 0], self._owner(s - 1), 0, s - 1)
             elif kind == "B" and s < S - 1 and self._owner(s + 1) != self.rank:
-                pending[op] = self._recv(eng.dy_in[m % 2], self._owner(s + 1), 1)
+                pending[op] = self._recv(eng.dy_in[m % 2], self._owner(s + 1), 1, s)
 
         if my_ops:
             post_recv(my_ops[0])
@@ -235,6 +250,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                 (nxt[0] == "F" and nxt[2] % eng.slots == slot)))
             if early:
                 post_recv(nxt)
+            self._log(f"op {kind} s{s} m{m}")
             w = pending.pop(op, None)
             if w is not None:
                 w.wait()                                            # stream-level: the compute stream waits for the transfer
@@ -260,7 +276,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                         tensor_statistics_device(out.view(-1), out=self._stats_buf[s])
                         self._have_buf[s] = 1.0
                 elif self._owner(s + 1) != self.rank:
-                    busy[("F", s, slot)] = self._send(out, self._owner(s + 1), 0)
+                    busy[("F", s, slot)] = self._send(out, self._owner(s + 1), 0, s)
             else:
                 k = m % 2
                 reuse(("B", s, k))
@@ -269,7 +285,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                 with nvtx_range(f"pp.bwd s{s} m{m}"):
                     eng._backward(slot, k)
                 if s > 0 and self._owner(s - 1) != self.rank:
-                    busy[("B", s, k)] = self._send(eng.dx_out[k], self._owner(s - 1), 1)
+                    busy[("B", s, k)] = self._send(eng.dx_out[k], self._owner(s - 1), 1, s - 1)
             if not early and nxt is not None:
                 post_recv(nxt)
         for w in list(busy.values()) + sends:
@@ -437,7 +453,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                     elif self._owner(s - 1) == self.rank:
                         eng.res[0, 0].copy_(self.engines[s - 1].res[0, self.engines[s - 1].L])
                     else:
-                        self._recv(eng.res[0, 0], self._owner(s - 1), 0).wait()
+                        self._recv(eng.res[0, 0], self._owner(s - 1), 0, s - 1).wait()
                     eng._forward(0)
                     if eng.has_head:
                         from ..ops import nn as K
@@ -445,7 +461,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                         lg = eng.logits[:, : eng.V].float()
                         loss_sum += torch.nn.functional.cross_entropy(lg, ys[m].reshape(-1), reduction="sum").double()
                     elif self._owner(s + 1) != self.rank:
-                        self._send(eng.res[0, eng.L], self._owner(s + 1), 0).wait()
+                        self._send(eng.res[0, eng.L], self._owner(s + 1), 0, s).wait()
             have = 1.0 if S - 1 in self.engines else 0.0
             vals = comm.all_gather_vector(torch.cat([loss_sum / (self.micro * self.mb * self.T),
                                                      torch.tensor([have], dtype=torch.float64, device=self.device)]))
