@@ -152,9 +152,26 @@ class FusedPipelineStrategy(PipelineStrategy):
                 a, b = self._owner(sid, d), self._owner(sid + 1, d)
                 if a != b:
                     need.add((a, b, 0, sid)); need.add((b, a, 1, sid))
+        fresh = []
         for key in sorted(need):
             if key not in self._pair_groups:
                 self._pair_groups[key] = dist.new_group([key[0], key[1]])
+                fresh.append(key)
+        # First use of a communicator is a blocking host-side handshake that also allocates device buffers (an implicit
+        # device synchronisation).  Done lazily inside a step it deadlocks as soon as receives are posted ahead: rank A
+        # blocks in the handshake of its early irecv before it has enqueued the send that rank B's GPU is waiting for,
+        # while B's handshake waits for B's GPU to drain.  So every new flow is exercised once here, with idle devices,
+        # in one global order (each rank touches only its own flows, matched pairwise -> no cycle).
+        if fresh:
+            torch.cuda.synchronize()
+            dummy = torch.zeros(8, dtype=torch.bfloat16, device=self.device)
+            for key in fresh:
+                a, b = key[0], key[1]
+                if self.rank == a:
+                    dist.isend(dummy, b, group=self._pair_groups[key]).wait()
+                elif self.rank == b:
+                    dist.irecv(dummy, a, group=self._pair_groups[key]).wait()
+            torch.cuda.synchronize()
 
     def _dp_ranks(self, sid: int) -> List[int]:
         return [self._owner(sid, d) for d in range(self.dp)]
