@@ -28,8 +28,6 @@ int tdl_set_error(const char* fmt, ...);
 
 enum TdlDtype { TDL_F32 = 0, TDL_BF16 = 1, TDL_F16 = 2 };
 
-int tdl_small_footprint();          // runtime.cu: launch shape of the memory-bound helper kernels
-
 static inline int tdl_num_sms() {
     static int sms = 0;
     if (sms == 0) {

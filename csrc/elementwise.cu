@@ -792,17 +792,11 @@ __global__ void __launch_bounds__(256) reduce_slots_bias_kernel(const __nv_bfloa
 
 // block size / grid of a memory-bound helper kernel: 256 threads x up to 8 blocks per SM, or (small-footprint mode) 128
 // threads x 2 blocks per SM so the blocks fit beside a resident tensor-core CTA
-// An SM changes its L1 / shared-memory split only when it is idle.  A helper kernel that is meant to become resident BESIDE
-// the tensor-core CTAs of another stream therefore asks for their split (maximum shared memory), once per kernel.
-template <typename F> inline void prefer_shared_carveout(F* kernel) {
-    if (tdl_small_footprint()) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-}
-
-inline int helper_threads() { return tdl_small_footprint() ? 128 : 256; }
+// block size / grid of the memory-bound helper kernels (pack + norm, sum of squares, AdamW)
+inline int helper_threads() { return 256; }
 inline int helper_grid(long long n, int per_thread) {
-    const int th = helper_threads();
-    long long b = (n + (long long)th * per_thread - 1) / ((long long)th * per_thread);
-    const long long cap = (long long)tdl_num_sms() * (tdl_small_footprint() ? 2 : 8);
+    long long b = (n + 256ll * per_thread - 1) / (256ll * per_thread);
+    const long long cap = (long long)tdl_num_sms() * 8;
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
@@ -906,8 +900,6 @@ extern "C" int tdl_adamw(float* p32, void* p16, const void* grad, int grad_dtype
     TDL_REQUIRE(n % 4 == 0, "AdamW length must be a multiple of 4 (pad the flat buffer)");
     const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
     const int grid = helper_grid(n, 4 * 4), th = helper_threads();
-    prefer_shared_carveout(adamw_kernel<float>);
-    prefer_shared_carveout(adamw_kernel<__nv_bfloat16>);
     if (grad_dtype == TDL_F32)
         adamw_kernel<float><<<grid, th, 0, STREAM(stream)>>>(p32, (__nv_bfloat16*)p16, (const float*)grad, m, v, n, n_decay,
                                                               lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, hyper_dev);
@@ -951,7 +943,6 @@ extern "C" int tdl_xent_fwd_bwd(void* logits, const int64_t* targets, float* row
 
 extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double* sumsq, const float* scale_dev, void* stream) {
     TDL_REQUIRE(n % 8 == 0, "bucket length must be a multiple of 8");
-    prefer_shared_carveout(pack_norm_kernel);
     pack_norm_kernel<<<helper_grid(n, 8 * 4), helper_threads(), 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst_bf16, n, sumsq, scale_dev);
     TDL_LAUNCH_CHECK();
     return 0;
@@ -960,7 +951,6 @@ extern "C" int tdl_pack_norm(const float* src, void* dst_bf16, int64_t n, double
 // sumsq (device double) += sum x^2 ; the cross-rank exchange re-zeroes the accumulator after publishing it
 extern "C" int tdl_sumsq(const void* x, int dtype, int64_t n, double* sumsq, void* stream) {
     const int grid = helper_grid(n, 16), th = helper_threads();
-    prefer_shared_carveout(sumsq_kernel<float>);
     if (dtype == TDL_F32) sumsq_kernel<float><<<grid, th, 0, STREAM(stream)>>>((const float*)x, n, sumsq);
     else if (dtype == TDL_BF16) sumsq_kernel<__nv_bfloat16><<<grid, th, 0, STREAM(stream)>>>((const __nv_bfloat16*)x, n, sumsq);
     else if (dtype == TDL_F16) sumsq_kernel<__half><<<grid, th, 0, STREAM(stream)>>>((const __half*)x, n, sumsq);

@@ -86,9 +86,7 @@ template <> __device__ __forceinline__ void st_multimem_v4<float>(void* p, const
 // stats_partial: [W] dot(g_i, med) then [1] |med|^2   (doubles, accumulated with atomics)
 // store_rank < 0: the reduced vector goes to every peer (W stores, or ONE multimem.st when `mc_out` is the bucket's
 // multicast address); store_rank >= 0: only to out.p[store_rank] (ZeRO-1: the owner alone consumes its slice).
-// TPB = 64 is the variant that runs UNDER the backward pass: 2 warps x <= 128 registers fit beside a resident GEMM or
-// attention CTA (which leave ~10 K registers and a few KB of shared memory per SM).
-template <typename T, int W, int TPB>
+template <typename T, int W, int TPB = 256>
 __global__ void __launch_bounds__(TPB) trust_reduce_kernel(PeerPtrs in, PeerPtrs out, long long vec_begin, long long vec_end,
                                                            const float* __restrict__ coeff, double* __restrict__ stats_partial,
                                                            int store_rank, void* mc_out) {
@@ -393,13 +391,14 @@ extern "C" size_t tdl_exchange_pad_bytes(void) { return sizeof(ExchPad); }
 // The slice [vec_begin, vec_end) is in 16-byte vectors.  coeff: device [W].  stats_partial: device doubles
 // [W+1], accumulated (caller zeroes; the exchange kernel re-zeroes it after publishing).
 // store_rank: -1 = every peer, r = only out_ptrs[r].  mc_out: multicast (NVLS) address of the bucket or NULL.
-// threads: 256 (stand-alone) or 64 (the variant meant to run under other kernels); max_blocks <= 0: 4 x #SMs.
+// threads: 256; max_blocks <= 0: 4 x #SMs.  (A 64-thread variant meant to sit beside resident tensor-core CTAs was built
+// and dropped: the block scheduler never placed it there)
 extern "C" int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin,
                                    int64_t vec_end, const float* coeff, double* stats_partial, int store_rank, void* mc_out,
                                    int threads, int max_blocks, void* stream) {
     TDL_REQUIRE(W >= 1 && W <= MAX_W, "world size %d unsupported (1..%d)", W, MAX_W);
     TDL_REQUIRE(store_rank < W, "store_rank %d out of range", store_rank);
-    TDL_REQUIRE(threads == 256 || threads == 64, "trust_reduce: 64 or 256 threads per block");
+    TDL_REQUIRE(threads == 256, "trust_reduce: 256 threads per block");
     PeerPtrs in{}, out{};
     for (int i = 0; i < W; ++i) { in.p[i] = in_ptrs[i]; out.p[i] = out_ptrs[i]; }
     const long long nvec = vec_end - vec_begin;
@@ -409,10 +408,7 @@ extern "C" int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, 
     if (per_sm < 0) { const char* e = getenv("TDL_TR_BLOCKS"); per_sm = e ? atoi(e) : 4; if (per_sm < 1) per_sm = 1; }
     const long long cap = max_blocks > 0 ? max_blocks : (long long)tdl_num_sms() * per_sm;
     const int grid = (int)(blocks > cap ? cap : blocks);
-    // the 64-thread variant is meant to sit beside tensor-core CTAs: same L1 / shared-memory split as theirs (see param_gather.cu)
-#define LAUNCH(T, WW) do { if (threads == 64) cudaFuncSetAttribute(trust_reduce_kernel<T, WW, 64>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-                           if (threads == 256) trust_reduce_kernel<T, WW, 256><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); \
-                           else trust_reduce_kernel<T, WW, 64><<<grid, 64, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out); } while (0)
+#define LAUNCH(T, WW) trust_reduce_kernel<T, WW, 256><<<grid, 256, 0, STREAM(stream)>>>(in, out, vec_begin, vec_end, coeff, stats_partial, store_rank, mc_out)
 #define BY_W(T) switch (W) { case 1: LAUNCH(T, 1); break; case 2: LAUNCH(T, 2); break; case 3: LAUNCH(T, 3); break; \
     case 4: LAUNCH(T, 4); break; case 5: LAUNCH(T, 5); break; case 6: LAUNCH(T, 6); break; case 7: LAUNCH(T, 7); break; \
     case 8: LAUNCH(T, 8); break; }
@@ -459,12 +455,6 @@ extern "C" int tdl_exchange(void* const* pad_ptrs, int rank, int W, int which, c
     TDL_REQUIRE(W >= 1 && W <= MAX_W && count <= EXCH_MAX && (which == 0 || which == 1), "bad exchange arguments");
     PeerPtrs pads{};
     for (int i = 0; i < W; ++i) pads.p[i] = pad_ptrs[i];
-    static bool configured = false;
-    if (!configured) {            // may have to start while tensor-core CTAs hold every SM: ask for their L1 / shared split
-        cudaFuncSetAttribute(exchange_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaFuncSetAttribute(coefficients_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        configured = true;
-    }
     exchange_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, rank, W, which, vals, count, epoch_counter, zero_vals);
     TDL_LAUNCH_CHECK();
     return 0;

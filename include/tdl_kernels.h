@@ -19,9 +19,6 @@ extern "C" {
 const char* tdl_last_error(void);
 int tdl_version(void);
 int tdl_device_sm_count(void);
-/* 1: the memory-bound helper kernels (pack+norm, sum of squares, AdamW) launch 128-thread blocks, two per SM, which fit
- * beside a resident persistent GEMM / attention CTA (used for the aggregation that runs under the backward pass) */
-void tdl_set_small_footprint(int on);
 
 /* ---- K5: tensor statistics (reference attack_detector.py:78,185-200) ------------------------- */
 size_t tdl_stats_scratch_bytes(int64_t n);
@@ -109,8 +106,7 @@ size_t tdl_exchange_pad_bytes(void);
 int tdl_trust_reduce(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
                      const float* coeff, double* stats_partial, void* stream);
 /* as tdl_trust_reduce; store_rank >= 0: only out_ptrs[store_rank] receives the result (ZeRO-1 owner slice); mc_out: NVLS
- * multicast address of the bucket (one multimem.st instead of W peer stores) or NULL; threads 256, or 64 for the variant
- * small enough to run beside a resident GEMM CTA (gradient aggregation overlapped with backward); max_blocks <= 0: default */
+ * multicast address of the bucket (one multimem.st instead of W peer stores) or NULL; threads: 256; max_blocks <= 0: default */
 int tdl_trust_reduce_ex(void* const* in_ptrs, void* const* out_ptrs, int W, int dtype, int64_t vec_begin, int64_t vec_end,
                         const float* coeff, double* stats_partial, int store_rank, void* mc_out, int threads, int max_blocks,
                         void* stream);

@@ -38,14 +38,14 @@ for mangled, d in zip(names, dem):
         f.write(f"// {d}\n// {mangled}\n"); f.writelines(body)
     text = "".join(body)
     counts = {k: len(re.findall(r"\b" + re.escape(k), text)) for k in keys}
-    counts["MULTIMEM"] = len(re.findall(r"MULTIMEM|\.MMLD|\.MMST", text))
+    counts["LDGMC (multimem.ld_reduce)"] = len(re.findall(r"\bLDGMC", text))
     n_instr = len(re.findall(r"^\s+/\*[0-9a-f]{4}\*/", text, re.M))
     index.append((fname, n_instr, counts, d))
 with open(f"{out}/INDEX.md", "w") as f:
     f.write("# SASS listings per kernel (cuobjdump -sass of libtdl_kernels.so, sm_100a)\n\n")
     f.write("| file | instructions | tensor-core / TMA / TMEM / NVLS evidence | kernel |\n|---|---|---|---|\n")
     for fname, n, c, d in sorted(index):
-        ev = ", ".join(f"{k} x{v}" for k, v in c.items() if v and k in ("UTCHMMA", "UTCBAR", "UTMALDG", "UTMASTG", "UTMAREDG", "LDTM", "STTM", "MULTIMEM", "MUFU.EX2", "HMMA"))
+        ev = ", ".join(f"{k} x{v}" for k, v in c.items() if v and k in ("UTCHMMA", "UTCBAR", "UTMALDG", "UTMASTG", "UTMAREDG", "LDTM", "STTM", "LDGMC (multimem.ld_reduce)", "MUFU.EX2", "HMMA"))
         f.write(f"| {fname}.sass | {n} | {ev or '-'} | `{d[:140]}` |\n")
 print(len(index), "kernels")
 PY

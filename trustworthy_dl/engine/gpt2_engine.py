@@ -104,7 +104,6 @@ class GPT2Engine:
             n_buckets = int(os.environ.get("TDL_BUCKETS", "4"))
         self.n_buckets = max(1, min(int(n_buckets), self.L))
         self.overlap = (os.environ.get("TDL_OVERLAP", "1") != "0") if overlap is None else bool(overlap)
-        self._side_small = os.environ.get("TDL_SIDE_SMALL", "0") == "1"
         self._build_params(seed, trust_threshold, clip_ratio, dp_ranks, arena, arena_offset, pad, pad_index)
         self._build_activations()
         self.side = torch.cuda.Stream(device=self.device)
@@ -592,16 +591,7 @@ class GPT2Engine:
                     ev.record(main)
                     self.side.wait_event(ev)
                     with torch.cuda.stream(self.side):
-                        # TDL_SIDE_SMALL=1: launch the side-stream kernels as small-footprint blocks (64 / 128 threads) meant to
-                        # sit beside resident tensor-core CTAs.  Off by default: on B200 the block scheduler did not place
-                        # them beside a resident persistent GEMM grid (2 GPUs: 94.6 ms/step against 91.9 ms with normal
-                        # blocks that take their turn at kernel boundaries).
-                        small = self._side_small and i < last
-                        _lib.lib().tdl_set_small_footprint(1 if small else 0)
-                        try:
-                            self._reduce_segment(i, overlapped=small)
-                        finally:
-                            _lib.lib().tdl_set_small_footprint(0)
+                        self._reduce_segment(i, overlapped=False)
 
                 self._backward(0, 0, seg_done)
                 main.wait_stream(self.side)

@@ -180,7 +180,7 @@ class SymmetricTrustReducer:
                        owner_only: bool = False, accumulate: bool = True) -> None:
         """K2 on elements [begin, begin+numel) of the bucket with coefficients from THIS sub-bucket's norms
         (gathered from ``sumsq``, a device double): exchange norms -> coefficients -> reduce -> barrier.
-        ``overlapped``: use the small-footprint kernel variant that can run beside a resident GEMM CTA.
+        ``overlapped``: kept for callers; the reduction always uses the 256-thread kernel.
         ``owner_only``: every rank keeps only its own slice of the result (ZeRO-1).
         Statistics accumulate over the calls of a step; :meth:`enqueue_finalize` closes the step."""
         W, r = self.world, self.rank
@@ -193,8 +193,7 @@ class SymmetricTrustReducer:
         vb, ve = self.slice_of(begin, numel)
         _lib.call("tdl_trust_reduce_ex", self._bucket_ptrs, self._bucket_ptrs, i32(W), i32(_lib.DTYPE_CODES[self.dtype]),
                   i64(vb), i64(ve), ptr(self.coeff), ptr(self.partials), i32(r if owner_only else -1),
-                  None if owner_only else self._mc, i32(64 if overlapped else 256), i32(_overlap_blocks() if overlapped else 0),
-                  stream_ptr())
+                  None if owner_only else self._mc, i32(256), i32(0), stream_ptr())
         self.barrier(1)                                               # every peer's slice has landed in my bucket
 
     def enqueue_finalize(self, update_trust: bool = True, out_dev: Optional[torch.Tensor] = None,
@@ -236,10 +235,3 @@ class SymmetricTrustReducer:
         self.enqueue_local_norm()
         self.enqueue_reduce(update_trust=False)
         return self.stats, self.coeff
-
-
-def _overlap_blocks() -> int:
-    """Grid of the reduction variant that runs under the backward pass (TDL_TR_OVERLAP_BLOCKS, default 1 per SM: beside
-    a resident GEMM CTA there is shared memory for exactly one small block)."""
-    v = os.environ.get("TDL_TR_OVERLAP_BLOCKS")
-    return int(v) if v else int(_lib.lib().tdl_device_sm_count())
