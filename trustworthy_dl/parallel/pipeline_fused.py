@@ -45,7 +45,7 @@ from .symm import SymmetricBuffer
 
 logger = logging.getLogger(__name__)
 
-__all__ = ["FusedPipelineStrategy", "fused_pipeline_applicable", "split_layers"]
+__all__ = ["FusedPipelineStrategy", "fused_pipeline_applicable", "split_layers", "can_post_early", "stage_slots"]
 
 HEAD_COST = 2.7          # LM head + loss, fwd + bwd, in units of one transformer block (measured: 3 x 2.5 ms + 1.4 ms vs 3.3 ms)
 EMBED_COST = 0.1
@@ -75,6 +75,29 @@ def split_layers(n_layer: int, stages: int) -> List[Tuple[int, int]]:
     costs[-1] += HEAD_COST
     b = balanced_partition(costs, stages)
     return list(zip(b[:-1], b[1:]))
+
+
+def stage_slots(sid: int, num_stages: int, micro_batches: int, one_f_one_b: bool) -> int:
+    """Activation slots of stage ``sid``: under 1F1B at most ``num_stages - sid`` micro-batches are in flight there,
+    under GPipe order all of them."""
+    return max(1, min(micro_batches, num_stages - sid)) if one_f_one_b else micro_batches
+
+
+def can_post_early(cur: Tuple[str, int, int], nxt: Tuple[str, int, int], slots: int) -> bool:
+    """May the receive of op ``nxt`` be posted BEFORE op ``cur`` is enqueued (so the transfer runs under ``cur``)?
+
+    Not when ``cur`` still reads the buffer the receive writes: the same gradient buffer (a backward after a backward of
+    the same stage with the same micro-batch parity) or the same activation slot (a forward that re-uses the slot of the
+    micro-batch whose forward / backward runs now).  Ops of other stages never share buffers.  ``slots`` = activation
+    slots of the stage of ``cur``.  Pure function: `tests/test_pipeline_plan.py` replays whole schedules against it."""
+    kind, s, m = cur
+    if nxt[1] != s:
+        return True
+    if nxt[0] == "B" and kind == "B" and nxt[2] % 2 == m % 2:
+        return False
+    if nxt[0] == "F" and nxt[2] % slots == m % slots:
+        return False
+    return True
 
 
 class FusedPipelineStrategy(PipelineStrategy):
@@ -177,7 +200,7 @@ class FusedPipelineStrategy(PipelineStrategy):
         return [self._owner(sid, d) for d in range(self.dp)]
 
     def _slots(self, sid: int) -> int:
-        return self.micro if self.t.config.parallelism != "pipeline" else max(1, min(self.micro, self.S - sid))
+        return stage_slots(sid, self.S, self.micro, self.t.config.parallelism == "pipeline")
 
     def _make_engine(self, sid: int, load: bool, ranks: Optional[List[int]] = None):
         from ..engine.gpt2_engine import GPT2Engine
@@ -262,9 +285,7 @@ class FusedPipelineStrategy(PipelineStrategy):
             # the receive buffer of the NEXT op is free unless this op still reads it: the same gradient buffer (B after B,
             # same parity) or the same activation slot (F re-using the slot whose backward runs now)
             nxt = my_ops[i + 1] if i + 1 < len(my_ops) else None
-            early = nxt is not None and not (nxt[1] == s and (
-                (nxt[0] == kind == "B" and nxt[2] % 2 == m % 2) or
-                (nxt[0] == "F" and nxt[2] % eng.slots == slot)))
+            early = nxt is not None and can_post_early(op, nxt, eng.slots)
             if early:
                 post_recv(nxt)
             self._log(f"op {kind} s{s} m{m}")
