@@ -40,6 +40,7 @@ def main(argv=None) -> int:
     p.add_argument("--model", default="gpt2-medium")
     p.add_argument("--security", choices=["off", "reference"], default="off")
     p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--compile", action="store_true", help="wrap the stock model in torch.compile (baseline arm only)")
     args = p.parse_args(argv)
     import torch
     import torch.distributed as dist
@@ -53,10 +54,13 @@ def main(argv=None) -> int:
     torch.manual_seed(0)
     cfg = GPT2Config(**GPT2_PRESETS[args.model])
     model = GPT2LMHeadModel(cfg).to(dev)
+    if args.compile:
+        model = torch.compile(model)
     if world > 1:
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
     opt = torch.optim.AdamW(model.parameters(), lr=5e-5, weight_decay=0.01, fused=True)
     core = model.module if world > 1 else model
+    core = getattr(core, "_orig_mod", core)
     detector = trust = None
     if args.security == "reference":
         det_mod, tm_mod = _load_ref("attack_detector"), _load_ref("trust_manager")
@@ -75,7 +79,8 @@ def main(argv=None) -> int:
         idx, tgt = data[i % 4]
         with torch.autocast("cuda", dtype=torch.bfloat16):
             logits = model(idx)
-        loss = torch.nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), tgt.reshape(-1))
+            # bf16 logits straight into the loss (no fp32 copy of the 3.3 GB tensor): the arm is not handicapped
+            loss = torch.nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]), tgt.reshape(-1))
         loss.backward()
         if detector is not None:                       # reference-style: whole activation to the host, numpy/scipy stats
             flagged = detector.detect_output_anomaly(hidden["x"].float(), rank, i)

@@ -186,3 +186,53 @@ def test_hybrid_replicas_stay_in_sync_without_attack():
     res = run_distributed(_hybrid_worker, 4, None, 6, timeout=400.0)
     assert res[0]["own"] == [0] and res[2]["own"] == [0] and res[0]["wsum"] == pytest.approx(res[2]["wsum"], rel=1e-6)
     assert res[1]["wsum"] == pytest.approx(res[3]["wsum"], rel=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# bucketed aggregation (what the fused engine runs per gradient segment) against the one-bucket rule
+# ---------------------------------------------------------------------------------------------------------------------
+def _ranks(W, N, seed=0, noise=0.3):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    base = torch.randn(N, generator=g)
+    return [base + noise * torch.randn(N, generator=g) for _ in range(W)]
+
+
+@pytest.mark.parametrize("W", [2, 4, 8])
+@pytest.mark.parametrize("attack", ["none", "scale", "sign_flip", "nan", "one_bucket_only"])
+def test_bucketed_aggregation_verdicts_match_the_single_bucket_rule(W, attack):
+    """Per-bucket norms / coefficients (the segments of the overlapped engine) flag the same ranks as one coefficient
+    set over the whole gradient for every injected-poisoning scenario, and honest steps give the same aggregate."""
+    import torch
+    from trustworthy_dl.ops import reference_impl as R
+    N = 4096
+    bounds = [(0, 1024), (1024, 2048), (2048, 3072), (3072, 4096)]
+    gs = _ranks(W, N, seed=W)
+    bad = W - 1
+    if attack == "scale":
+        gs[bad] = gs[bad] * 11.0
+    elif attack == "sign_flip":
+        gs[bad] = -3.0 * gs[bad]
+    elif attack == "nan":
+        gs[bad] = gs[bad].clone(); gs[bad][::5] = float("nan")
+    elif attack == "one_bucket_only":
+        gs[bad] = gs[bad].clone(); gs[bad][1024:2048] *= 40.0          # poison confined to one segment
+    tw = torch.full((W,), 1.0 / W)
+    out_b, info_b = R.bucketed_trust_reduce(gs, bounds, tw)
+    out_1, info_1 = R.bucketed_trust_reduce(gs, [(0, N)], tw)
+    assert torch.isfinite(out_b).all() and torch.isfinite(out_1).all()
+    if attack == "none":
+        assert info_b["flags"].tolist() == info_1["flags"].tolist() == [0] * W
+        assert torch.allclose(out_b, out_1, atol=1e-5)
+        assert torch.allclose(out_b, torch.stack(gs).mean(0), atol=1e-5)
+    elif attack == "sign_flip" and W < 3:
+        pass                               # two ranks cannot tell which one flipped (cosine needs a majority); norms decide
+    else:
+        assert info_b["flags"][bad] == 1 and info_b["flags"][:bad].sum() == 0, info_b
+        if attack != "one_bucket_only":
+            assert info_1["flags"].tolist() == info_b["flags"].tolist()
+    if attack == "one_bucket_only":
+        # the per-bucket rule rejects the rank in the poisoned segment only, and still flags it for the step
+        assert info_b["rejected"][bad]
+        honest = torch.stack(gs[:bad]).mean(0)
+        assert torch.allclose(out_b[1024:2048], honest[1024:2048], atol=1e-4)

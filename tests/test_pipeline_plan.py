@@ -62,6 +62,16 @@ def _replay(S, M, owner, kind):
                 assert prev in end_time and end_time[prev] <= t, f"rank {rank}: {op} may land at {t} before {prev} finished"
             if k == "F" and m - slots >= 0:
                 assert end_time[("F", s, m - slots)] <= t
+        # co-located neighbours hand activations / gradients over by a device copy out of the producer's buffers: the copy
+        # must run before the producer re-uses that buffer (its next forward into the same slot, its next-but-one backward)
+        pos = {op: i for i, op in enumerate(my_ops)}
+        for (k, s, m) in my_ops:
+            if k == "F" and s > 0 and owner[s - 1] == rank:
+                again = ("F", s - 1, m + stage_slots(s - 1, S, M, one_f_one_b))
+                assert pos[("F", s - 1, m)] < pos[(k, s, m)] and (again not in pos or pos[(k, s, m)] < pos[again]), (rank, k, s, m)
+            if k == "B" and s < S - 1 and owner[s + 1] == rank:
+                again = ("B", s + 1, m + 2)
+                assert pos[("B", s + 1, m)] < pos[(k, s, m)] and (again not in pos or pos[(k, s, m)] < pos[again]), (rank, k, s, m)
         # slot sufficiency: between F(s, m) and B(s, m) no other forward of stage s uses the same slot
         for (k, s, m) in my_ops:
             if k != "F":

@@ -234,3 +234,42 @@ def robust_coefficients(norms: torch.Tensor, trust_weights: torch.Tensor, clip_r
     if float(tot) <= 0:
         return torch.zeros_like(n, dtype=torch.float32)
     return torch.where(valid, wv * clip / tot, torch.zeros_like(n)).float()
+
+
+def bucketed_trust_reduce(grads_per_rank: Sequence[torch.Tensor], bounds: Sequence[Tuple[int, int]], trust_weights: torch.Tensor,
+                          clip_ratio: float = 2.0, norm_ratio_max: float = 2.5, cosine_min: float = 0.0):
+    """Oracle of one STEP of the bucketed aggregation (engine/gpt2_engine.py): every bucket ``[a, b)`` is reduced with
+    coefficients from that bucket's own norms (K1 -> K3 coefficients -> K2); the verdict is taken once per step from the
+    accumulated squared norms, the "rejected in some bucket" marks and the accumulated dot / |median|^2 sums, exactly as
+    ``finalize_trust_kernel`` does.
+
+    Returns ``(reduced [N], info)`` with ``info = {norms, cos, flags, rejected}`` (per rank)."""
+    W = len(grads_per_rank)
+    g = [x.reshape(-1).float() for x in grads_per_rank]
+    out = torch.zeros_like(g[0])
+    acc_sq = torch.zeros(W, dtype=torch.float64)
+    dots = torch.zeros(W, dtype=torch.float64)
+    med2 = 0.0
+    rejected = torch.zeros(W, dtype=torch.bool)
+    for a, b in bounds:
+        parts = [x[a:b] for x in g]
+        norms = torch.stack([p.norm() for p in parts])
+        acc_sq += norms.double() ** 2
+        coeff = robust_coefficients(norms, trust_weights, clip_ratio, norm_ratio_max)
+        live = (trust_weights > 0) & torch.isfinite(norms)
+        rejected |= live & (coeff == 0)
+        red, stats = trust_weighted_reduce(parts, coeff, 0.0, norms)
+        out[a:b] = red
+        dots += stats[:, 1].double()
+        med2 += float(stats[0, 2])
+    norms = acc_sq.sqrt()
+    mn = med2 ** 0.5
+    cos = torch.where((norms > 0) & (mn > 0), dots / (norms * mn).clamp_min(1e-300), torch.ones_like(dots))
+    fin = torch.sort(norms[torch.isfinite(norms)]).values
+    ref = float(fin[(fin.numel() - 1) // 2]) if fin.numel() else 0.0
+    ok = torch.isfinite(norms) & torch.isfinite(cos) & ~rejected
+    if W >= 3:
+        ok &= cos >= cosine_min
+    if W >= 2 and ref > 0:
+        ok &= norms <= norm_ratio_max * ref
+    return out, {"norms": norms, "cos": cos, "flags": (~ok).int(), "rejected": rejected}
