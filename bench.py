@@ -195,7 +195,7 @@ def main() -> int:
     def e2e_step(i):
         losses.append(eng.train_step(host_idx[i % n_batches], host_tgt[i % n_batches]))
 
-    e2e_ms = timed(e2e_step, args.steps, 1)
+    e2e_ms = timed(e2e_step, args.steps, warm)
     e2e_value = tokens_per_step / (e2e_ms / args.steps / 1e3)
     h2d = 2 * B * T * 8
     d2h = 4 + 12 * 8
