@@ -110,6 +110,41 @@ def test_data_parallel_trust_weighted_allreduce(mode):
     assert res[0]["trust"][1] < 0.5
 
 
+def _dp_param_worker(rank, world, steps, attack_step, targets):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(rank)                                              # replicas are synchronised by setup, not by the seed
+    att = AdversarialAttacker(AttackConfig(attack_types=["model_poisoning"], target_nodes=targets, intensity=0.5,
+                                           start_step=attack_step, end_step=attack_step + 1))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=12, num_nodes=world,
+                         learning_rate=1e-3, checkpoint_interval=0, device="cpu", parallelism="data", optimizer="sgd",
+                         parameter_monitoring_enabled=True)
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 12, num_batches=steps)]
+    w = torch.cat([p.detach().reshape(-1) for p in t.model_partitions[0].parameters()])
+    return {"losses": losses, "wsum": float(w.double().sum()),
+            "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+            "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist()}
+
+
+def test_data_parallel_replica_check_flags_and_repairs_a_poisoned_replica():
+    clean = run_distributed(_dp_param_worker, 3, 8, 10 ** 6, [1])
+    res = run_distributed(_dp_param_worker, 3, 8, 5, [1])
+    assert len({r["wsum"] for r in clean}) == 1 and clean[0]["attacks"] == []   # bit-identical replicas, no false alarm
+    assert all(r["attacks"] == [(1, 5, "model_poisoning")] for r in res)        # flagged before the poisoned forward ran
+    assert len({r["wsum"] for r in res}) == 1                                   # the replica was repaired from the majority
+    assert res[0]["losses"][:4] == clean[0]["losses"][:4]
+    assert res[0]["owner"][1] != 1 and res[0]["trust"][1] < 0.5
+
+
+def test_data_parallel_replica_check_without_majority_blames_nobody():
+    res = run_distributed(_dp_param_worker, 2, 6, 4, [1])
+    assert all(r["attacks"] == [] for r in res)
+    assert len({r["wsum"] for r in res}) == 1                                   # still resynchronised
+
+
 def _tp_worker(rank, world, steps, attack_step):
     from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
     from trustworthy_dl.utils.data_loader import get_dataloader

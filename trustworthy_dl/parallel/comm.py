@@ -12,7 +12,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["init_process_group", "rank", "world_size", "send_tensor", "recv_tensor", "isend_tensor",
-           "all_gather_vector", "broadcast_float", "is_gloo"]
+           "all_gather_vector", "broadcast_float", "broadcast_tensor", "is_gloo"]
 
 _DTYPES = [torch.float32, torch.bfloat16, torch.float16, torch.int64, torch.int32, torch.float64, torch.uint8, torch.bool]
 
@@ -103,6 +103,18 @@ def all_gather_vector(v: torch.Tensor) -> torch.Tensor:
     out = torch.empty(W * x.numel(), dtype=torch.float64, device=dev)
     dist.all_gather_into_tensor(out, x)
     return out.reshape(W, -1).cpu()
+
+
+def broadcast_tensor(t: torch.Tensor, src: int) -> None:
+    """In-place broadcast of ``t`` from rank ``src`` (staged through the host on the gloo backend)."""
+    if world_size() == 1:
+        return
+    if is_gloo() and t.is_cuda:
+        h = t.detach().cpu()
+        dist.broadcast(h, src)
+        t.copy_(h)
+    else:
+        dist.broadcast(t.detach(), src)
 
 
 def broadcast_float(value: float, src: int) -> float:

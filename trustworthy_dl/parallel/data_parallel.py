@@ -52,6 +52,7 @@ class DataParallelStrategy:
         self.rank, self.world = comm.rank(), comm.world_size()
         self.device = trainer.device
         self.engine = None
+        self.flat_params = None
         self._sec_s = 0.0
         self._step_s = 0.0
 
@@ -94,6 +95,17 @@ class DataParallelStrategy:
             gdtype = torch.float32
             self.reducer = TrustAllReduce(sum(p.numel() for p in self.params), gdtype, self.device)
             flatten_grads_into(self.params, gdtype, self.device, self.reducer.buffer)
+            self.flat_params = None
+            if c.parameter_monitoring_enabled:
+                # one flat parameter vector (every ``p.data`` a view into it, before the optimizer is built) that all
+                # replicas start from bit-identically: the per-step replica check reads it with one checksum kernel
+                self.flat_params = torch.cat([p.detach().reshape(-1) for p in self.params])
+                if self.world > 1:
+                    comm.broadcast_tensor(self.flat_params, 0)
+                off = 0
+                for p in self.params:
+                    p.data = self.flat_params[off:off + p.numel()].view_as(p)
+                    off += p.numel()
             t.optimizers[0] = t._make_optimizer(self.params)
             t.schedulers[0] = t._make_scheduler(t.optimizers[0])
         # data shards play the role of stages: shard i starts on rank i
@@ -115,6 +127,8 @@ class DataParallelStrategy:
         if self.engine is not None:
             return self._engine_step(batch, t0)
         model = t.model_partitions[0]
+        if self.flat_params is not None:
+            self._check_replicas(step)
         local = self._local_batch(batch)
         self.reducer.buffer.zero_()
         loss_val, n_local = 0.0, 0
@@ -256,6 +270,49 @@ class DataParallelStrategy:
             "loss": loss, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
         return loss
+
+    def _check_replicas(self, step: int) -> None:
+        """The parameter monitor of the replicated path ("Param Monitor", reference README.md:22; the reference has no
+        code behind it).  Replicas apply the same aggregated gradient with the same optimizer, so their parameters
+        are bit-identical by construction; before every forward each rank publishes the 64-bit checksum of its flat
+        parameter vector (K9's checksum kernel, 16 bytes on the wire).  A rank that disagrees with the strict majority is
+        flagged MODEL_POISONING before it computes anything, loses its data shard, and its replica is repaired by a
+        broadcast from a majority rank.  Without a strict majority nobody is blamed; the most trusted rank's replica
+        is taken as the reference."""
+        from ..ops.integrity import checksum64
+        t = self.t
+        if t.attacker is not None:
+            t.attacker.poison_parameters(self.rank, self.params, step)
+        ck = checksum64(self.flat_params)
+        table = comm.all_gather_vector(torch.tensor([ck & 0xFFFFFFFF, ck >> 32], dtype=torch.float64))
+        keys = [(int(a), int(b)) for a, b in table.tolist()]
+        votes: Dict[tuple, int] = {}
+        for k in keys:
+            votes[k] = votes.get(k, 0) + 1
+        ref = max(votes, key=lambda k: (votes[k], -keys.index(k)))
+        if votes[ref] == self.world:
+            return
+        trust = t.trust_manager.trust_vector()
+        decisive = 2 * votes[ref] > self.world
+        if not decisive:
+            ref = keys[int(np.argmax(trust))]
+            logger.warning("step %d: replicas disagree without a majority; resynchronising from the most trusted rank", step)
+        src = max((r for r in range(self.world) if keys[r] == ref), key=lambda r: (trust[r], -r))
+        if decisive:
+            for node in (r for r in range(self.world) if keys[r] != ref):
+                t.parameter_monitor.report_mismatch(node, step)
+                if t.trust_manager.get_node_status(node).value == "compromised":
+                    continue
+                logger.error("Parameter poisoning detected on node %d", node)
+                t.attack_history.append({"node_id": node, "timestamp": time.time(), "step": step,
+                                         "attack_type": "model_poisoning",
+                                         "parameter_stats": {"checksum_mismatch": True, "repaired_from": src}})
+                t.metrics_collector.record_event("attack", node_id=node, type="model_poisoning", step=step)
+                t.trust_manager.mark_compromised(node, "model_poisoning")
+                self.reassign(node)
+                from ..core.distributed_trainer import TrainingState
+                t.training_state = TrainingState.UNDER_ATTACK
+        comm.broadcast_tensor(self.flat_params, src)
 
     def _deviation(self, node: int, st) -> float:
         em, es = self.t.node_monitor.get_expected_mean(node), self.t.node_monitor.get_expected_std(node)
