@@ -7,7 +7,7 @@ from mp_utils import run_distributed
 from trustworthy_dl.parallel.pipeline import make_schedule
 
 
-def _mp_worker(rank, world, parallelism, micro, attack_step, steps):
+def _mp_worker(rank, world, parallelism, micro, attack_step, steps, optimizer="sgd"):
     from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
     from trustworthy_dl.utils.data_loader import get_dataloader
     torch.manual_seed(0)
@@ -18,11 +18,16 @@ def _mp_worker(rank, world, parallelism, micro, attack_step, steps):
         att.activate_attacks()
     cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world,
                          learning_rate=1e-3, checkpoint_interval=0, device="cpu", parallelism=parallelism,
-                         micro_batches=micro, optimizer="sgd")
+                         micro_batches=micro, optimizer=optimizer)
     t = DistributedTrainer(cfg, attacker=att)
     t._rank, t._world = rank, world
     losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=steps)]
-    return {"losses": losses, "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+    opt_steps = {}
+    for sid, opt in t.optimizers.items():
+        st = [v for v in opt.state_dict()["state"].values()]
+        opt_steps[sid] = (int(max(float(v["step"]) for v in st)) if st and "step" in st[0] else None,
+                          sorted(st[0].keys()) if st else [])
+    return {"losses": losses, "opt_steps": opt_steps, "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
             "reassign": [(r["from_node"], r["to_node"], r["step"], r["stages"]) for r in t.reassignment_history],
             "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist(),
             "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
@@ -61,6 +66,21 @@ def test_config1_resnet32_two_stage_gloo_with_poisoned_node():
     assert a["trust"] == pytest.approx(b["trust"]) and a["trust"][1] < 0.5 < a["trust"][0]
     assert all(torch.isfinite(torch.tensor(a["losses"])))
     assert len(a["losses"]) == 18                                        # kept training after migration
+
+
+def test_migration_carries_optimizer_state():
+    """The migrated stage continues with the Adam moments and step count it had on the source rank."""
+    res = run_distributed(_mp_worker, 2, "model", 1, 12, 18, "adamw")
+    a, b = res
+    assert a["reassign"] == b["reassign"] == [(1, 0, 12, [1])]
+    assert b["opt_steps"] == {}                                          # the source rank gave the optimizer up
+    s0, s1 = a["opt_steps"][0], a["opt_steps"][1]
+    assert s0[1] == s1[1] and "exp_avg" in s1[1] and "exp_avg_sq" in s1[1]
+    assert s0[0] == 18                                                   # stage 0 never moved
+    assert s1[0] in (17, 18)                                             # 11 steps on rank 1 + the rest on rank 0 (the
+                                                                         # poisoned step's update may be dropped), not 6
+    res_sgd = run_distributed(_mp_worker, 2, "model", 1, 12, 14)
+    assert res_sgd[0]["opt_steps"][1][1] == ["momentum_buffer"]
 
 
 def test_model_parallel_matches_single_process():

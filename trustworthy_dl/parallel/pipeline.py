@@ -365,20 +365,44 @@ class PipelineStrategy:
         return dst
 
     def _migrate(self, sid: int, src: int, dst: int) -> None:
+        """Move stage ``sid`` with everything an identical continuation needs: parameters and buffers, the optimizer's
+        per-parameter state (Adam moments / momentum buffers / step counts), its hyper-parameters as the scheduler left
+        them, and the scheduler state (the reference checkpoints per-node optimizers, distributed_trainer.py:453-457, and
+        "moves" a partition at :367-380 without any of it).  One flat fp32 payload with a checksum, plus a small pickled
+        description of its layout."""
+        import io
+        import pickle
         st = self.stages[sid]
         if self.rank == src:
-            flat = torch.cat([p.detach().reshape(-1).float() for p in st.state_dict().values()
-                              if p.is_floating_point()] or [torch.zeros(1)])
+            chunks = [p.detach().reshape(-1).float() for p in st.state_dict().values() if p.is_floating_point()]
+            dev = chunks[0].device if chunks else self.device
+            opt = self.t.optimizers.pop(sid, None)
+            sched = self.t.schedulers.pop(sid, None)
+            meta = None
+            if opt is not None:
+                osd = opt.state_dict()
+                layout, scalars = [], {}
+                for idx in sorted(osd["state"]):
+                    for k, v in sorted(osd["state"][idx].items()):
+                        if torch.is_tensor(v):
+                            layout.append((idx, k, tuple(v.shape), v.dtype))
+                            chunks.append(v.detach().reshape(-1).float().to(dev))
+                        else:
+                            scalars[(idx, k)] = v
+                meta = {"layout": layout, "scalars": scalars, "param_groups": osd["param_groups"],
+                        "sched": sched.state_dict() if sched is not None else None}
+            flat = torch.cat(chunks or [torch.zeros(1, device=dev)])
             cs = float(flat.double().sum().item())
             # GPU->GPU over NVLink under NCCL (the wire device is the stage's own device); host memory under gloo
             comm.send_tensor(torch.cat([flat, torch.tensor([cs], dtype=torch.float32, device=flat.device)]), dst, tag=2)
-            opt = self.t.optimizers.pop(sid, None)
-            self.t.schedulers.pop(sid, None)
+            blob = torch.frombuffer(bytearray(pickle.dumps(meta)), dtype=torch.uint8)
+            comm.send_tensor(blob.to(dev), dst, tag=2)
             st.to("cpu")
             for p in st.parameters():
                 p.grad = None
         elif self.rank == dst:
             buf = comm.recv_tensor(src, self.device, tag=2)
+            meta = pickle.load(io.BytesIO(comm.recv_tensor(src, self.device, tag=2).cpu().numpy().tobytes()))
             flat = buf[:-1]
             if abs(float(flat.double().sum().item()) - float(buf[-1].item())) > 1e-3 * max(1.0, abs(float(buf[-1].item()))):
                 raise RuntimeError(f"stage {sid}: parameter checksum mismatch after migration {src}->{dst}")
@@ -391,7 +415,23 @@ class PipelineStrategy:
                     off += n
             for p in st.parameters():
                 p.grad = None
+            self.t.optimizers.pop(sid, None)
+            self.t.schedulers.pop(sid, None)
             self._adopt(sid)
+            opt = self.t.optimizers.get(sid)
+            if meta is not None and opt is not None:
+                state: Dict[int, Dict] = {}
+                for idx, k, shape, dtype in meta["layout"]:
+                    n = 1
+                    for d in shape:
+                        n *= d
+                    state.setdefault(idx, {})[k] = flat[off:off + n].reshape(shape).to(dtype).clone()
+                    off += n
+                for (idx, k), v in meta["scalars"].items():
+                    state.setdefault(idx, {})[k] = v
+                opt.load_state_dict({"state": state, "param_groups": meta["param_groups"]})
+                if meta["sched"] is not None and self.t.schedulers.get(sid) is not None:
+                    self.t.schedulers[sid].load_state_dict(meta["sched"])
 
     # ------------------------------------------------------------------ misc
     @torch.no_grad()
