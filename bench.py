@@ -43,7 +43,8 @@ def reference_unavailable():
     why = ("reference is not installable: /root/reference has no setup.py/pyproject.toml (pip: 'neither setup.py nor "
            "pyproject.toml found'), and distributed_trainer.py imports five modules that are not shipped "
            "(node_monitor, gradient_verification, attack_detection, metrics, model_factory)")
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", "0")) == 0:                    # one line per job, also under torchrun
+        print(json.dumps({"impl": "reference", "unavailable": why}))
     return 0
 
 
