@@ -103,7 +103,6 @@ def can_post_early(cur: Tuple[str, int, int], nxt: Tuple[str, int, int], slots: 
 class FusedPipelineStrategy(PipelineStrategy):
     # ------------------------------------------------------------------ setup
     def setup(self) -> None:
-        from ..engine.gpt2_engine import GPT2Engine, SEG_ALIGN
         t, c = self.t, self.t.config
         if c.num_nodes != self.world:
             c.num_nodes = self.world
@@ -132,16 +131,7 @@ class FusedPipelineStrategy(PipelineStrategy):
         t.stage_map.owner = [d * self.pp + (s % self.pp) for d in range(self.dp) for s in range(S)]
         t.stage_costs = [float(b - a) + (EMBED_COST if s == 0 else 0.0) + (HEAD_COST if s == S - 1 else 0.0)
                          for s, (a, b) in enumerate(self.ranges)] * self.dp
-        # ---- one world-symmetric arena for the gradient buckets of every stage, one exchange pad per stage, one
-        #      fp32 staging area for migrations; allocated once, sized for the largest stage
-        C, Vp = cfg.n_embd, cfg.padded_vocab_size
-        per_layer = 12 * C * C + 13 * C
-        self.max_p = max((b - a) * per_layer + ((Vp + cfg.n_positions) * C if s == 0 else 0) + ((Vp + 2) * C if s == S - 1 else 0)
-                         for s, (a, b) in enumerate(self.ranges)) + 8 * SEG_ALIGN
-        self.arena = SymmetricBuffer(S * self.max_p, torch.bfloat16, self.device)
-        pad_words = (int(_lib.lib().tdl_exchange_pad_bytes()) + 7) // 8
-        self.pads = SymmetricBuffer(S * pad_words, torch.int64, self.device)
-        self.mig = SymmetricBuffer(3 * self.max_p + 64, torch.float32, self.device, zero=False)
+        self._alloc_shared(cfg)
         self.n_buckets = 1 if self.dp == 1 else 2
         self.engines: Dict[int, Any] = {}
         # nn.Module view of each stage (public API: ``trainer.model_partitions``; numel for the migration model).  The live
@@ -168,6 +158,31 @@ class FusedPipelineStrategy(PipelineStrategy):
         self._have_buf = torch.zeros(S, dtype=torch.float64, device=self.device)
         self._dp_groups = {}
 
+    def _alloc_shared(self, cfg) -> None:
+        """One world-symmetric arena for the gradient buckets of every stage, one exchange pad per stage, one fp32 staging
+        area for migrations; allocated once, sized for the largest stage."""
+        from ..engine.gpt2_engine import SEG_ALIGN
+        S = self.S
+        C, Vp = cfg.n_embd, cfg.padded_vocab_size
+        per_layer = 12 * C * C + 13 * C
+        self.max_p = max((b - a) * per_layer + ((Vp + cfg.n_positions) * C if s == 0 else 0) + ((Vp + 2) * C if s == S - 1 else 0)
+                         for s, (a, b) in enumerate(self.ranges)) + 8 * SEG_ALIGN
+        self.arena = SymmetricBuffer(S * self.max_p, torch.bfloat16, self.device)
+        pad_words = (int(_lib.lib().tdl_exchange_pad_bytes()) + 7) // 8
+        self.pads = SymmetricBuffer(S * pad_words, torch.int64, self.device)
+        self.mig = SymmetricBuffer(3 * self.max_p + 64, torch.float32, self.device, zero=False)
+
+    def _sync_device(self) -> None:
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+
+    def _tensor_stats(self, x: torch.Tensor, out: torch.Tensor) -> None:
+        tensor_statistics_device(x, out=out)
+
+    def _local_grad_sumsq(self, eng) -> None:
+        """dp = 1: norm of the stage's fp32 gradients for the verifier (no bucket is packed before the verdict)."""
+        _lib.call("tdl_sumsq", ptr(eng.g32), i32(0), i64(eng.P), ptr(eng.grad_sumsq), stream_ptr())
+
     def _ensure_groups(self) -> None:
         need = set()
         for d in range(self.dp):
@@ -186,7 +201,7 @@ class FusedPipelineStrategy(PipelineStrategy):
         # while B's handshake waits for B's GPU to drain.  So every new flow is exercised once here, with idle devices,
         # in one global order (each rank touches only its own flows, matched pairwise -> no cycle).
         if fresh:
-            torch.cuda.synchronize()
+            self._sync_device()
             dummy = torch.zeros(8, dtype=torch.bfloat16, device=self.device)
             for key in fresh:
                 a, b = key[0], key[1]
@@ -194,7 +209,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                     dist.isend(dummy, b, group=self._pair_groups[key]).wait()
                 elif self.rank == b:
                     dist.irecv(dummy, a, group=self._pair_groups[key]).wait()
-            torch.cuda.synchronize()
+            self._sync_device()
 
     def _dp_ranks(self, sid: int) -> List[int]:
         return [self._owner(sid, d) for d in range(self.dp)]
@@ -299,7 +314,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                 elif self._owner(s - 1) == self.rank:
                     eng.res[slot, 0].copy_(self.engines[s - 1].res[m % self.engines[s - 1].slots, self.engines[s - 1].L])
                 if s > 0 and c.attack_detection_enabled and m == 0:       # receiver-side check of the previous stage's output
-                    tensor_statistics_device(eng.res[slot, 0].view(-1), out=self._stats_buf[s - 1])
+                    self._tensor_stats(eng.res[slot, 0].view(-1), self._stats_buf[s - 1])
                     self._have_buf[s - 1] = 1.0
                 with nvtx_range(f"pp.fwd s{s} m{m}"):
                     eng._forward(slot)
@@ -311,7 +326,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                 if eng.has_head:
                     eng.tgt[slot].copy_(self._tgt_all[m])
                     if c.attack_detection_enabled and m == 0:
-                        tensor_statistics_device(out.view(-1), out=self._stats_buf[s])
+                        self._tensor_stats(out.view(-1), self._stats_buf[s])
                         self._have_buf[s] = 1.0
                 elif self._owner(s + 1) != self.rank:
                     busy[("F", s, slot)] = self._send(out, self._owner(s + 1), 0, s)
@@ -342,7 +357,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                 with nvtx_range(f"pp.dp_sync s{sid}"):
                     eng.reduce_and_update()
             else:
-                _lib.call("tdl_sumsq", ptr(eng.g32), i32(0), i64(eng.P), ptr(eng.grad_sumsq), stream_ptr())
+                self._local_grad_sumsq(eng)
                 if scales[sid] != 1.0:                              # the poisoned bucket is what this rank would ship
                     eng.grad_sumsq.mul_(scales[sid] ** 2)
             norm_sq += eng.grad_sumsq
