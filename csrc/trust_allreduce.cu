@@ -455,6 +455,15 @@ extern "C" int tdl_exchange(void* const* pad_ptrs, int rank, int W, int which, c
     TDL_REQUIRE(W >= 1 && W <= MAX_W && count <= EXCH_MAX && (which == 0 || which == 1), "bad exchange arguments");
     PeerPtrs pads{};
     for (int i = 0; i < W; ++i) pads.p[i] = pad_ptrs[i];
+    static bool configured = false;
+    if (!configured) {
+        // These one-block kernels are issued on the side stream while persistent tensor-core CTAs hold every SM with the
+        // maximum shared-memory split; asking for the same split lets them start without waiting for an SM to go idle
+        // and be reconfigured.  (The configuration the 8-GPU numbers in profiles/r2 were measured with.)
+        cudaFuncSetAttribute(exchange_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(coefficients_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured = true;
+    }
     exchange_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, rank, W, which, vals, count, epoch_counter, zero_vals);
     TDL_LAUNCH_CHECK();
     return 0;
