@@ -46,7 +46,14 @@ def _oracle(steps, batch):
                 p -= LR * p.grad
                 p.grad = None
         losses.append(float(loss.detach()))
-    return losses, float(sum(p.detach().double().sum() for p in params))
+    val = 0.0
+    with torch.no_grad():
+        for b in _batches(2, batch):
+            h = E[b["input"]]
+            for W in Ws:
+                h = torch.tanh(h @ W)
+            val += float(torch.nn.functional.cross_entropy((h @ H).view(-1, V), b["target"].view(-1))) / 2
+    return losses, float(sum(p.detach().double().sum() for p in params)), val
 
 
 class _Reducer:
@@ -112,6 +119,11 @@ class _StageEngine:
             h.backward(self.dy_in[k])
         if x is not None:
             self.dx_out[k].copy_(x.grad)
+
+    def head_loss_sum(self, slot, targets):
+        with torch.no_grad():
+            return torch.nn.functional.cross_entropy(self.res[slot, self.L] @ self.params[-1], targets.reshape(-1),
+                                                     reduction="sum").double()
 
     def flat_grad(self):
         return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params])
@@ -195,8 +207,9 @@ def _worker(rank, world, dp, virtual, micro, batch, steps, moves):
                 assert st.reassign(src) is not None
         losses.append(t.train_step(b))
         flows.append(len(st._pair_groups))
+    val = st.validate(_batches(2, batch))
     wsum = float(sum(p.detach().double().sum() for e in st.engines.values() for p in e.params))
-    return {"losses": losses, "owner": list(t.stage_map.owner), "stages": sorted(st.engines), "wsum": wsum, "flows": flows,
+    return {"losses": losses, "val": val, "owner": list(t.stage_map.owner), "stages": sorted(st.engines), "wsum": wsum, "flows": flows,
             "ranges": list(st.ranges), "attacks": len(t.attack_history)}
 
 
@@ -212,11 +225,12 @@ def _worker(rank, world, dp, virtual, micro, batch, steps, moves):
 ])
 def test_fused_pipeline_transport_matches_single_process(world, dp, virtual, micro, batch, moves):
     steps = 6
-    ref_losses, ref_wsum = _oracle(steps, batch)
+    ref_losses, ref_wsum, ref_val = _oracle(steps, batch)
     res = run_distributed(_worker, world, dp, virtual, micro, batch, steps, moves, timeout=300)
     for r in res:
         assert r["losses"] == pytest.approx(ref_losses, rel=2e-4, abs=2e-5), (r["losses"], ref_losses)
         assert r["owner"] == res[0]["owner"] and r["attacks"] == 0
+        assert r["val"] == pytest.approx(ref_val, rel=2e-4)          # forward-only pass over the same transport
     for at, src in moves:
         assert src not in res[0]["owner"]                          # the rank gave up everything it hosted
     # every stage of every replica is hosted exactly once, and the hosted weights add up to the oracle's (x dp replicas)

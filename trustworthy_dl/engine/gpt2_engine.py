@@ -27,9 +27,9 @@ distributed_trainer.py:124-135, stage loop :153-161): activations enter and leav
 distributed_trainer.py:441-446): parameters are laid out in *segments* in the order their gradients
 complete during backward (top block group first, embeddings last).  As soon as a segment's last
 wgrad has been issued, a side stream packs it (K1), runs the trust-weighted reduction on that
-sub-bucket (K2, the 2-warp variant that fits beside a resident GEMM CTA; per-bucket norms -> per-bucket
-coefficients) and applies AdamW to it, while the main stream keeps back-propagating through lower
-blocks.  Only the last segment's reduction is exposed.  ``zero=1`` makes every rank keep and update
+sub-bucket (K2; per-bucket norms -> per-bucket coefficients) and applies AdamW to it, while the main stream
+keeps back-propagating through lower blocks.  Measured: those kernels do not become resident beside the persistent
+GEMM / attention CTAs, they take their turn at kernel boundaries, so most of the gain is the shorter exposed tail.  ``zero=1`` makes every rank keep and update
 only its slice of each segment (ZeRO-1) and pull the others' bf16 parameters with the integrity-checked
 parameter all-gather (K9: per-shard checksum vs the owner's published one + drift norm).
 """
@@ -684,6 +684,15 @@ class GPT2Engine:
         self._forward_blocks(0)
         K.linear_fwd(self.lnf[0], self.w16(self.head_name), self.logits)
         return self.logits.view(self.B, self.T, self.Vp)[..., : self.V].float()
+
+    @torch.no_grad()
+    def head_loss_sum(self, slot: int, targets: torch.Tensor) -> torch.Tensor:
+        """Summed cross-entropy (device double) of the tokens whose final LayerNorm output ``_forward(slot)`` just produced;
+        forward-only (validation of the stage that holds the head)."""
+        assert self.has_head
+        K.linear_fwd(self.lnf[slot], self.w16(self.head_name), self.logits)
+        lg = self.logits[:, : self.V].float()
+        return torch.nn.functional.cross_entropy(lg, targets.reshape(-1), reduction="sum").double()
 
     @torch.no_grad()
     def eval_loss(self, idx: torch.Tensor, targets: torch.Tensor) -> float:

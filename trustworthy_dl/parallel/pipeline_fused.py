@@ -509,10 +509,7 @@ class FusedPipelineStrategy(PipelineStrategy):
                         self._recv(eng.res[0, 0], self._owner(s - 1), 0, s - 1).wait()
                     eng._forward(0)
                     if eng.has_head:
-                        from ..ops import nn as K
-                        K.linear_fwd(eng.lnf[0], eng.w16(eng.head_name), eng.logits)
-                        lg = eng.logits[:, : eng.V].float()
-                        loss_sum += torch.nn.functional.cross_entropy(lg, ys[m].reshape(-1), reduction="sum").double()
+                        loss_sum += eng.head_loss_sum(0, ys[m])
                     elif self._owner(s + 1) != self.rank:
                         self._send(eng.res[0, eng.L], self._owner(s + 1), 0, s).wait()
             have = 1.0 if S - 1 in self.engines else 0.0
