@@ -29,7 +29,8 @@ def _batches(steps, batch):
             for _ in range(steps)]
 
 
-def _oracle(steps, batch):
+def _oracle(steps, batch, skip=None):
+    """``skip``: {step index: (a, b)} -> blocks [a, b) keep their weights in that step (a dropped stage update)."""
     E, Ws, H = _weights()
     params = [E] + Ws + [H]
     for p in params:
@@ -41,9 +42,11 @@ def _oracle(steps, batch):
             h = torch.tanh(h @ W)
         loss = torch.nn.functional.cross_entropy((h @ H).view(-1, V), b["target"].view(-1))
         loss.backward()
+        frozen = set(range(*skip[len(losses)])) if skip and len(losses) in skip else set()
         with torch.no_grad():
-            for p in params:
-                p -= LR * p.grad
+            for j, p in enumerate(params):
+                if j - 1 not in frozen or j == 0 or j == len(params) - 1:
+                    p -= LR * p.grad
                 p.grad = None
         losses.append(float(loss.detach()))
     val = 0.0
@@ -188,13 +191,18 @@ def _make_strategy(trainer):
     return Strategy(trainer)
 
 
-def _worker(rank, world, dp, virtual, micro, batch, steps, moves):
-    from trustworthy_dl import DistributedTrainer, TrainingConfig
+def _worker(rank, world, dp, virtual, micro, batch, steps, moves, attack_step=None):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    att = None
+    if attack_step is not None:
+        att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5,
+                                               start_step=attack_step))
+        att.activate_attacks()
     cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=batch, num_nodes=world,
                          learning_rate=LR, checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=micro,
-                         dp_size=dp, pp_virtual=virtual, seq_len=T, gradient_verification_enabled=False,
+                         dp_size=dp, pp_virtual=virtual, seq_len=T, gradient_verification_enabled=attack_step is not None,
                          model_kwargs={"n_layer": LAYERS, "n_positions": T})
-    t = DistributedTrainer(cfg)
+    t = DistributedTrainer(cfg, attacker=att)
     t._rank, t._world = rank, world
     t._backend_impl = _make_strategy(t)
     t._backend_impl.setup()
@@ -210,7 +218,9 @@ def _worker(rank, world, dp, virtual, micro, batch, steps, moves):
     val = st.validate(_batches(2, batch))
     wsum = float(sum(p.detach().double().sum() for e in st.engines.values() for p in e.params))
     return {"losses": losses, "val": val, "owner": list(t.stage_map.owner), "stages": sorted(st.engines), "wsum": wsum, "flows": flows,
-            "ranges": list(st.ranges), "attacks": len(t.attack_history)}
+            "ranges": list(st.ranges), "attacks": len(t.attack_history),
+            "attack_log": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+            "reassign": [(r["from_node"], r["step"], r["stages"]) for r in t.reassignment_history]}
 
 
 @pytest.mark.parametrize("world,dp,virtual,micro,batch,moves", [
@@ -241,3 +251,21 @@ def test_fused_pipeline_transport_matches_single_process(world, dp, virtual, mic
     assert res[0]["flows"][-1] >= res[0]["flows"][0]
     if moves and world == 3:
         assert res[0]["flows"][-1] > res[0]["flows"][0]            # the move created communicators for its new flows
+
+
+def test_fused_pipeline_poisoned_stage_is_flagged_moved_and_its_update_dropped():
+    """Rank 1 ships an 11x gradient at step 7: every rank flags it in that step, its stage moves (parameters intact), the
+    poisoned update is dropped -- by the old owner AND by the new one, which adopts the stage without gradients -- and
+    training continues on the new layout exactly like the single-process chain with that one update skipped."""
+    from trustworthy_dl.parallel.pipeline_fused import split_layers
+    steps, batch = 10, 8
+    a, b = split_layers(LAYERS, 3)[1]
+    ref_losses, ref_wsum, ref_val = _oracle(steps, batch, skip={6: (a, b)})
+    res = run_distributed(_worker, 3, 1, 1, 4, batch, steps, [], 7, timeout=300)
+    for r in res:
+        assert r["attack_log"] == [(1, 7, "gradient_poisoning")]
+        assert r["reassign"] == [(1, 7, [1])]
+        assert 1 not in r["owner"]
+        assert r["losses"] == pytest.approx(ref_losses, rel=2e-4, abs=2e-5), (r["losses"], ref_losses)
+        assert r["val"] == pytest.approx(ref_val, rel=2e-4)
+    assert sum(r["wsum"] for r in res) == pytest.approx(ref_wsum, rel=1e-5)

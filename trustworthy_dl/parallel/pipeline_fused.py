@@ -403,11 +403,11 @@ class FusedPipelineStrategy(PipelineStrategy):
                 t.node_monitor.record_output(node, *st)
         if self.dp == 1:
             # single holder of every stage: the (replicated) verdict gates the optimizer step of the poisoned rank
-            for sid in sorted(self.engines):
-                eng = self.engines[sid]
-                if self.rank in t._last_step_info["invalid_nodes"] or self.rank in flagged:
+            # (a stage adopted from a flagged rank during this step arrives without gradients: its update is dropped)
+            for sid in mine:
+                if sid not in self.engines or self.rank in t._last_step_info["invalid_nodes"] or self.rank in flagged:
                     continue
-                eng.reduce_and_update()
+                self.engines[sid].reduce_and_update()
         self._comm_s += comm_s
         self._step_s += time.perf_counter() - t0
         t.metrics_collector.collect_batch_metrics({
