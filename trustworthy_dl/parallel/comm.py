@@ -12,7 +12,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["init_process_group", "rank", "world_size", "send_tensor", "recv_tensor", "isend_tensor",
-           "all_gather_vector", "broadcast_float", "broadcast_tensor", "is_gloo"]
+           "all_gather_vector", "broadcast_float", "broadcast_tensor", "is_gloo", "is_short_batch"]
 
 _DTYPES = [torch.float32, torch.bfloat16, torch.float16, torch.int64, torch.int32, torch.float64, torch.uint8, torch.bool]
 
@@ -103,6 +103,24 @@ def all_gather_vector(v: torch.Tensor) -> torch.Tensor:
     out = torch.empty(W * x.numel(), dtype=torch.float64, device=dev)
     dist.all_gather_into_tensor(out, x)
     return out.reshape(W, -1).cpu()
+
+
+_short_batch_warned = False
+
+
+def is_short_batch(batch, expected: int) -> bool:
+    """The fused engines run static shapes (captured graphs, fixed activation buffers): a batch that is not the
+    configured size -- the last one of a loader without ``drop_last`` -- is skipped by every rank, with one log line."""
+    global _short_batch_warned
+    n = int(batch["input"].shape[0])
+    if n == expected:
+        return False
+    if not _short_batch_warned:
+        import logging
+        logging.getLogger(__name__).warning("skipping a batch of %d samples (configured batch_size %d): the fused engines run "
+                                            "static shapes; use drop_last or a divisible dataset", n, expected)
+        _short_batch_warned = True
+    return True
 
 
 def broadcast_tensor(t: torch.Tensor, src: int) -> None:

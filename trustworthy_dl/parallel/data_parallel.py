@@ -53,6 +53,7 @@ class DataParallelStrategy:
         self.device = trainer.device
         self.engine = None
         self.flat_params = None
+        self._last_loss = float("nan")
         self._sec_s = 0.0
         self._step_s = 0.0
 
@@ -203,6 +204,8 @@ class DataParallelStrategy:
         from ..core.trust_manager import NodeStatus, STATUS_CODES
         t, c = self.t, self.t.config
         step = t.global_step
+        if comm.is_short_batch(batch, c.batch_size):
+            return self._last_loss
         # static shapes on this path: every rank always processes its own slice; a compromised rank simply gets
         # coefficient 0 in the reduction (its shard is recorded as reassigned)
         local = {"input": batch["input"].chunk(self.world)[self.rank], "target": batch["target"].chunk(self.world)[self.rank]}
@@ -269,6 +272,7 @@ class DataParallelStrategy:
         t.metrics_collector.collect_batch_metrics({
             "loss": loss, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        self._last_loss = loss
         return loss
 
     def _check_replicas(self, step: int) -> None:

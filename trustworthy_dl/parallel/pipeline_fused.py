@@ -149,6 +149,7 @@ class FusedPipelineStrategy(PipelineStrategy):
         #      receive and two flows between the same pair of ranks can never be matched against each other.  Created for
         #      the flows the current stage map needs (every rank walks the same list); a reassignment adds its own.
         self._pair_groups: Dict[Tuple[int, int, int, int], Any] = {}
+        self._last_loss = float("nan")
         self._trace = None
         if os.environ.get("TDL_PP_TRACE"):
             os.makedirs("gpurun_out", exist_ok=True)
@@ -253,6 +254,8 @@ class FusedPipelineStrategy(PipelineStrategy):
         t0 = time.perf_counter()
         S, M = self.S, self.micro
         step = t.global_step
+        if comm.is_short_batch(batch, c.batch_size):
+            return self._last_loss
         xs = batch["input"].chunk(self.dp)[self.replica]
         ys = batch["target"].chunk(self.dp)[self.replica]
         mine = sorted(self.engines)
@@ -414,6 +417,7 @@ class FusedPipelineStrategy(PipelineStrategy):
             "loss": loss, "step": step, "epoch": t.current_epoch,
             "trust_scores": {i: t.trust_manager.get_trust_score(i) for i in range(self.world)},
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        self._last_loss = loss
         return loss
 
     # ---------------------------------------------------------- reassignment

@@ -259,6 +259,7 @@ class TensorParallelStrategy:
         self.rank, self.world = comm.rank(), comm.world_size()
         self.device = trainer.device
         self._sec_s = self._step_s = 0.0
+        self._last_loss = float("nan")
 
     def setup(self) -> None:
         global _FUSED
@@ -323,6 +324,8 @@ class TensorParallelStrategy:
         from ..core.trust_manager import NodeStatus
         t, c, eng = self.t, self.t.config, self.engine
         step = t.global_step
+        if comm.is_short_batch(batch, c.batch_size):
+            return self._last_loss
         scale = 1.0
         if t.attacker is not None and t.attacker._armed("gradient_poisoning", step, self.rank):
             i = t.attacker.config.intensity
@@ -363,6 +366,7 @@ class TensorParallelStrategy:
         t.metrics_collector.collect_batch_metrics({
             "loss": loss_val, "step": step, "epoch": t.current_epoch, "trust_scores": dict(enumerate(trust)),
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
+        self._last_loss = loss_val
         return loss_val
 
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
