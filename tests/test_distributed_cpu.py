@@ -144,7 +144,8 @@ def _dp_param_worker(rank, world, steps, attack_step, targets):
     t._rank, t._world = rank, world
     losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 12, num_batches=steps)]
     w = torch.cat([p.detach().reshape(-1) for p in t.model_partitions[0].parameters()])
-    return {"losses": losses, "wsum": float(w.double().sum()),
+    val = t._backend_impl.validate(get_dataloader("cifar10", "validation", 12, num_batches=2))
+    return {"losses": losses, "wsum": float(w.double().sum()), "val": val,
             "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
             "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist()}
 
@@ -153,6 +154,7 @@ def test_data_parallel_replica_check_flags_and_repairs_a_poisoned_replica():
     clean = run_distributed(_dp_param_worker, 3, 8, 10 ** 6, [1])
     res = run_distributed(_dp_param_worker, 3, 8, 5, [1])
     assert len({r["wsum"] for r in clean}) == 1 and clean[0]["attacks"] == []   # bit-identical replicas, no false alarm
+    assert len({r["val"] for r in clean}) == 1                                  # and one validation loss (BN statistics averaged)
     assert all(r["attacks"] == [(1, 5, "model_poisoning")] for r in res)        # flagged before the poisoned forward ran
     assert len({r["wsum"] for r in res}) == 1                                   # the replica was repaired from the majority
     assert res[0]["losses"][:4] == clean[0]["losses"][:4]

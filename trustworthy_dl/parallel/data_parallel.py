@@ -346,6 +346,14 @@ class DataParallelStrategy:
         model = self.t.model_partitions[0]
         if self.engine is not None:
             self.engine.export_to_module(model)       # the engine trains its own flat buffers: evaluate THOSE weights
+        elif self.world > 1:
+            # parameters are identical on every replica, BatchNorm running statistics are not (each rank saw its own
+            # shard): evaluate with their mean over the replicas so that every rank reports the same number
+            for b in model.buffers():
+                if b.is_floating_point():
+                    h = b.detach().cpu() if comm.is_gloo() and b.is_cuda else b.detach()
+                    torch.distributed.all_reduce(h)
+                    b.copy_(h.to(b.device) / self.world)
         model.eval()
         total, n = 0.0, 0
         for batch in loader:
