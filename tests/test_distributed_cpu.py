@@ -27,7 +27,8 @@ def _mp_worker(rank, world, parallelism, micro, attack_step, steps, optimizer="s
         st = [v for v in opt.state_dict()["state"].values()]
         opt_steps[sid] = (int(max(float(v["step"]) for v in st)) if st and "step" in st[0] else None,
                           sorted(st[0].keys()) if st else [])
-    return {"losses": losses, "opt_steps": opt_steps, "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+    return {"losses": losses, "opt_steps": opt_steps, "rx": sorted(t._backend_impl._known_rx), "tx": sorted(t._backend_impl._known_tx),
+            "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
             "reassign": [(r["from_node"], r["to_node"], r["step"], r["stages"]) for r in t.reassignment_history],
             "owner": list(t.stage_map.owner), "trust": t.trust_manager.trust_vector().tolist(),
             "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
@@ -98,6 +99,8 @@ def test_model_parallel_matches_single_process():
 def test_pipeline_1f1b_runs_and_learns():
     res = run_distributed(_mp_worker, 2, "pipeline", 4, None, 12)
     assert res[0]["losses"] == pytest.approx(res[1]["losses"])
+    # message layouts are learnt from the first header and reused (payload-only messages, no host round trip) afterwards
+    assert res[0]["tx"] == res[1]["rx"] == [("F", 0, 2)] and res[1]["tx"] == res[0]["rx"] == [("B", 0, 2)]
     assert res[0]["attacks"] == [] and res[0]["owner"] == [0, 1]
 
 

@@ -69,10 +69,13 @@ def _header(t: torch.Tensor) -> torch.Tensor:
     return h
 
 
-def isend_tensor(t: torch.Tensor, dst: int, tag: int = 0) -> List:
-    """Non-blocking typed send; returns work handles (keep the tensor alive until waited)."""
+def isend_tensor(t: torch.Tensor, dst: int, tag: int = 0, header: bool = True) -> List:
+    """Non-blocking typed send; returns work handles (keep the tensor alive until waited).  ``header=False``: the
+    receiver already knows shape and dtype (see :func:`recv_tensor`), only the payload travels."""
     dev = _comm_device(t)
     payload = t.detach().contiguous().to(dev)
+    if not header:
+        return [dist.isend(payload, dst, tag=tag), payload]
     hdr = _header(t).to(dev)
     return [dist.isend(hdr, dst, tag=tag), dist.isend(payload, dst, tag=tag), payload, hdr]
 
@@ -82,8 +85,15 @@ def send_tensor(t: torch.Tensor, dst: int, tag: int = 0) -> None:
         w.wait()
 
 
-def recv_tensor(src: int, device: torch.device, tag: int = 0) -> torch.Tensor:
+def recv_tensor(src: int, device: torch.device, tag: int = 0, like: Optional[Tuple[Tuple[int, ...], torch.dtype]] = None) -> torch.Tensor:
+    """Typed receive.  Without ``like`` the shape/dtype header is received first and read on the host (one
+    synchronisation); with ``like = (shape, dtype)`` -- a message whose layout both sides already know -- the payload is
+    received straight into a new buffer and nothing waits on the host."""
     dev = _wire_device(device)
+    if like is not None:
+        buf = torch.empty(like[0], dtype=like[1], device=dev)
+        dist.recv(buf, src, tag=tag)
+        return buf.to(device)
     hdr = torch.empty(8, dtype=torch.int64, device=dev)
     dist.recv(hdr, src, tag=tag)
     h = hdr.cpu().tolist()

@@ -90,6 +90,11 @@ class PipelineStrategy:
         self._comm_s = 0.0
         self._step_s = 0.0
         self._grad_handoff: Dict[Tuple[int, int], torch.Tensor] = {}
+        # message layouts both ends already know: key = (direction, stage boundary, micro-batch rows).  The first message
+        # of a key travels with a shape/dtype header (read on the host: one synchronisation); afterwards only the payload
+        # is sent and the receive needs no host round trip.  Cleared on every rank when the stage map changes.
+        self._known_rx: Dict[Tuple[str, int, int], Tuple[Tuple[int, ...], torch.dtype]] = {}
+        self._known_tx: set = set()
 
     # ------------------------------------------------------------------ setup
     def setup(self) -> None:
@@ -181,6 +186,18 @@ class PipelineStrategy:
                 off += n
         return {}
 
+    def _send_msg(self, x: torch.Tensor, dst: int, tag: int, key: Tuple[str, int, int]) -> List:
+        first = key not in self._known_tx
+        self._known_tx.add(key)
+        return comm.isend_tensor(x, dst, tag=tag, header=first)
+
+    def _recv_msg(self, src: int, tag: int, key: Tuple[str, int, int]) -> torch.Tensor:
+        like = self._known_rx.get(key)
+        x = comm.recv_tensor(src, self.device, tag=tag, like=like)
+        if like is None:
+            self._known_rx[key] = (tuple(x.shape), x.dtype)
+        return x
+
     # ------------------------------------------------------------- one step
     def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
         t, c = self.t, self.t.config
@@ -194,6 +211,7 @@ class PipelineStrategy:
         stage_stats = torch.zeros(S, NUM_STATS, dtype=torch.float64)
         have_stats = torch.zeros(S, dtype=torch.float64)
         losses: List[torch.Tensor] = []
+        stats_dev: Dict[int, torch.Tensor] = {}
         comm_s = 0.0
         for kind, s, m in self.schedule:
             if self._owner(s) != self.rank:
@@ -206,12 +224,12 @@ class PipelineStrategy:
                 else:
                     tc = time.perf_counter()
                     with nvtx_range(f"pp.recv_act s{s} m{m}"):
-                        x_in = comm.recv_tensor(self._owner(s - 1), self.device, tag=0)
+                        x_in = self._recv_msg(self._owner(s - 1), 0, ("F", s - 1, xs[m].shape[0]))
                     comm_s += time.perf_counter() - tc
                 if s > 0:
                     # receiver-side verification of the previous stage's output
                     if c.attack_detection_enabled and m == 0:
-                        stage_stats[s - 1] = tensor_statistics(x_in).cpu()
+                        stats_dev[s - 1] = tensor_statistics(x_in)          # stays on the device until the schedule is issued
                         have_stats[s - 1] = 1.0
                     if x_in.is_floating_point():
                         x_in.requires_grad_(True)
@@ -222,11 +240,11 @@ class PipelineStrategy:
                 acts[(s, m)] = (x_in if s > 0 else None, out)
                 if s == S - 1:
                     if c.attack_detection_enabled and m == 0:
-                        stage_stats[s] = tensor_statistics(out.detach()).cpu()
+                        stats_dev[s] = tensor_statistics(out.detach())
                         have_stats[s] = 1.0
                     losses.append(t.calculate_loss(out, ys[m]) / M)
                 elif self._owner(s + 1) != self.rank:
-                    pending_sends += comm.isend_tensor(out.detach(), self._owner(s + 1), tag=0)
+                    pending_sends += self._send_msg(out.detach(), self._owner(s + 1), 0, ("F", s, xs[m].shape[0]))
             else:
                 x_in, out = acts.pop((s, m))
                 if s == S - 1:
@@ -238,7 +256,7 @@ class PipelineStrategy:
                     else:
                         tc = time.perf_counter()
                         with nvtx_range(f"pp.recv_grad s{s} m{m}"):
-                            g = comm.recv_tensor(self._owner(s + 1), self.device, tag=1)
+                            g = self._recv_msg(self._owner(s + 1), 1, ("B", s, xs[m].shape[0]))
                         comm_s += time.perf_counter() - tc
                     with nvtx_range(f"pp.bwd s{s} m{m}"):
                         out.backward(g)
@@ -246,11 +264,14 @@ class PipelineStrategy:
                     if self._owner(s - 1) == self.rank:
                         self._grad_handoff[(s, m)] = x_in.grad
                     else:
-                        pending_sends += comm.isend_tensor(x_in.grad, self._owner(s - 1), tag=1)
+                        pending_sends += self._send_msg(x_in.grad, self._owner(s - 1), 1, ("B", s - 1, xs[m].shape[0]))
         for w in pending_sends:
             if hasattr(w, "wait"):
                 w.wait()
         self._grad_handoff.clear()
+        if stats_dev:                                              # one device->host copy for all stage statistics
+            order = sorted(stats_dev)
+            stage_stats[order] = torch.stack([stats_dev[k].double() for k in order]).cpu()
 
         # ---- local gradients: fault injection + norm --------------------------------
         my_grads = [p.grad for sid in self._my_stages() for p in self.stages[sid].parameters() if p.grad is not None]
@@ -353,6 +374,7 @@ class PipelineStrategy:
         for sid in moved:
             self._migrate(sid, src, dst)
         t.stage_map.move_all(src, dst)
+        self._known_rx.clear(); self._known_tx.clear()             # new owners have not seen any header yet
         from ..core.reassignment import estimate_migration_time
         t.reassignment_history.append({
             "from_node": src, "to_node": dst, "timestamp": time.time(), "step": t.global_step, "stages": moved,
