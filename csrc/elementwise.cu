@@ -790,9 +790,7 @@ __global__ void __launch_bounds__(256) reduce_slots_bias_kernel(const __nv_bfloa
     }
 }
 
-// block size / grid of a memory-bound helper kernel: 256 threads x up to 8 blocks per SM, or (small-footprint mode) 128
-// threads x 2 blocks per SM so the blocks fit beside a resident tensor-core CTA
-// block size / grid of the memory-bound helper kernels (pack + norm, sum of squares, AdamW)
+// block size / grid of the memory-bound helper kernels (pack + norm, sum of squares, AdamW): 256 threads, <= 8 blocks per SM
 inline int helper_threads() { return 256; }
 inline int helper_grid(long long n, int per_thread) {
     long long b = (n + 256ll * per_thread - 1) / (256ll * per_thread);
