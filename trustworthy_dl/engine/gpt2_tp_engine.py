@@ -7,7 +7,8 @@ the MLP run on **local heads / local hidden columns** over all ``M`` tokens.
 
 Per block, forward (rank r):
 
-    LayerNorm(shard) -> symmetric buffer ---barrier---> K8  AG(ln1) @ Wqkv_r^T + b    [M, 3C/W]   (TMA pulls peer tiles)
+    LayerNorm(shard) -> symmetric buffer ---barrier---> K8  AG(ln1) @ Wqkv_r^T + b    [M, 3C/W]   (one P2P pull, then the GEMM;
+                                                                                        TDL_K8=tma: TMA reads of the peer tiles)
     attention on the C/W local heads (csrc/attention.cu)                               [M, C/W]
     K7  atty_r @ Wo_r^T -> TMA stores of partial tiles into the OWNER's slots ---barrier---> sum slots + bias + residual
     LayerNorm(shard) -> symmetric buffer ---barrier---> K8  AG(ln2) @ Wfc_r^T, GELU epilogue saving GELU'  [M, 4C/W]
