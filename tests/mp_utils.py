@@ -35,12 +35,22 @@ def run_distributed(fn, world: int, *args, timeout: float = 240.0):
     procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, results)) for r in range(world)]
     for p in procs:
         p.start()
-    for p in procs:
-        p.join(timeout)
-    alive = [p for p in procs if p.is_alive()]
-    for p in alive:
-        p.kill()
-    assert not alive, "distributed test timed out"
+    import time
+    deadline = time.time() + timeout
+    while any(p.is_alive() for p in procs) and time.time() < deadline:
+        if any(v[0] == "err" for v in dict(results).values()):
+            break                                  # a rank failed: its peers would wait for it in a collective until the deadline
+        time.sleep(0.1)
+    alive = [i for i, p in enumerate(procs) if p.is_alive()]
+    if alive:
+        if any(v[0] == "err" for v in dict(results).values()):
+            time.sleep(1.0)                        # let the other ranks report their own exception, if any
+        failed = {r: v[1] for r, v in dict(results).items() if v[0] == "err"}
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+        assert not failed, "\n".join(f"rank {r} failed:\n{tb}" for r, tb in sorted(failed.items()))
+        raise AssertionError(f"distributed test timed out (ranks {alive} still running after {timeout:.0f} s)")
     out = []
     for r in range(world):
         status, val = results.get(r, ("err", "no result"))

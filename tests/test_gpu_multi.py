@@ -40,12 +40,23 @@ def _run(fn, world):
     procs = [ctx.Process(target=_entry, args=(r, world, port, fn, ret)) for r in range(world)]
     for p in procs:
         p.start()
-    for p in procs:
-        p.join(240)
-    for p in procs:
-        if p.is_alive():
-            p.kill()
-            pytest.fail("multi-GPU worker timed out")
+    import time
+    deadline = time.time() + 240
+    while any(p.is_alive() for p in procs) and time.time() < deadline:
+        if any(v[0] == "err" for v in dict(ret).values()):
+            break                                  # a rank failed: its peers would wait for it in a collective until the deadline
+        time.sleep(0.2)
+    failed = {r: v[1] for r, v in dict(ret).items() if v[0] == "err"}
+    hung = [i for i, p in enumerate(procs) if p.is_alive()]
+    if hung:
+        time.sleep(2.0 if failed else 0.0)         # let the other ranks report their own exception, if any
+        failed = {r: v[1] for r, v in dict(ret).items() if v[0] == "err"}
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+        if failed:
+            pytest.fail("\n".join(f"rank {r}:\n{tb}" for r, tb in sorted(failed.items())))
+        pytest.fail(f"multi-GPU workers timed out (ranks {hung} still running after 240 s, no rank reported an exception)")
     out = []
     for r in range(world):
         st, val = ret.get(r, ("err", "no result"))
