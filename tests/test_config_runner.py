@@ -62,6 +62,11 @@ def test_runner_end_to_end_artifacts(tmp_path):
     data = json.loads((out / "chart_data.json").read_text())
     assert len(data["trust_evolution"]["nodes"]["1"]) == 3
     assert data["trust_evolution"]["nodes"]["1"][-1] < data["trust_evolution"]["nodes"]["0"][-1]  # measured, not simulated
+    so = s["security_outcomes"]                               # README "key findings", measured from this run's histories
+    assert so["attacked_nodes"] == [1] and so["detected_nodes"] == [1] and so["missed_nodes"] == [] and so["false_positive_nodes"] == []
+    assert so["detection_latency_steps"] == {"1": 0} and so["detection_rate"] == 1.0        # flagged the step it was injected
+    assert so["reassignment_time_estimated_s"] > 0 and so["loss_before_attack"] > 0
+    assert "Measured attack outcomes" in (out / "experiment_report.md").read_text()
 
 
 def test_runner_cli_honours_config(tmp_path):

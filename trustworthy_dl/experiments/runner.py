@@ -232,7 +232,50 @@ class ExperimentRunner:
                             "compromised_nodes": len(self.trainer.trust_manager.get_compromised_nodes()),
                             "total_attacks_detected": ts.get("total_attacks", 0),
                             "reassignments": len(self.trainer.reassignment_history)})
+            summary["security_outcomes"] = self._security_outcomes()
         return summary
+
+    def _security_outcomes(self) -> Dict[str, Any]:
+        """The quantities README.md:140-156 lists as findings, measured from this run's histories (the reference plots
+        simulated curves instead, experiment_runner.py:430-519): detection latency per attacked node, nodes missed /
+        wrongly flagged, what the reassignments cost, how far the loss moved and how long it took to come back."""
+        tr, at = self.trainer, self.attacker
+        if tr is None:
+            return {}
+        injected: Dict[int, int] = {}                               # node -> first step it injected a fault
+        for e in (at.log if at is not None else []):
+            if e.get("node_id") is not None:
+                injected.setdefault(int(e["node_id"]), int(e["step"]))
+        detected: Dict[int, int] = {}                               # node -> first step it was flagged
+        for a in tr.attack_history:
+            detected.setdefault(int(a["node_id"]), int(a["step"]))
+        latency = {n: detected[n] - s for n, s in injected.items() if n in detected and detected[n] >= s}
+        false_pos = sorted(n for n, s in detected.items() if n not in injected or s < injected[n])
+        missed = sorted(n for n in injected if n not in latency)
+        out: Dict[str, Any] = {
+            "attacked_nodes": sorted(injected), "detected_nodes": sorted(detected),
+            "detection_latency_steps": {str(n): v for n, v in sorted(latency.items())},
+            "mean_detection_latency_steps": float(np.mean(list(latency.values()))) if latency else None,
+            "missed_nodes": missed, "false_positive_nodes": false_pos,
+            "detection_rate": (len(latency) / len(injected)) if injected else None,
+            "reassignment_time_measured_s": float(sum(r.get("measured_time", 0.0) or 0.0 for r in tr.reassignment_history)),
+            "reassignment_time_estimated_s": float(sum(r.get("migration_time", 0.0) or 0.0 for r in tr.reassignment_history))}
+        losses = [m["loss"] for m in self.results_data["training_metrics"]]     # entry i = global step i + 1
+        if injected and losses:
+            k = min(injected.values())                              # first poisoned step (1-based)
+            before = losses[max(0, k - 6):k - 1]
+            if before:
+                base = float(np.mean(before))
+                after = losses[k - 1:]
+                out["loss_before_attack"] = base
+                out["peak_loss_after_attack"] = float(max(after[:10])) if after else None
+                rec = None
+                for j in range(len(after)):
+                    if float(np.mean(after[j:j + 3])) <= 1.05 * base:
+                        rec = j
+                        break
+                out["recovery_steps"] = rec                         # steps until a 3-step mean is back within 5 % of the level before
+        return out
 
     # --------------------------------------------------------------- artefacts
     def _save_results(self, results: Dict[str, Any]) -> None:
@@ -364,7 +407,18 @@ class ExperimentRunner:
             f"- **Compromised Nodes**: {s.get('compromised_nodes', 'N/A')}",
             f"- **Total Attacks Detected**: {s.get('total_attacks_detected', 'N/A')}",
             f"- **Reassignments**: {s.get('reassignments', 'N/A')}",
-            f"- **Detector flags**: {det.get('total_detections', 'N/A')}", "", "## Attack / reassignment log"]
+            f"- **Detector flags**: {det.get('total_detections', 'N/A')}"]
+        so = s.get("security_outcomes") or {}
+        if so:
+            lines += ["", "### Measured attack outcomes",
+                      f"- **Attacked nodes**: {so.get('attacked_nodes')} — **flagged**: {so.get('detected_nodes')}",
+                      f"- **Detection latency (steps after the first injected fault)**: {so.get('detection_latency_steps')}",
+                      f"- **Missed nodes**: {so.get('missed_nodes')} — **false positives**: {so.get('false_positive_nodes')}",
+                      f"- **Reassignment time**: {self._fmt(so.get('reassignment_time_measured_s'), '.3f')} s measured, "
+                      f"{self._fmt(so.get('reassignment_time_estimated_s'), '.3f')} s by the migration model",
+                      f"- **Loss before / peak after the attack**: {self._fmt(so.get('loss_before_attack'), '.4f')} / "
+                      f"{self._fmt(so.get('peak_loss_after_attack'), '.4f')}; **recovery**: {so.get('recovery_steps')} steps"]
+        lines += ["", "## Attack / reassignment log"]
         for a in results.get("attack_history", [])[:20]:
             lines.append(f"- step {a.get('step')}: node {a.get('node_id')} — {a.get('attack_type')}")
         for r in results.get("reassignment_history", [])[:20]:
