@@ -35,6 +35,7 @@ setup(
     entry_points={"console_scripts": [
         "trustworthy-dl-train=trustworthy_dl.cli:main",
         "trustworthy-dl-experiment=trustworthy_dl.experiments.runner:main",
+        "trustworthy-dl-sweep=trustworthy_dl.experiments.sweep:main",
     ]},
     cmdclass={"build_ext": build_ext},
 )

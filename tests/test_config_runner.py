@@ -81,3 +81,16 @@ def test_report_with_empty_summary_does_not_raise(tmp_path):
     cfg = ExperimentConfig("e", "resnet32", "cifar10", 2, 1, 4, 1e-3, output_dir=str(tmp_path))
     text = ExperimentRunner(cfg)._create_report_content({"experiment_summary": {}})            # Q18
     assert "N/A" in text
+
+
+def test_attack_sweep_tabulates_measured_outcomes(tmp_path):
+    from trustworthy_dl.experiments.sweep import attack_sweep
+    base = ExperimentConfig(experiment_name="s", model_name="resnet32", dataset_name="cifar10", num_nodes=2, num_epochs=3,
+                            batch_size=4, learning_rate=1e-3, attack_start_epoch=2, target_nodes=[1], steps_per_epoch=6,
+                            output_dir=str(tmp_path), training_overrides={"device": "cpu"})
+    rows = attack_sweep(base, ["gradient_poisoning"], [0.5], ["scale"])
+    assert [r["attack_type"] for r in rows] == ["none", "gradient_poisoning"]
+    assert rows[0]["attacks_detected"] == 0 and rows[0]["false_positive_nodes"] == []          # clean run: nothing flagged
+    assert rows[1]["detection_rate"] == 1.0 and rows[1]["mean_detection_latency_steps"] == 0.0 and rows[1]["missed_nodes"] == []
+    table = (tmp_path / "sweep_table.md").read_text()
+    assert "scale" in table and (tmp_path / "sweep_results.json").exists()
