@@ -80,8 +80,6 @@ def test_migration_carries_optimizer_state():
     assert s0[0] == 18                                                   # stage 0 never moved
     assert s1[0] in (17, 18)                                             # 11 steps on rank 1 + the rest on rank 0 (the
                                                                          # poisoned step's update may be dropped), not 6
-    res_sgd = run_distributed(_mp_worker, 2, "model", 1, 12, 14)
-    assert res_sgd[0]["opt_steps"][1][1] == ["momentum_buffer"]
 
 
 def test_model_parallel_matches_single_process():

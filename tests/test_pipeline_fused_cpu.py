@@ -224,7 +224,6 @@ def _worker(rank, world, dp, virtual, micro, batch, steps, moves, attack_step=No
 
 
 @pytest.mark.parametrize("world,dp,virtual,micro,batch,moves", [
-    (2, 1, 1, 4, 8, []),                   # plain 1F1B over two stages
     (2, 1, 2, 4, 8, [(3, 1)]),             # interleaved stages {0,2} / {1,3}; then rank 0 hosts everything (local hand-offs only)
     (3, 1, 1, 4, 8, [(2, 1)]),             # a middle stage moves: new flows between ranks that never talked before
     (3, 1, 2, 6, 12, [(2, 2)]),            # six interleaved stages on three ranks, the rank with the head gives its stages up
