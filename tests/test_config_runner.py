@@ -67,6 +67,9 @@ def test_runner_end_to_end_artifacts(tmp_path):
     assert so["detection_latency_steps"] == {"1": 0} and so["detection_rate"] == 1.0        # flagged the step it was injected
     assert so["reassignment_time_estimated_s"] > 0 and so["loss_before_attack"] > 0
     assert "Measured attack outcomes" in (out / "experiment_report.md").read_text()
+    m = res["training_results"]["training_metrics"][-1]
+    det = res["detection_statistics"]
+    assert det["true_positive_rate"] > 0 and det["false_positive_rate"] == 0     # counters fed from the injector's ground truth
 
 
 def test_runner_cli_honours_config(tmp_path):

@@ -512,7 +512,9 @@ class DistributedTrainer:
         self._last_step_info = {}
         self._heartbeat()
         if self._backend_impl is not None:
-            return self._backend_impl.train_step(batch)
+            loss_val = self._backend_impl.train_step(batch)
+            self._score_detection()
+            return loss_val
         t0 = time.perf_counter()
         if self.attacker is not None and self.config.parameter_monitoring_enabled:
             for sid, part in self.model_partitions.items():
@@ -537,7 +539,24 @@ class DistributedTrainer:
             "loss": loss_val, "step": self.global_step, "epoch": self.current_epoch,
             "trust_scores": {i: self.trust_manager.get_trust_score(i) for i in range(self.config.num_nodes)},
             "step_time": time.perf_counter() - t0, "samples": n})
+        self._score_detection()
         return loss_val
+
+    def _score_detection(self) -> None:
+        """With a fault injector attached the ground truth of every step is known: feed the detector's TP / FP counters
+        and the metrics collector's detection / false-positive rates (README.md:160; the reference declares the counters,
+        attack_detector.py:62-67, and never increments them).  One entry per node that hosts work or was flagged."""
+        if self.attacker is None:
+            return
+        step = self.global_step
+        flagged = {a["node_id"] for a in self.attack_history if a.get("step") == step}
+        for node in range(self.config.num_nodes):
+            truth = self.attacker.was_attacked(step, node)
+            hit = node in flagged
+            if not hit and self.trust_manager.get_node_status(node).value == "compromised":
+                continue                                     # excluded in an earlier step: no longer a sample either way
+            self.attack_detector.record_ground_truth(truth, hit)
+            self.metrics_collector.record_detection(hit, truth)
 
     def train_epoch(self, dataloader, epoch: int) -> float:
         self.current_epoch = epoch
