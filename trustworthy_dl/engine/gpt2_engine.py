@@ -342,12 +342,9 @@ class GPT2Engine:
         self._refresh_working_copies()
 
     # ---- stage migration (trust-driven reassignment): everything a new owner needs to continue bit-identically ----
-    def migration_tensors(self) -> List[torch.Tensor]:
-        """Flat tensors that move with the stage: fp32 master parameters, both Adam moments, the optimizer clock and
-        the cross-rank exchange epochs (so the new owner's barriers line up with the stage's other replicas)."""
-        return [self.p32, self.m, self.v, self.hyper, self.reducer.epochs]
-
     def after_migration(self) -> None:
+        """Called by the pipeline strategy once the stage's state (fp32 master parameters, both Adam moments, the optimizer
+        clock, the cross-rank exchange epochs) has been copied into this engine's buffers."""
         self._refresh_working_copies()
 
     # ------------------------------------------------------------------ activations

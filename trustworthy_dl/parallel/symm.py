@@ -223,10 +223,6 @@ class SymmetricTrustReducer:
         self.barrier(1)
 
     # ---- convenience (eager DP strategy) --------------------------------------------------------
-    def load_trust(self, trust_values, status_codes) -> None:
-        self.trust.copy_(torch.as_tensor(trust_values, dtype=torch.float32))
-        self.status.copy_(torch.as_tensor(status_codes, dtype=torch.int32))
-
     def reduce_(self, trust_weights: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
         """Eager path: weights given by the host trust manager (already zero for compromised ranks).  Returns device
         tensors ``(stats[W,4], coeff[W])`` that stay valid until the next call (no clone, no sync)."""
