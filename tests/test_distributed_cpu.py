@@ -294,3 +294,39 @@ def test_bucketed_aggregation_verdicts_match_the_single_bucket_rule(W, attack):
         assert info_b["rejected"][bad]
         honest = torch.stack(gs[:bad]).mean(0)
         assert torch.allclose(out_b[1024:2048], honest[1024:2048], atol=1e-4)
+
+
+def _resume_worker(rank, world, ckpt_dir, phase, attack_step):
+    """phase 'a': train 14 steps (attack + reassignment at ``attack_step``), checkpoint at step 14, train 4 more.
+    phase 'b': fresh trainers resume from the step-14 files and train the same 4 steps."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5,
+                                           start_step=attack_step))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=2, optimizer="adamw",
+                         checkpoint_dir=ckpt_dir)
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    batches = list(get_dataloader("cifar10", "train", 8, num_batches=18))
+    if phase == "a":
+        for b in batches[:14]:
+            t.train_step(b)
+        t.save_checkpoint()
+    else:
+        t.load_checkpoint()
+    tail = [t.train_step(b) for b in batches[14:]]
+    return {"tail": tail, "owner": list(t.stage_map.owner), "opt": sorted(t.optimizers), "step": t.global_step}
+
+
+def test_multi_process_resume_after_reassignment(tmp_path):
+    """Per-rank checkpoint files written after a stage changed hands: resumed ranks take over the saved ownership (modules,
+    optimizers with their state) and continue exactly like the run that was not interrupted."""
+    a = run_distributed(_resume_worker, 2, str(tmp_path), "a", 10)
+    b = run_distributed(_resume_worker, 2, str(tmp_path), "b", 10)
+    assert a[0]["owner"] == b[0]["owner"] == [0, 0] and a[0]["opt"] == b[0]["opt"] == [0, 1] and b[1]["opt"] == []
+    assert b[0]["step"] == 18
+    assert b[0]["tail"] == pytest.approx(a[0]["tail"], rel=1e-5)
+    assert b[1]["tail"] == pytest.approx(b[0]["tail"])

@@ -128,6 +128,21 @@ class _StageEngine:
             return torch.nn.functional.cross_entropy(self.res[slot, self.L] @ self.params[-1], targets.reshape(-1),
                                                      reduction="sum").double()
 
+    device = torch.device("cpu")
+
+    def state_dict(self):
+        return {"flat": torch.cat([p.detach().reshape(-1) for p in self.params])}
+
+    def load_state_dict(self, sd):
+        off = 0
+        with torch.no_grad():
+            for p in self.params:
+                p.copy_(sd["flat"][off:off + p.numel()].view_as(p))
+                off += p.numel()
+
+    def export_to_module(self, model):
+        pass
+
     def flat_grad(self):
         return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params])
 
@@ -268,3 +283,40 @@ def test_fused_pipeline_poisoned_stage_is_flagged_moved_and_its_update_dropped()
         assert r["losses"] == pytest.approx(ref_losses, rel=2e-4, abs=2e-5), (r["losses"], ref_losses)
         assert r["val"] == pytest.approx(ref_val, rel=2e-4)
     assert sum(r["wsum"] for r in res) == pytest.approx(ref_wsum, rel=1e-5)
+
+
+def _resume_worker(rank, world, ckpt_dir, phase):
+    """'a': 4 steps with a move before step 2, checkpoint, 2 more steps.  'b': fresh ranks resume the step-4 files."""
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=8, num_nodes=world, learning_rate=LR,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=4, dp_size=1, pp_virtual=2,
+                         seq_len=T, gradient_verification_enabled=False, checkpoint_dir=ckpt_dir,
+                         model_kwargs={"n_layer": LAYERS, "n_positions": T})
+    t = DistributedTrainer(cfg)
+    t._rank, t._world = rank, world
+    t._backend_impl = _make_strategy(t)
+    t._backend_impl.setup()
+    st = t._backend_impl
+    batches = _batches(6, 8)
+    if phase == "a":
+        for i, b in enumerate(batches[:4]):
+            if i == 2:
+                t.global_step = i
+                assert st.reassign(1) is not None
+            t.train_step(b)
+        t.save_checkpoint()
+    else:
+        t.load_checkpoint()
+    tail = [t.train_step(b) for b in batches[4:]]
+    return {"tail": tail, "owner": list(t.stage_map.owner), "stages": sorted(st.engines), "step": t.global_step}
+
+
+def test_fused_pipeline_resume_after_reassignment(tmp_path):
+    ref_losses, _, _ = _oracle(6, 8)
+    a = run_distributed(_resume_worker, 3, str(tmp_path), "a", timeout=300)
+    b = run_distributed(_resume_worker, 3, str(tmp_path), "b", timeout=300)
+    assert a[0]["owner"] == b[0]["owner"] and 1 not in b[0]["owner"] and b[1]["stages"] == []
+    assert [r["stages"] for r in a] == [r["stages"] for r in b]
+    for r in a + b:
+        assert r["tail"] == pytest.approx(ref_losses[4:], rel=2e-4)
+    assert b[0]["step"] == 6

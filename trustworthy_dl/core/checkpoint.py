@@ -66,6 +66,13 @@ def load_checkpoint(trainer, path: str, strict: bool = True, restore_rng: bool =
     ckpt = torch.load(path, map_location="cpu", weights_only=False)
     trainer.current_epoch = int(ckpt["epoch"])
     trainer.global_step = int(ckpt["global_step"])
+    impl = getattr(trainer, "_backend_impl", None)
+    # ownership first: a run that reassigned stages before it was checkpointed resumes with THAT map, and a rank must host
+    # (module on its device, optimizer / stage engine created) what the map gives it before the states below are loaded
+    if ckpt.get("stage_map") and trainer.stage_map is not None:
+        trainer.stage_map.load_state_dict(ckpt["stage_map"])
+        if hasattr(impl, "sync_ownership"):
+            impl.sync_ownership()
     for k, sd in ckpt["model_partitions"].items():
         if k in trainer.model_partitions:
             trainer.model_partitions[k].load_state_dict(sd, strict=strict)
@@ -86,8 +93,6 @@ def load_checkpoint(trainer, path: str, strict: bool = True, restore_rng: bool =
         trainer.gradient_verifier.load_state_dict(ckpt["gradient_verifier"])
     if ckpt.get("node_monitor"):
         trainer.node_monitor.load_state_dict(ckpt["node_monitor"])
-    if ckpt.get("stage_map") and trainer.stage_map is not None:
-        trainer.stage_map.load_state_dict(ckpt["stage_map"])
     trainer.attack_history = list(ckpt.get("attack_history", []))
     trainer.reassignment_history = list(ckpt.get("reassignment_history", []))
     if "training_state" in ckpt:
@@ -95,7 +100,6 @@ def load_checkpoint(trainer, path: str, strict: bool = True, restore_rng: bool =
     engine = getattr(getattr(trainer, "_backend_impl", None), "engine", None)
     if engine is not None and ckpt.get("engine"):
         engine.load_state_dict({k: v.to(engine.device) if v.dim() else v for k, v in ckpt["engine"].items()})
-    impl = getattr(trainer, "_backend_impl", None)
     if hasattr(impl, "load_checkpoint_state") and ckpt.get("strategy"):
         impl.load_checkpoint_state(ckpt["strategy"])
     if restore_rng and ckpt.get("rng"):

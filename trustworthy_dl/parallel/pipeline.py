@@ -136,6 +136,18 @@ class PipelineStrategy:
             self.t.optimizers[sid] = self.t._make_optimizer(params)
             self.t.schedulers[sid] = self.t._make_scheduler(self.t.optimizers[sid])
 
+    def sync_ownership(self) -> None:
+        """The stage map changed under us (a checkpoint written after a reassignment is being resumed): host exactly the
+        stages the map assigns to this rank -- module on the device with an optimizer, everything else released."""
+        for sid in range(self.S):
+            if self._owner(sid) == self.rank:
+                self._adopt(sid)
+            elif sid in self.t.optimizers:
+                self.t.optimizers.pop(sid)
+                self.t.schedulers.pop(sid, None)
+                self.stages[sid].to("cpu")
+        self._known_rx.clear(); self._known_tx.clear()
+
     def _owner(self, sid: int, replica: Optional[int] = None) -> int:
         """Rank that runs stage ``sid`` of ``replica`` (default: this rank's replica)."""
         d = self.replica if replica is None else replica

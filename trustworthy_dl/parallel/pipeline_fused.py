@@ -431,6 +431,20 @@ class FusedPipelineStrategy(PipelineStrategy):
                     eng.reducer.set_group(self._dp_ranks(sid))
         return dst
 
+    def sync_ownership(self) -> None:
+        """Resume of a checkpoint written after a reassignment: create the stage engines the loaded map assigns to this
+        rank (their state follows through :meth:`load_checkpoint_state`), drop the others, open the flows of the new map."""
+        for sid in range(self.S):
+            mine = self._owner(sid) == self.rank
+            if mine and sid not in self.engines:
+                self.engines[sid] = self._make_engine(sid, load=False)
+            elif not mine and sid in self.engines:
+                del self.engines[sid]
+        self._ensure_groups()
+        for sid, eng in self.engines.items():
+            if eng.world > 1:
+                eng.reducer.set_group(self._dp_ranks(sid))
+
     def _migrate(self, sid: int, src: int, dst: int) -> None:
         """Move stage ``sid`` from rank ``src`` to ``dst``: parameters + Adam moments + optimizer clock + exchange epochs
         through the migration arena with the integrity-checked pull (K9).  Every rank takes part in the two barriers."""
