@@ -330,3 +330,73 @@ def test_multi_process_resume_after_reassignment(tmp_path):
     assert b[0]["step"] == 18
     assert b[0]["tail"] == pytest.approx(a[0]["tail"], rel=1e-5)
     assert b[1]["tail"] == pytest.approx(b[0]["tail"])
+
+
+def _resume_any_worker(rank, world, ckpt_dir, phase, parallelism):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5, start_step=7))
+    att.activate_attacks()
+    if parallelism == "tensor":
+        cfg = TrainingConfig(model_name="gpt2-tiny", dataset_name="tiny-tokens", batch_size=4, num_nodes=world, learning_rate=1e-2,
+                             checkpoint_interval=0, device="cpu", parallelism="tensor", optimizer="adamw", seq_len=32,
+                             model_kwargs={"n_positions": 32}, checkpoint_dir=ckpt_dir)
+        batches = list(get_dataloader("tiny-tokens", "train", 4, num_batches=14, seq_len=32))
+    else:
+        cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=12, num_nodes=world, learning_rate=1e-3,
+                             checkpoint_interval=0, device="cpu", parallelism="data", optimizer="adamw", checkpoint_dir=ckpt_dir,
+                             parameter_monitoring_enabled=True)
+        batches = list(get_dataloader("cifar10", "train", 12, num_batches=14))
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    if phase == "a":
+        for b in batches[:10]:
+            t.train_step(b)
+        t.save_checkpoint()
+    else:
+        t.load_checkpoint()
+    tail = [t.train_step(b) for b in batches[10:]]
+    return {"tail": tail, "trust": t.trust_manager.trust_vector().tolist(), "attacks": [(a["node_id"], a["step"]) for a in t.attack_history],
+            "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
+
+
+@pytest.mark.parametrize("parallelism", ["data", "tensor"])
+def test_multi_process_resume_identical_continuation(tmp_path, parallelism):
+    """Checkpoint after the attack was handled (rank 1 flagged at step 7), resume in fresh processes: same losses, same trust
+    vector, same statuses, and the attack is not re-reported."""
+    world = 3 if parallelism == "data" else 2
+    a = run_distributed(_resume_any_worker, world, str(tmp_path), "a", parallelism)
+    b = run_distributed(_resume_any_worker, world, str(tmp_path), "b", parallelism)
+    assert a[0]["attacks"] == b[0]["attacks"] and a[0]["attacks"][0] == (1, 7)
+    assert b[0]["tail"] == pytest.approx(a[0]["tail"], rel=1e-5)
+    assert b[0]["trust"] == pytest.approx(a[0]["trust"]) and a[0]["status"] == b[0]["status"]
+
+
+def _train_loop_worker(rank, world, ckpt_dir, parallelism):
+    import os
+    from trustworthy_dl import DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world, learning_rate=1e-3,
+                         num_epochs=2, checkpoint_interval=3, device="cpu", parallelism=parallelism, micro_batches=2,
+                         optimizer="sgd", checkpoint_dir=ckpt_dir, lr_schedule="cosine")
+    t = DistributedTrainer(cfg)
+    t._rank, t._world = rank, world
+    t.train(get_dataloader("cifar10", "train", 8, num_batches=4), get_dataloader("cifar10", "validation", 8, num_batches=2))
+    stats = t.get_training_stats()
+    return {"state": stats["training_state"], "step": stats["global_step"], "files": sorted(os.listdir(ckpt_dir)),
+            "lr": [g["lr"] for o in t.optimizers.values() for g in o.param_groups], "loss": stats["metrics"]["final_loss"]}
+
+
+@pytest.mark.parametrize("parallelism", ["pipeline", "data"])
+def test_full_train_loop_multi_process(tmp_path, parallelism):
+    """``DistributedTrainer.train`` (epochs, validation, per-rank checkpoints every ``checkpoint_interval`` steps, scheduler
+    steps) under two processes."""
+    res = run_distributed(_train_loop_worker, 2, str(tmp_path), parallelism)
+    for r in res:
+        assert r["state"] == "completed" and r["step"] == 8
+        assert {"checkpoint_step_3.rank0.pt", "checkpoint_step_3.rank1.pt", "checkpoint_step_6.rank0.pt",
+                "checkpoint_step_6.rank1.pt"} <= set(r["files"])
+        assert all(lr < 1e-3 for lr in r["lr"])                          # the cosine schedule stepped once per epoch
+    assert res[0]["loss"] == pytest.approx(res[1]["loss"])
