@@ -400,3 +400,29 @@ def test_full_train_loop_multi_process(tmp_path, parallelism):
                 "checkpoint_step_6.rank1.pt"} <= set(r["files"])
         assert all(lr < 1e-3 for lr in r["lr"])                          # the cosine schedule stepped once per epoch
     assert res[0]["loss"] == pytest.approx(res[1]["loss"])
+
+
+def _two_bad_worker(rank, world):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1, 2], intensity=0.5, start_step=8))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=2, optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=12)]
+    return {"losses": losses, "owner": list(t.stage_map.owner), "attacks": sorted((a["node_id"], a["step"]) for a in t.attack_history),
+            "moves": [(r["from_node"], r["to_node"], r["stages"]) for r in t.reassignment_history], "opt": sorted(t.optimizers)}
+
+
+def test_two_stages_compromised_in_the_same_step():
+    """Ranks 1 and 2 of a three-stage pipeline poison their gradients in the same step: both are flagged, both stages move to
+    the remaining trusted rank (one after the other, every rank taking the same decisions), training continues there."""
+    res = run_distributed(_two_bad_worker, 3)
+    for r in res:
+        assert r["attacks"] == [(1, 8), (2, 8)] and r["owner"] == [0, 0, 0]
+        assert [m[:2] for m in r["moves"]] == [(1, 0), (2, 0)]
+        assert r["losses"] == pytest.approx(res[0]["losses"]) and all(torch.isfinite(torch.tensor(r["losses"])))
+    assert res[0]["opt"] == [0, 1, 2] and res[1]["opt"] == res[2]["opt"] == []

@@ -175,6 +175,7 @@ class DistributedTrainer:
         self.model: Optional[nn.Module] = model
         self.attack_history: List[Dict] = []
         self.reassignment_history: List[Dict] = []
+        self._pending_baseline_resets: set = set()
         self._rank, self._world = 0, 1
         self._backend_impl = None                               # multi-process strategy object
         self._last_step_info: Dict[str, Any] = {}
@@ -320,6 +321,7 @@ class DistributedTrainer:
             gradients[node] = grads + gradients[node]
         self._last_step_info["invalid_nodes"] = set()
         self._last_step_info["invalid_stages"] = set()
+        bad: List[int] = []
         for node, grads in gradients.items():
             if self.attacker is not None:
                 self.attacker.poison_gradients(node, grads, self.global_step)
@@ -328,7 +330,12 @@ class DistributedTrainer:
                     logger.warning("Invalid gradients detected from node %d", node)
                     self._last_step_info["invalid_nodes"].add(node)
                     self._last_step_info["invalid_stages"].update(self.stage_map.stages_of(node))
-                    self.handle_gradient_attack(node, grads)
+                    bad.append(node)
+        # every node is judged before anything moves: all offenders are demoted first, then their stages are reassigned
+        for node in bad:
+            self.handle_gradient_attack(node, gradients[node], reassign=False)
+        for node in bad:
+            self.reassign_node_tasks(node)
         return gradients
 
     # ------------------------------------------------------------------ trust
@@ -389,8 +396,9 @@ class DistributedTrainer:
         return float(np.mean(np.minimum(1.0, norms[ok] / exp[ok])))
 
     # ---------------------------------------------------------- attack handling
-    def handle_detected_attack(self, node_id: int, output: Optional[torch.Tensor], result=None) -> None:
-        """Reference :273-299."""
+    def handle_detected_attack(self, node_id: int, output: Optional[torch.Tensor], result=None, reassign: bool = True) -> None:
+        """Reference :273-299.  ``reassign=False``: record + demote only; the caller reassigns after it has judged every
+        node of the step (so that stages are not handed to a node that is about to be flagged itself)."""
         logger.error("Attack detected on node %d", node_id)
         st = self._last_step_info.get("out_stats", {}).get(node_id, (None, None))
         hist = self.attack_detector.output_history.get(node_id)
@@ -406,11 +414,12 @@ class DistributedTrainer:
         self.attack_history.append(info)
         self.metrics_collector.record_event("attack", node_id=node_id, type="output_anomaly", step=self.global_step)
         self.trust_manager.mark_compromised(node_id, "output_anomaly")
-        self.reassign_node_tasks(node_id)
+        if reassign:
+            self.reassign_node_tasks(node_id)
         self.training_state = TrainingState.UNDER_ATTACK
 
-    def handle_gradient_attack(self, node_id: int, gradients: List[torch.Tensor]) -> None:
-        """Reference :301-322 (also flips the training state, which the reference forgets)."""
+    def handle_gradient_attack(self, node_id: int, gradients: List[torch.Tensor], reassign: bool = True) -> None:
+        """Reference :301-322 (also flips the training state, which the reference forgets).  ``reassign``: as above."""
         logger.error("Gradient attack detected on node %d", node_id)
         self.attack_history.append({
             "node_id": node_id, "timestamp": time.time(), "step": self.global_step,
@@ -419,7 +428,8 @@ class DistributedTrainer:
                                "num_gradients": len(gradients)}})
         self.metrics_collector.record_event("attack", node_id=node_id, type="gradient_poisoning", step=self.global_step)
         self.trust_manager.mark_compromised(node_id, "gradient_poisoning")
-        self.reassign_node_tasks(node_id)
+        if reassign:
+            self.reassign_node_tasks(node_id)
         self.training_state = TrainingState.UNDER_ATTACK
 
     def reassign_node_tasks(self, compromised_node_id: int) -> Optional[int]:
@@ -449,6 +459,20 @@ class DistributedTrainer:
                                             step=self.global_step)
         return best
 
+    def defer_baseline_reset(self, node_id: int) -> None:
+        """The detector / monitor / verifier baselines of a node that adopts new stages no longer describe what it computes
+        -- but they still have to judge what that node did in THIS step (two nodes can misbehave in the same step, and the
+        second must not be acquitted because the first one's stages just landed on it).  So the reset waits for the next
+        step."""
+        self._pending_baseline_resets.add(int(node_id))
+
+    def _apply_pending_resets(self) -> None:
+        for node in sorted(self._pending_baseline_resets):
+            self.attack_detector.reset_node_history(node)
+            self.node_monitor.reset_node(node)
+            self.gradient_verifier.reset_node(node)
+        self._pending_baseline_resets.clear()
+
     def estimate_migration_time(self, source_node: int, target_node: int) -> float:
         numel = sum(p.numel() for s in self.stage_map.stages_of(source_node)
                     for p in self.model_partitions[s].parameters())
@@ -462,10 +486,7 @@ class DistributedTrainer:
             self.node_configs[target_node].model_partition = names
         if source_node in self.node_configs:
             self.node_configs[source_node].model_partition = ""
-        # detector/monitor baselines of the target no longer describe what it computes
-        self.attack_detector.reset_node_history(target_node)
-        self.node_monitor.reset_node(target_node)
-        self.gradient_verifier.reset_node(target_node)
+        self.defer_baseline_reset(target_node)
         logger.info("Task reassignment completed: %d -> %d (stages %s)", source_node, target_node, moved)
         return moved
 
@@ -510,6 +531,7 @@ class DistributedTrainer:
         self.setup()
         self.global_step += 1
         self._last_step_info = {}
+        self._apply_pending_resets()
         self._heartbeat()
         if self._backend_impl is not None:
             loss_val = self._backend_impl.train_step(batch)

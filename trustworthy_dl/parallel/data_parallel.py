@@ -159,20 +159,25 @@ class DataParallelStrategy:
                                       dtype=torch.float64)])
         table = comm.all_gather_vector(vec).numpy()
         t._last_step_info = {"out_stats": {}, "invalid_nodes": set(), "grad_norms": {}}
+        offenders: List[int] = []                        # judged first, demoted together, data shards reassigned afterwards
         for node in range(self.world):
             if table[node, 12] > 0:
                 t._last_step_info["out_stats"][node] = (float(table[node, 0]), float(table[node, 1]))
                 if c.attack_detection_enabled:
                     res = t.attack_detector.observe_stats(table[node, :12], node, step)
                     if res.is_attack:
-                        t.handle_detected_attack(node, None, result=res)
+                        t.handle_detected_attack(node, None, result=res, reassign=False)
+                        offenders.append(node)
         if c.gradient_verification_enabled:
             ok = t.gradient_verifier.verify_rank_stats(stats[:, 0], stats[:, 1], float(stats[0, 2]), step)
             for node in np.nonzero(~ok)[0]:
                 node = int(node)
                 if t.trust_manager.get_node_status(node).value != "compromised":
                     t._last_step_info["invalid_nodes"].add(node)
-                    t.handle_gradient_attack(node, [])
+                    t.handle_gradient_attack(node, [], reassign=False)
+                    offenders.append(node)
+        for node in offenders:
+            t.reassign_node_tasks(node)
         flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
         cos = stats[:, 3]
         for node in range(self.world):

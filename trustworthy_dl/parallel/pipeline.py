@@ -312,18 +312,25 @@ class PipelineStrategy:
                 out_stats[self._owner(s, int(src) // self.pp)] = ss[src, s]   # a node's last stage wins
         t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
                              "invalid_nodes": set(), "grad_norms": {}}
+        # every node is judged before anything moves: offenders are recorded and demoted first, then their stages are
+        # reassigned (never onto a node that was flagged in the same step)
+        offenders: List[int] = []
         if c.attack_detection_enabled:
             for node, v in out_stats.items():
                 res = t.attack_detector.observe_stats(v, node, step)
                 if res.is_attack:
-                    t.handle_detected_attack(node, None, result=res)
+                    t.handle_detected_attack(node, None, result=res, reassign=False)
+                    offenders.append(node)
         if c.gradient_verification_enabled:
             for node in range(self.world):
-                if node in {a["node_id"] for a in t.attack_history if a["step"] == step}:
+                if node in offenders:
                     continue
                 if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
                     t._last_step_info["invalid_nodes"].add(node)
-                    t.handle_gradient_attack(node, [])
+                    t.handle_gradient_attack(node, [], reassign=False)
+                    offenders.append(node)
+        for node in offenders:
+            t.reassign_node_tasks(node)
         flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
         for node in range(self.world):
             st = t._last_step_info["out_stats"].get(node)
@@ -392,8 +399,7 @@ class PipelineStrategy:
             "from_node": src, "to_node": dst, "timestamp": time.time(), "step": t.global_step, "stages": moved,
             "migration_time": estimate_migration_time(numel, 4, t.config.migration_model),
             "measured_time": time.perf_counter() - t0})
-        for obj in (t.attack_detector, t.node_monitor, t.gradient_verifier):
-            (obj.reset_node_history if hasattr(obj, "reset_node_history") else obj.reset_node)(dst)
+        t.defer_baseline_reset(dst)              # dst's baselines still judge what dst did in this step; reset before the next one
         if dst in t.node_configs:
             t.node_configs[dst].model_partition = "+".join(f"partition_{s2}" for s2 in self._my_stages(dst))
         return dst

@@ -383,18 +383,25 @@ class FusedPipelineStrategy(PipelineStrategy):
                 out_stats[self._owner(s, int(src) // self.pp)] = ss[src, s]
         t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
                              "invalid_nodes": set(), "grad_norms": {}}
+        # every node is judged before anything moves: offenders are recorded and demoted first, then their stages are
+        # reassigned (never onto a node that was flagged in the same step)
+        offenders: List[int] = []
         if c.attack_detection_enabled:
             for node, v in out_stats.items():
                 res = t.attack_detector.observe_stats(v, node, step)
                 if res.is_attack:
-                    t.handle_detected_attack(node, None, result=res)
+                    t.handle_detected_attack(node, None, result=res, reassign=False)
+                    offenders.append(node)
         if c.gradient_verification_enabled:
             for node in range(self.world):
-                if node in {a["node_id"] for a in t.attack_history if a["step"] == step}:
+                if node in offenders:
                     continue
                 if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
                     t._last_step_info["invalid_nodes"].add(node)
-                    t.handle_gradient_attack(node, [])
+                    t.handle_gradient_attack(node, [], reassign=False)
+                    offenders.append(node)
+        for node in offenders:
+            t.reassign_node_tasks(node)
         flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
         for node in range(self.world):
             st = t._last_step_info["out_stats"].get(node)
