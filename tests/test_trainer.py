@@ -116,3 +116,21 @@ def test_train_readme_form_and_validation(tmp_path):
     out = t.train(dataset="tiny-tokens", epochs=1, trust_manager=tm)
     assert t.trust_manager is tm and out["training_state"] == "completed" and out["global_step"] == 3
     assert "val_loss" in out["history"][0] and out["metrics"]["num_batches"] == 3
+
+
+def test_two_nodes_poison_in_the_same_step_single_process():
+    """The reference runner's own scenario (targets [1, 3], experiment_runner.py:93): both are flagged in the step they
+    inject, each stage goes to a node that was NOT flagged (load-aware: different targets), no false positive."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1, 3], intensity=0.5, start_step=8))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=4, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=12)]
+    assert sorted((a["node_id"], a["step"]) for a in t.attack_history) == [(1, 8), (3, 8)]
+    assert set(t.stage_map.owner) == {0, 2} and all(r["to_node"] in (0, 2) for r in t.reassignment_history)
+    s = t.metrics_collector.get_summary()
+    assert s["detection_rate"] == 1.0 and s["false_positive_rate"] == 0.0
+    assert all(l == l for l in losses)
