@@ -426,3 +426,35 @@ def test_two_stages_compromised_in_the_same_step():
         assert [m[:2] for m in r["moves"]] == [(1, 0), (2, 0)]
         assert r["losses"] == pytest.approx(res[0]["losses"]) and all(torch.isfinite(torch.tensor(r["losses"])))
     assert res[0]["opt"] == [0, 1, 2] and res[1]["opt"] == res[2]["opt"] == []
+
+
+def _output_poison_worker(rank, world, target):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["output_poisoning"], target_nodes=[target], intensity=0.5, start_step=14))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=2, optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=17)]
+    s = t.metrics_collector.get_summary()
+    return {"owner": list(t.stage_map.owner), "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history],
+            "losses": losses, "det": s.get("detection_rate"), "fp": s.get("false_positive_rate"),
+            "status": [t.trust_manager.get_node_status(n).value for n in range(world)]}
+
+
+@pytest.mark.parametrize("target", [0, 2])
+def test_poisoned_stage_output_taints_the_step_not_the_other_nodes(target):
+    """A stage emits a corrupted activation.  Everything computed from it in that step -- later stage outputs, the loss
+    (it jumps), every gradient (they explode) -- is tainted: only the stage that produced it is flagged, the honest stages
+    around it are neither blamed for the exploding gradients nor polluted in their baselines, the step's update is dropped,
+    and every process scores the same detection rate from the replicated ground truth."""
+    res = run_distributed(_output_poison_worker, 3, target)
+    for r in res:
+        assert r["attacks"] == [(target, 14, "output_anomaly")]
+        assert target not in r["owner"] and r["status"][target] == "compromised"
+        assert [st for n, st in enumerate(r["status"]) if n != target] == ["trusted", "trusted"]
+        assert r["det"] == 1.0 and r["fp"] == 0.0
+        assert r["losses"] == pytest.approx(res[0]["losses"])

@@ -134,3 +134,24 @@ def test_two_nodes_poison_in_the_same_step_single_process():
     s = t.metrics_collector.get_summary()
     assert s["detection_rate"] == 1.0 and s["false_positive_rate"] == 0.0
     assert all(l == l for l in losses)
+
+
+def test_poisoned_last_stage_output_does_not_blame_upstream_nodes():
+    """Single process, same rule: the last stage corrupts its output, the loss and all gradients of that step explode, and
+    only the last stage's node is flagged (before: every upstream node failed the gradient-norm check in that step)."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["output_poisoning"], target_nodes=[2], intensity=0.5, start_step=14))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=3, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    w_before = None
+    for i, b in enumerate(get_dataloader("cifar10", "train", 8, num_batches=16)):
+        if i == 13:
+            w_before = [p.detach().clone() for p in t.model_partitions[0].parameters()]
+        t.train_step(b)
+        if i == 13:                                                   # the tainted step's update was dropped everywhere
+            assert all(torch.equal(a, b2) for a, b2 in zip(w_before, t.model_partitions[0].parameters()))
+    assert [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history] == [(2, 14, "output_anomaly")]
+    assert 2 not in t.stage_map.owner

@@ -88,6 +88,14 @@ class AdversarialAttacker:
             self.per_node[node_id] += 1
         self.log.append({"type": kind, "step": step, "node_id": node_id, **extra})
 
+    NODE_ATTACKS = ("gradient_poisoning", "model_poisoning", "output_poisoning")
+
+    def injects(self, step: int, node_id: int) -> bool:
+        """Would this configuration inject a node-level fault at ``node_id`` in ``step`` (if the node hosts work)?  Unlike
+        :meth:`was_attacked` this does not read the log, so every process of a multi-process run -- each has its own
+        injector, and only the target's own process logs the injection -- gives the same answer."""
+        return any(self._armed(k, step, node_id) for k in self.NODE_ATTACKS)
+
     def was_attacked(self, step: int, node_id: Optional[int] = None) -> bool:
         return any(e["step"] == step and (node_id is None or e["node_id"] == node_id) for e in self.log)
 

@@ -176,6 +176,7 @@ class DistributedTrainer:
         self.attack_history: List[Dict] = []
         self.reassignment_history: List[Dict] = []
         self._pending_baseline_resets: set = set()
+        self._hosts_at_step_start: Optional[set] = None
         self._rank, self._world = 0, 1
         self._backend_impl = None                               # multi-process strategy object
         self._last_step_info: Dict[str, Any] = {}
@@ -284,7 +285,9 @@ class DistributedTrainer:
                 if self.attacker is not None:
                     x = self.attacker.poison_output(node, x, self.global_step)
                 node_outputs[node] = x.detach()
-                if self.config.attack_detection_enabled:
+                # Once a stage's output has been flagged, everything computed from it in this step is tainted: later stage
+                # outputs are not judged (and do not enter any baseline), see ``_step_tainted``.
+                if self.config.attack_detection_enabled and not self._step_tainted():
                     if self.config.deferred_detection and x.is_cuda:
                         from ..ops.stats import tensor_statistics_device
                         pending.append((node, tensor_statistics_device(x)))
@@ -292,15 +295,26 @@ class DistributedTrainer:
                         res = self.attack_detector.analyze_output(x, node, self.global_step)
                         self._note_output_stats(node, self.attack_detector.output_history[node].view()[-1])
                         if res.is_attack:
+                            self._last_step_info["tainted_by"] = node
                             self.handle_detected_attack(node, x, result=res)
         if pending:                                            # one D2H copy for the whole step
             block = torch.stack([s for _, s in pending]).cpu().numpy()
             for (node, _), vec in zip(pending, block):
+                if self._step_tainted():
+                    break
                 res = self.attack_detector.observe_stats(vec, node, self.global_step)
                 self._note_output_stats(node, vec)
                 if res.is_attack:
+                    self._last_step_info["tainted_by"] = node
                     self.handle_detected_attack(node, node_outputs[node], result=res)
         return x, node_outputs
+
+    def _step_tainted(self) -> bool:
+        """True once a stage output of this step has been flagged.  What follows a poisoned activation -- the outputs of
+        later stages, the loss, every gradient -- says nothing about the nodes that computed it: it is neither judged nor
+        allowed into a baseline, and the step's update is dropped (an honest stage downstream of a poisoned one must not be
+        blamed for the gradient explosion the poison causes)."""
+        return self._last_step_info.get("tainted_by") is not None
 
     def _note_output_stats(self, node: int, vec: np.ndarray) -> None:
         self._last_step_info.setdefault("out_stats", {})[node] = (float(vec[0]), float(vec[1]))
@@ -325,7 +339,7 @@ class DistributedTrainer:
         for node, grads in gradients.items():
             if self.attacker is not None:
                 self.attacker.poison_gradients(node, grads, self.global_step)
-            if self.config.gradient_verification_enabled:
+            if self.config.gradient_verification_enabled and not self._step_tainted():
                 if not self.gradient_verifier.verify_gradients(grads, node, self.global_step):
                     logger.warning("Invalid gradients detected from node %d", node)
                     self._last_step_info["invalid_nodes"].add(node)
@@ -343,7 +357,10 @@ class DistributedTrainer:
                             gradients: Dict[int, List[torch.Tensor]]) -> None:
         """Reference :209-226 — every node, every step."""
         flagged = {a["node_id"] for a in self.attack_history if a["step"] == self.global_step}
+        tainted = self._step_tainted()
         for node in range(self.config.num_nodes):
+            if tainted and node not in flagged:
+                continue                                         # nothing this node produced in a tainted step is evidence
             dev = self.calculate_output_deviation(node_outputs.get(node), node)
             gc = self.calculate_gradient_consistency(gradients.get(node), node)
             self.trust_manager.update_trust_score(node, dev, gc)
@@ -501,8 +518,9 @@ class DistributedTrainer:
     def optimizer_step(self, gradients: Dict[int, List[torch.Tensor]]) -> None:
         """Per-stage optimizer step (reference :441-446); poisoned gradients are dropped."""
         invalid = self._last_step_info.get("invalid_stages", set())
+        tainted = self._step_tainted()
         for sid, opt in self.optimizers.items():
-            if sid in invalid:
+            if sid in invalid or tainted:
                 opt.zero_grad(set_to_none=True)
                 continue
             if self.config.clip_norm > 0:
@@ -532,6 +550,7 @@ class DistributedTrainer:
         self.global_step += 1
         self._last_step_info = {}
         self._apply_pending_resets()
+        self._hosts_at_step_start = set(self.stage_map.owner) if self.stage_map is not None else None
         self._heartbeat()
         if self._backend_impl is not None:
             loss_val = self._backend_impl.train_step(batch)
@@ -572,8 +591,11 @@ class DistributedTrainer:
             return
         step = self.global_step
         flagged = {a["node_id"] for a in self.attack_history if a.get("step") == step}
+        hosts = self._hosts_at_step_start
         for node in range(self.config.num_nodes):
-            truth = self.attacker.was_attacked(step, node)
+            # ground truth that every process of a multi-process run agrees on: the injector's configuration and the stage
+            # map the step started with (a node that hosts nothing cannot inject anything)
+            truth = self.attacker.injects(step, node) and (hosts is None or node in hosts)
             hit = node in flagged
             if not hit and self.trust_manager.get_node_status(node).value == "compromised":
                 continue                                     # excluded in an earlier step: no longer a sample either way

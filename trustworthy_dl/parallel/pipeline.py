@@ -306,40 +306,7 @@ class PipelineStrategy:
         hv = table[:, S * NUM_STATS:S * NUM_STATS + S]
         norms = table[:, -3]
         loss = float(table[table[:, -1] > 0, -2].sum()) / self.dp  # mean over replicas
-        out_stats: Dict[int, np.ndarray] = {}
-        for s in range(S):
-            for src in np.nonzero(hv[:, s] > 0)[0]:                 # reporter verified stage s of ITS replica
-                out_stats[self._owner(s, int(src) // self.pp)] = ss[src, s]   # a node's last stage wins
-        t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
-                             "invalid_nodes": set(), "grad_norms": {}}
-        # every node is judged before anything moves: offenders are recorded and demoted first, then their stages are
-        # reassigned (never onto a node that was flagged in the same step)
-        offenders: List[int] = []
-        if c.attack_detection_enabled:
-            for node, v in out_stats.items():
-                res = t.attack_detector.observe_stats(v, node, step)
-                if res.is_attack:
-                    t.handle_detected_attack(node, None, result=res, reassign=False)
-                    offenders.append(node)
-        if c.gradient_verification_enabled:
-            for node in range(self.world):
-                if node in offenders:
-                    continue
-                if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
-                    t._last_step_info["invalid_nodes"].add(node)
-                    t.handle_gradient_attack(node, [], reassign=False)
-                    offenders.append(node)
-        for node in offenders:
-            t.reassign_node_tasks(node)
-        flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
-        for node in range(self.world):
-            st = t._last_step_info["out_stats"].get(node)
-            dev = 1.0 if st is None else self._deviation(node, st)
-            gc = 0.0 if not t.stage_map.stages_of(node) and node not in flagged else \
-                (1.0 if node not in t._last_step_info["invalid_nodes"] else 0.0)
-            t.trust_manager.update_trust_score(node, dev, gc)
-            if st is not None and node not in flagged:
-                t.node_monitor.record_output(node, *st)
+        tainted = self._judge_step(ss, hv, norms, step)
 
         # ---- optimizer --------------------------------------------------------------
         for sid in list(t.optimizers):
@@ -349,7 +316,9 @@ class PipelineStrategy:
             # a rank that failed verification drops its own step ONLY when it is the sole holder of the stage: with
             # dp > 1 every replica already holds the same trust-weighted aggregate (the coefficients excluded the bad
             # rank), and skipping the step on one replica would make the stage's copies diverge for good
-            if self.dp == 1 and self.rank in t._last_step_info["invalid_nodes"]:
+            # a step in which a stage OUTPUT was flagged is dropped everywhere: every gradient of it descends from a
+            # poisoned activation
+            if tainted or (self.dp == 1 and self.rank in t._last_step_info["invalid_nodes"]):
                 opt.zero_grad(set_to_none=True)
                 continue
             if c.clip_norm > 0:
@@ -363,6 +332,64 @@ class PipelineStrategy:
             "trust_scores": {i: t.trust_manager.get_trust_score(i) for i in range(self.world)},
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
         return loss
+
+    def _judge_step(self, ss: np.ndarray, hv: np.ndarray, norms: np.ndarray, step: int) -> bool:
+        """The replicated decisions of one step, from the gathered table (identical on every rank): ``ss[src, s]`` = the 12
+        statistics rank ``src`` measured on the output of stage ``s`` of its replica, ``hv`` says which entries exist,
+        ``norms[node]`` = that rank's gradient norm.  Returns True when a stage output was flagged (the step is tainted).
+
+        * Every node is judged before anything moves: offenders are recorded and demoted first, then their stages are
+          reassigned, never onto a node flagged in the same step.
+        * Stage outputs are judged in stage order, per replica, and only up to the first one flagged: everything computed
+          from a poisoned activation -- the outputs of later stages, the loss, every gradient of that replica -- is
+          tainted, so it is neither judged nor allowed into a baseline (an honest stage downstream of a poisoned one must
+          not be blamed for the gradient explosion the poison causes)."""
+        t, c, S = self.t, self.t.config, self.S
+        out_stats: Dict[int, np.ndarray] = {}
+        last_stage: Dict[int, int] = {}
+        for s in range(S):
+            for src in np.nonzero(hv[:, s] > 0)[0]:                 # reporter verified stage s of ITS replica
+                node = self._owner(s, int(src) // self.pp)
+                out_stats[node] = ss[src, s]                        # a node's last stage wins
+                last_stage[node] = s
+        t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
+                             "invalid_nodes": set(), "grad_norms": {}}
+        offenders: List[int] = []
+        tainted_replicas: set = set()
+        unjudged: set = set()
+        if c.attack_detection_enabled:
+            for node in sorted(out_stats, key=lambda n: (n // self.pp, last_stage[n])):
+                if node // self.pp in tainted_replicas:
+                    unjudged.add(node)
+                    continue
+                res = t.attack_detector.observe_stats(out_stats[node], node, step)
+                if res.is_attack:
+                    t.handle_detected_attack(node, None, result=res, reassign=False)
+                    offenders.append(node)
+                    tainted_replicas.add(node // self.pp)
+        if c.gradient_verification_enabled:
+            for node in range(self.world):
+                if node in offenders or node // self.pp in tainted_replicas:
+                    continue
+                if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
+                    t._last_step_info["invalid_nodes"].add(node)
+                    t.handle_gradient_attack(node, [], reassign=False)
+                    offenders.append(node)
+        for node in offenders:
+            t.reassign_node_tasks(node)
+        flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
+        for node in range(self.world):
+            if node // self.pp in tainted_replicas and node not in flagged:
+                continue                                            # nothing this node produced in a tainted step is evidence
+            st = t._last_step_info["out_stats"].get(node)
+            dev = 1.0 if st is None else self._deviation(node, st)
+            gc = 0.0 if not t.stage_map.stages_of(node) and node not in flagged else \
+                (1.0 if node not in t._last_step_info["invalid_nodes"] else 0.0)
+            t.trust_manager.update_trust_score(node, dev, gc)
+            if st is not None and node not in flagged and node not in unjudged:
+                t.node_monitor.record_output(node, *st)
+        t._last_step_info["tainted_by"] = offenders[0] if tainted_replicas else None
+        return bool(tainted_replicas)
 
     def _deviation(self, node: int, st) -> float:
         em, es = self.t.node_monitor.get_expected_mean(node), self.t.node_monitor.get_expected_std(node)

@@ -377,45 +377,13 @@ class FusedPipelineStrategy(PipelineStrategy):
         hv = table[:, S * NUM_STATS:S * NUM_STATS + S]
         norms = table[:, -3]
         loss = float(table[table[:, -1] > 0, -2].sum()) / self.dp
-        out_stats: Dict[int, np.ndarray] = {}
-        for s in range(S):
-            for src in np.nonzero(hv[:, s] > 0)[0]:
-                out_stats[self._owner(s, int(src) // self.pp)] = ss[src, s]
-        t._last_step_info = {"out_stats": {n: (float(v[0]), float(v[1])) for n, v in out_stats.items()},
-                             "invalid_nodes": set(), "grad_norms": {}}
-        # every node is judged before anything moves: offenders are recorded and demoted first, then their stages are
-        # reassigned (never onto a node that was flagged in the same step)
-        offenders: List[int] = []
-        if c.attack_detection_enabled:
-            for node, v in out_stats.items():
-                res = t.attack_detector.observe_stats(v, node, step)
-                if res.is_attack:
-                    t.handle_detected_attack(node, None, result=res, reassign=False)
-                    offenders.append(node)
-        if c.gradient_verification_enabled:
-            for node in range(self.world):
-                if node in offenders:
-                    continue
-                if t.stage_map.stages_of(node) and not t.gradient_verifier.verify_norm(float(norms[node]), node, step):
-                    t._last_step_info["invalid_nodes"].add(node)
-                    t.handle_gradient_attack(node, [], reassign=False)
-                    offenders.append(node)
-        for node in offenders:
-            t.reassign_node_tasks(node)
+        tainted = self._judge_step(ss, hv, norms, step)
         flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
-        for node in range(self.world):
-            st = t._last_step_info["out_stats"].get(node)
-            dev = 1.0 if st is None else self._deviation(node, st)
-            gc = 0.0 if not t.stage_map.stages_of(node) and node not in flagged else \
-                (1.0 if node not in t._last_step_info["invalid_nodes"] else 0.0)
-            t.trust_manager.update_trust_score(node, dev, gc)
-            if st is not None and node not in flagged:
-                t.node_monitor.record_output(node, *st)
         if self.dp == 1:
             # single holder of every stage: the (replicated) verdict gates the optimizer step of the poisoned rank
             # (a stage adopted from a flagged rank during this step arrives without gradients: its update is dropped)
             for sid in mine:
-                if sid not in self.engines or self.rank in t._last_step_info["invalid_nodes"] or self.rank in flagged:
+                if tainted or sid not in self.engines or self.rank in t._last_step_info["invalid_nodes"] or self.rank in flagged:
                     continue
                 self.engines[sid].reduce_and_update()
         self._comm_s += comm_s
