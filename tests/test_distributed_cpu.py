@@ -458,3 +458,42 @@ def test_poisoned_stage_output_taints_the_step_not_the_other_nodes(target):
         assert [st for n, st in enumerate(r["status"]) if n != target] == ["trusted", "trusted"]
         assert r["det"] == 1.0 and r["fp"] == 0.0
         assert r["losses"] == pytest.approx(res[0]["losses"])
+
+
+def _probation_worker(rank, world, end_step):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["gradient_poisoning"], target_nodes=[1], intensity=0.5, start_step=8,
+                                           end_step=end_step))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=12, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="data", optimizer="sgd")
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    coeff_on_probation = []
+    for b in get_dataloader("cifar10", "train", 12, num_batches=34):
+        t.train_step(b)
+        if not t.stage_map.stages_of(1):
+            coeff_on_probation.append(float(t._backend_impl.reducer.last_coeff[1]))
+    w = torch.cat([p.detach().reshape(-1) for p in t.model_partitions[0].parameters()])
+    return {"owner": list(t.stage_map.owner), "trust": t.trust_manager.get_trust_score(1), "status": t.trust_manager.get_node_status(1).value,
+            "moves": [(r["from_node"], r["to_node"], r.get("kind")) for r in t.reassignment_history], "wsum": float(w.double().sum()),
+            "probation_coeff": coeff_on_probation, "attacks": [(a["node_id"], a["step"]) for a in t.attack_history]}
+
+
+def test_probation_a_demoted_rank_earns_its_shard_back_only_when_it_behaves():
+    """README 'recovery patterns for nodes after attack mitigation': the demoted rank keeps computing its home shard with
+    coefficient 0.  Attack over after three steps -> its measured behaviour lifts its trust back over the threshold and the
+    shard returns; attack still running -> it stays excluded (and is re-flagged whenever its status drifts up)."""
+    healed = run_distributed(_probation_worker, 3, 11, timeout=400)
+    for r in healed:
+        assert r["attacks"] == [(1, 8)] and r["owner"] == [0, 1, 2] and r["status"] == "trusted" and r["trust"] > 0.7
+        assert [m[2] for m in r["moves"]] == ["data_shard", "shard_returned"] and r["moves"][1][1] == 1
+        assert r["probation_coeff"] and max(r["probation_coeff"]) == 0.0       # never influenced the model while on probation
+    assert len({r["wsum"] for r in healed}) == 1
+    stubborn = run_distributed(_probation_worker, 3, None, timeout=400)
+    for r in stubborn:
+        assert 1 not in r["owner"] and r["trust"] < 0.5 and max(r["probation_coeff"]) == 0.0
+        assert len(r["attacks"]) >= 2 and all(n == 1 for n, _ in r["attacks"])
+    assert len({r["wsum"] for r in stubborn}) == 1

@@ -119,6 +119,8 @@ class TrainingConfig:
     log_interval: int = 10
     seed: int = 0
     engine: str = "auto"                       # auto | eager | fused (GPT2Engine on sm_100a)
+    probation: bool = True                     # data parallel: a demoted rank keeps computing its home shard with coefficient 0
+                                               #     (evidence for its trust score); the shard returns once it is trusted again
     zero: int = 0                              # 1 = ZeRO-1 on the fused data-parallel path: sharded optimizer step +
                                                #     integrity-checked parameter all-gather (K9) every step
 

@@ -131,6 +131,13 @@ class DataParallelStrategy:
         if self.flat_params is not None:
             self._check_replicas(step)
         local = self._local_batch(batch)
+        # Probation ("recovery patterns for nodes after attack mitigation", README.md:141): a rank that lost its data shard
+        # keeps computing the shard it started with.  Its gradient enters the reduction with coefficient 0 -- it cannot
+        # influence the model -- but its norm, its cosine to the median and its output statistics are measured like
+        # everybody's, which is the only evidence a demoted rank can offer; without it its trust saturates at 0.3 for good.
+        shadow = local is None and c.probation and t.trust_manager.get_node_status(self.rank).value != "offline"
+        if shadow:
+            local = {"input": batch["input"].chunk(self.world)[self.rank], "target": batch["target"].chunk(self.world)[self.rank]}
         self.reducer.buffer.zero_()
         loss_val, n_local = 0.0, 0
         out_stats = None
@@ -142,14 +149,20 @@ class DataParallelStrategy:
             loss = t.calculate_loss(out, local["target"])
             flatten_grads_into(self.params, self.reducer.buffer.dtype, self.device, self.reducer.buffer)
             loss.backward()
-            loss_val, n_local = float(loss.item()), local["input"].shape[0]
+            loss_val, n_local = float(loss.item()), (0 if shadow else local["input"].shape[0])
             if c.attack_detection_enabled:
                 from ..ops.stats import tensor_statistics
                 out_stats = tensor_statistics(out.detach()).cpu()
         if t.attacker is not None:
             t.attacker.poison_gradients(self.rank, [self.reducer.buffer], step)
         ts = time.perf_counter()
-        weights = torch.from_numpy(t.trust_manager.aggregation_weights()).float()
+        w_np = t.trust_manager.aggregation_weights()
+        idle = [n for n in range(self.world) if not t.stage_map.stages_of(n)]
+        if idle and len(idle) < self.world:                  # a rank on probation computes a shard somebody else covers: weight 0
+            w_np = w_np.copy()
+            w_np[idle] = 0.0
+            w_np = w_np / w_np.sum() if w_np.sum() > 0 else np.full(self.world, 1.0 / self.world)
+        weights = torch.from_numpy(w_np).float()
         with nvtx_range("dp.trust_allreduce"):
             stats, coeff = self.reducer.reduce_(weights)
         stats = stats.detach().cpu().double().numpy()
@@ -172,8 +185,8 @@ class DataParallelStrategy:
             ok = t.gradient_verifier.verify_rank_stats(stats[:, 0], stats[:, 1], float(stats[0, 2]), step)
             for node in np.nonzero(~ok)[0]:
                 node = int(node)
+                t._last_step_info["invalid_nodes"].add(node)         # evidence for the trust score whatever the status
                 if t.trust_manager.get_node_status(node).value != "compromised":
-                    t._last_step_info["invalid_nodes"].add(node)
                     t.handle_gradient_attack(node, [], reassign=False)
                     offenders.append(node)
         for node in offenders:
@@ -187,6 +200,8 @@ class DataParallelStrategy:
             t.trust_manager.update_trust_score(node, dev, gc)
             if st is not None and node not in flagged:
                 t.node_monitor.record_output(node, *st)
+        if c.probation:
+            self._return_shards(step)
         self._sec_s += time.perf_counter() - ts
         # ---- optimizer on the aggregated gradient ------------------------------------
         opt = t.optimizers[0]
@@ -279,6 +294,26 @@ class DataParallelStrategy:
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
         self._last_loss = loss
         return loss
+
+    def _return_shards(self, step: int) -> None:
+        """End of probation: a rank whose status is assignable again (TRUSTED / RECOVERING) and whose trust is back above
+        the threshold takes its home shard back from whoever has been covering it (replicated decision, no traffic)."""
+        t = self.t
+        tm = t.trust_manager
+        flagged = {a["node_id"] for a in t.attack_history if a["step"] == step}
+        for node in range(self.world):
+            if t.stage_map.stages_of(node) or node in flagged or not tm.can_assign_task(node) \
+                    or tm.get_trust_score(node) < t.config.trust_threshold:
+                continue
+            cover = t.stage_map.owner[node]                      # shard i is rank i's home shard
+            t.stage_map.owner[node] = node
+            t.reassignment_history.append({"from_node": cover, "to_node": node, "timestamp": time.time(), "step": step,
+                                           "stages": [node], "migration_time": 0.0, "kind": "shard_returned"})
+            t.metrics_collector.record_event("reassignment", from_node=cover, to_node=node, step=step)
+            t.defer_baseline_reset(cover)                        # both see a different batch from the next step on
+            t.defer_baseline_reset(node)
+            logger.info("node %d is trusted again (%.3f): data shard %d returned by node %d", node,
+                        tm.get_trust_score(node), node, cover)
 
     def _check_replicas(self, step: int) -> None:
         """The parameter monitor of the replicated path ("Param Monitor", reference README.md:22; the reference has no
