@@ -155,3 +155,16 @@ def test_poisoned_last_stage_output_does_not_blame_upstream_nodes():
             assert all(torch.equal(a, b2) for a, b2 in zip(w_before, t.model_partitions[0].parameters()))
     assert [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history] == [(2, 14, "output_anomaly")]
     assert 2 not in t.stage_map.owner
+
+
+def test_train_saves_a_final_checkpoint_and_resume_continues_with_the_next_epoch(tmp_path):
+    kw = dict(model_name="resnet32", dataset_name="cifar10", batch_size=4, num_nodes=2, learning_rate=1e-3, device="cpu",
+              optimizer="sgd", checkpoint_interval=100, checkpoint_dir=str(tmp_path), steps_per_epoch=5)
+    t = DistributedTrainer(TrainingConfig(num_epochs=1, **kw))
+    t.train()
+    assert sorted(os.listdir(tmp_path)) == ["checkpoint_step_5.pt"]              # 5 steps < interval: only the final save
+    t2 = DistributedTrainer(TrainingConfig(num_epochs=3, **kw))
+    t2.load_checkpoint()
+    stats = t2.train()
+    assert [h["epoch"] for h in stats["history"]] == [1, 2] and stats["global_step"] == 15
+    assert "checkpoint_step_15.pt" in os.listdir(tmp_path)

@@ -60,7 +60,12 @@ def main(argv=None) -> int:
                                               master_port=int(os.environ.get("MASTER_PORT", "12355")))
     try:
         if args.resume:
-            trainer.load_checkpoint(None if args.resume == "latest" else args.resume)
+            try:
+                trainer.load_checkpoint(None if args.resume == "latest" else args.resume)
+            except FileNotFoundError as e:
+                if args.resume != "latest":
+                    raise
+                logging.getLogger(__name__).warning("--resume: %s; starting from scratch", e)
         stats = trainer.train()
         if int(os.environ.get("RANK", "0")) == 0:
             print(json.dumps({k: v for k, v in stats.items() if k != "history"}, default=str))

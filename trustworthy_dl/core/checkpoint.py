@@ -46,6 +46,7 @@ def save_checkpoint(trainer, directory: Optional[str] = None, rank: Optional[int
         "node_monitor": trainer.node_monitor.state_dict(),
         "stage_map": trainer.stage_map.state_dict() if trainer.stage_map is not None else None,
         "training_state": trainer.training_state.value,
+        "epoch_complete": bool(getattr(trainer, "_epoch_complete", False)),
         "rng": {"torch": torch.get_rng_state(),
                 "cuda": torch.cuda.get_rng_state_all() if torch.cuda.is_available() else None},
         "config": dict(trainer.config.__dict__),

@@ -179,6 +179,9 @@ class DistributedTrainer:
         self.reassignment_history: List[Dict] = []
         self._pending_baseline_resets: set = set()
         self._hosts_at_step_start: Optional[set] = None
+        self._start_epoch = 0
+        self._epoch_complete = False
+        self._last_checkpoint_step = -1
         self._rank, self._world = 0, 1
         self._backend_impl = None                               # multi-process strategy object
         self._last_step_info: Dict[str, Any] = {}
@@ -648,7 +651,8 @@ class DistributedTrainer:
         logger.info("Starting training for %d epochs", num_epochs)
         self.training_state = TrainingState.TRAINING
         history = []
-        for epoch in range(num_epochs):
+        for epoch in range(self._start_epoch, num_epochs):           # a resumed run continues with the first unfinished epoch
+            self._epoch_complete = False
             avg = self.train_epoch(train_dataloader, epoch)
             rec = {"epoch": epoch, "train_loss": avg}
             if val_dataloader is not None:
@@ -661,7 +665,11 @@ class DistributedTrainer:
                     self.trust_manager.initiate_recovery(n)
             for sch in self.schedulers.values():
                 sch.step()
+            self._epoch_complete = True
             history.append(rec)
+        self._start_epoch = 0
+        if self.config.checkpoint_interval and history and self._last_checkpoint_step != self.global_step:
+            self.save_checkpoint()                                   # final state (the reference only saves every N steps, :423-424)
         self.training_state = TrainingState.COMPLETED
         logger.info("Training completed successfully")
         return {"history": history, **self.get_training_stats()}
@@ -690,6 +698,7 @@ class DistributedTrainer:
     # ------------------------------------------------------------- persistence
     def save_checkpoint(self, directory: Optional[str] = None) -> str:
         path = _ckpt.save_checkpoint(self, directory, rank=self._rank if self._world > 1 else None)
+        self._last_checkpoint_step = self.global_step
         logger.info("Checkpoint saved: %s", path)
         return path
 
@@ -699,7 +708,10 @@ class DistributedTrainer:
             path = _ckpt.latest_checkpoint(self.config.checkpoint_dir, self._rank if self._world > 1 else None)
             if path is None:
                 raise FileNotFoundError(f"no checkpoint in {self.config.checkpoint_dir}")
-        return _ckpt.load_checkpoint(self, path)
+        ckpt = _ckpt.load_checkpoint(self, path)
+        self._start_epoch = self.current_epoch + (1 if ckpt.get("epoch_complete") else 0)
+        self._last_checkpoint_step = self.global_step
+        return ckpt
 
     def get_training_stats(self) -> Dict[str, Any]:
         return {"current_epoch": self.current_epoch, "global_step": self.global_step,
