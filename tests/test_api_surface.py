@@ -61,3 +61,16 @@ def test_attacker_log_queries_and_detection_rates_from_ground_truth():
     assert t.attack_detector.detection_stats["true_positives"] == 1
     att.deactivate_attacks()
     assert not att.is_active() and not att._armed("gradient_poisoning", 9, 1)
+
+
+def test_model_follows_the_named_dataset():
+    """``vgg11`` + ``cifar10`` used to die in the classifier (ImageNet-sized flatten on a 32 x 32 input)."""
+    t = DistributedTrainer(TrainingConfig(model_name="vgg11", dataset_name="cifar10", batch_size=4, num_nodes=2, device="cpu",
+                                          checkpoint_interval=0))
+    loss = t.train_step(next(iter(get_dataloader("cifar10", "train", 4, num_batches=1))))
+    assert loss == loss and t.model.classifier[-1].fc.out_features == 10
+    t2 = DistributedTrainer(TrainingConfig(model_name="resnet32", dataset_name="imagenet", num_nodes=2, device="cpu"))
+    assert t2._dataset_model_kwargs() == {"num_classes": 1000}
+    t3 = DistributedTrainer(TrainingConfig(model_name="vgg16", dataset_name="cifar10", num_nodes=2, device="cpu",
+                                           model_kwargs={"num_classes": 7}))
+    assert t3._dataset_model_kwargs() == {"num_classes": 7, "input_size": 32}            # explicit kwargs win

@@ -208,8 +208,22 @@ class DistributedTrainer:
         if self.model is None:
             torch.manual_seed(self.config.seed)
             self.model = ModelFactory().create_model(self.config.model_name, self.config.model_size,
-                                                     **self.config.model_kwargs)
+                                                     **self._dataset_model_kwargs())
         return self.model
+
+    def _dataset_model_kwargs(self) -> Dict[str, Any]:
+        """``model_kwargs`` plus what the named dataset implies and the user left open: the class count of an image set
+        for the image models, and VGG's input size (its classifier width follows from it).  So ``vgg11`` + ``cifar10`` or
+        ``resnet32`` + ``imagenet`` just work."""
+        from ..utils.data_loader import DATASETS
+        kw = dict(self.config.model_kwargs)
+        spec = DATASETS.get(str(self.config.dataset_name).lower())
+        name = str(self.config.model_name).lower()
+        if spec and spec.get("kind") == "image" and name.startswith(("vgg", "resnet")):
+            kw.setdefault("num_classes", int(spec["classes"]))
+            if name.startswith("vgg") and not (name.endswith("-cifar") or self.config.model_size == "cifar"):
+                kw.setdefault("input_size", int(spec["shape"][-1]))
+        return kw
 
     def create_model_partitions(self, model_name: Optional[str] = None) -> Dict[int, nn.Module]:
         """Balanced contiguous stages, one per node (reference :116-146; Q3/Q4 fixed)."""
