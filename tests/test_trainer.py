@@ -168,3 +168,33 @@ def test_train_saves_a_final_checkpoint_and_resume_continues_with_the_next_epoch
     stats = t2.train()
     assert [h["epoch"] for h in stats["history"]] == [1, 2] and stats["global_step"] == 15
     assert "checkpoint_step_15.pt" in os.listdir(tmp_path)
+
+
+def test_model_poisoning_is_rolled_back_to_the_last_verified_parameters():
+    """Single process, parameter monitor on: node 1's stage is overwritten with noise before step 10.  The drift check
+    flags it before the forward, the stage is restored from the monitor's last verified snapshot, then it changes hands;
+    nobody else is blamed and the loss curve shows no excursion."""
+    from trustworthy_dl import AdversarialAttacker, AttackConfig
+    torch.manual_seed(0)
+    att = AdversarialAttacker(AttackConfig(attack_types=["model_poisoning"], target_nodes=[1], intensity=0.5, start_step=10,
+                                           end_step=11))
+    att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=2, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", optimizer="sgd", parameter_monitoring_enabled=True)
+    t = DistributedTrainer(cfg, attacker=att)
+    snap, losses = None, []
+    for i, b in enumerate(get_dataloader("cifar10", "train", 8, num_batches=13)):
+        if i == 9:                                                    # state after step 9 = what step 10 must start from
+            snap = [p.detach().clone() for p in t.model_partitions[1].parameters()]
+            orig_fwd = t.forward_pass
+
+            def checked_forward(x, *a, **k):                          # the forward of step 10 sees the restored weights
+                assert all(torch.equal(p, q) for p, q in zip(snap, t.model_partitions[1].parameters()))
+                return orig_fwd(x, *a, **k)
+            t.forward_pass = checked_forward
+        losses.append(t.train_step(b))
+        if i == 9:
+            t.forward_pass = orig_fwd
+    assert [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history] == [(1, 10, "model_poisoning")]
+    assert t.attack_history[0]["parameter_stats"]["restored_to_last_verified"] and t.stage_map.owner == [0, 0]
+    assert max(losses[9:]) < max(losses[:9]) + 0.3

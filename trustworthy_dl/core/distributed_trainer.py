@@ -580,19 +580,22 @@ class DistributedTrainer:
             for sid, part in self.model_partitions.items():
                 self.attacker.poison_parameters(self.stage_map.owner[sid], list(part.parameters()), self.global_step)
         if self.config.parameter_monitoring_enabled:
+            # (a) before the forward: the parameters must be exactly what the last optimizer step left behind
             for sid, part in self.model_partitions.items():
-                node = self.stage_map.owner[sid]
-                if self.parameter_monitor.detect_parameter_poisoning(sid, part.parameters(), self.global_step):
-                    self.attack_history.append({"node_id": node, "timestamp": time.time(), "step": self.global_step,
-                                                "attack_type": "model_poisoning"})
-                    self.trust_manager.mark_compromised(node, "model_poisoning")
-                    self.reassign_node_tasks(node)
-                    self.training_state = TrainingState.UNDER_ATTACK
+                if not self.parameter_monitor.unchanged(sid, part.parameters()):
+                    self._handle_parameter_attack(sid, "changed_between_steps")
+            self._apply_pending_resets()        # these moves precede the step's forward: the adopting node starts it with fresh baselines
         outputs, node_outputs = self.forward_pass(batch["input"])
         loss = self.calculate_loss(outputs, batch["target"])
         gradients = self.backward_pass(loss)
         self.update_trust_scores(node_outputs, gradients)
         self.optimizer_step(gradients)
+        if self.config.parameter_monitoring_enabled:
+            # (b) after the optimizer: the size of the update against the shard's own history (drift norm); the snapshot
+            #     the next step is compared with is refreshed here
+            for sid, part in self.model_partitions.items():
+                if self.parameter_monitor.detect_parameter_poisoning(sid, part.parameters(), self.global_step):
+                    self._handle_parameter_attack(sid, "drift")
         loss_val = float(loss.item())
         n = batch["input"].shape[0] * (batch["input"].shape[1] if batch["input"].dim() == 2 else 1)
         self.metrics_collector.collect_batch_metrics({
@@ -601,6 +604,22 @@ class DistributedTrainer:
             "step_time": time.perf_counter() - t0, "samples": n})
         self._score_detection()
         return loss_val
+
+    def _handle_parameter_attack(self, sid: int, reason: str) -> None:
+        """MODEL_POISONING verdict of the parameter monitor for stage ``sid``: repair first (the stage goes back to its
+        last verified parameters), then the usual consequences for the node that held it."""
+        node = self.stage_map.owner[sid]
+        part = self.model_partitions[sid]
+        restored = self.parameter_monitor.restore(sid, part.parameters())
+        logger.error("Parameter poisoning detected on node %d (stage %d, %s)", node, sid, reason)
+        self.attack_history.append({"node_id": node, "timestamp": time.time(), "step": self.global_step,
+                                    "attack_type": "model_poisoning",
+                                    "parameter_stats": {"reason": reason, "stage": sid, "restored_to_last_verified": restored}})
+        self.metrics_collector.record_event("attack", node_id=node, type="model_poisoning", step=self.global_step)
+        if self.trust_manager.get_node_status(node) is not NodeStatus.COMPROMISED:
+            self.trust_manager.mark_compromised(node, "model_poisoning")
+        self.reassign_node_tasks(node)
+        self.training_state = TrainingState.UNDER_ATTACK
 
     def _score_detection(self) -> None:
         """With a fault injector attached the ground truth of every step is known: feed the detector's TP / FP counters

@@ -60,13 +60,14 @@ class ParameterMonitor:
 
     def observe(self, shard_id: int, params: Iterable[torch.Tensor], step: int) -> Dict:
         """Track drift of one shard; returns ``{drift, expected, poisoned}``."""
-        from ..ops.integrity import drift_sq_and_update
         flat = self._flat(params)
         prev = self._prev.get(shard_id)
         if prev is None or prev.numel() != flat.numel():
             self._prev[shard_id] = flat.clone()
             return {"drift": 0.0, "expected": None, "poisoned": False}
-        drift = float(drift_sq_and_update(flat, prev)) ** 0.5          # prev <- flat in the same pass
+        # read-only pass first: the snapshot is the last VERIFIED state and must survive a bad verdict (see restore()); the
+        # fused drift+refresh kernel (ops.integrity.drift_sq_and_update, K9's building block) would overwrite it
+        drift = float(torch.linalg.vector_norm(flat.float() - prev.float()))
         hist = self._drifts[shard_id]
         expected = float(np.median(hist)) if len(hist) >= self.warmup else None
         poisoned = (not np.isfinite(drift)) or (expected is not None and expected > 0
@@ -76,7 +77,38 @@ class ParameterMonitor:
                                 "expected": expected})
         else:
             hist.append(drift)
+            prev.copy_(flat)
         return {"drift": drift, "expected": expected, "poisoned": poisoned}
+
+    def unchanged(self, shard_id: int, params: Iterable[torch.Tensor]) -> bool:
+        """Between the end of one optimizer step (where :meth:`observe` refreshed the snapshot) and the next forward nothing
+        may touch the parameters: any difference from the snapshot, however small, is tampering (the exact, checksum-style
+        half of the monitor; :meth:`observe` is the drift-norm half).  True when there is no snapshot yet."""
+        prev = self._prev.get(shard_id)
+        if prev is None:
+            return True
+        flat = self._flat(params)
+        ok = prev.numel() == flat.numel() and bool(torch.equal(flat, prev))
+        if not ok:
+            self.events.append({"shard": shard_id, "reason": "changed_between_steps"})
+            logger.error("parameter shard %d changed outside the optimizer", shard_id)
+        return ok
+
+    @torch.no_grad()
+    def restore(self, shard_id: int, params: Iterable[torch.Tensor]) -> bool:
+        """Roll a shard back to its last verified state (the snapshot the drift check keeps): the repair that follows a
+        MODEL_POISONING verdict when there is no replica to copy from.  Returns False when no snapshot exists."""
+        prev = self._prev.get(shard_id)
+        ps = list(params)
+        if prev is None or prev.numel() != sum(p.numel() for p in ps):
+            return False
+        off = 0
+        for p in ps:
+            n = p.numel()
+            p.copy_(prev[off:off + n].view_as(p).to(p.dtype))
+            off += n
+        self.events.append({"shard": shard_id, "reason": "restored"})
+        return True
 
     def observe_drift(self, shard_id: int, drift: float, step: int) -> Dict:
         """Same rule as :meth:`observe` for a drift norm that was measured elsewhere -- the parameter all-gather kernel
