@@ -497,3 +497,36 @@ def test_probation_a_demoted_rank_earns_its_shard_back_only_when_it_behaves():
         assert 1 not in r["owner"] and r["trust"] < 0.5 and max(r["probation_coeff"]) == 0.0
         assert len(r["attacks"]) >= 2 and all(n == 1 for n, _ in r["attacks"])
     assert len({r["wsum"] for r in stubborn}) == 1
+
+
+def _pp_param_worker(rank, world, attack):
+    from trustworthy_dl import AdversarialAttacker, AttackConfig, DistributedTrainer, TrainingConfig
+    from trustworthy_dl.utils.data_loader import get_dataloader
+    torch.manual_seed(0)
+    att = None
+    if attack:
+        att = AdversarialAttacker(AttackConfig(attack_types=["model_poisoning"], target_nodes=[1], intensity=0.5, start_step=9,
+                                               end_step=10))
+        att.activate_attacks()
+    cfg = TrainingConfig(model_name="resnet32", dataset_name="cifar10", batch_size=8, num_nodes=world, learning_rate=1e-3,
+                         checkpoint_interval=0, device="cpu", parallelism="pipeline", micro_batches=2, optimizer="sgd",
+                         parameter_monitoring_enabled=True)
+    t = DistributedTrainer(cfg, attacker=att)
+    t._rank, t._world = rank, world
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=13)]
+    return {"losses": losses, "owner": list(t.stage_map.owner),
+            "attacks": [(a["node_id"], a["step"], a["attack_type"]) for a in t.attack_history]}
+
+
+def test_pipeline_parameter_monitor_neutralises_model_poisoning():
+    """Rank 1's stage is overwritten with noise before step 9.  Its parameter monitor sees parameters that changed outside
+    the optimizer, rolls the stage back bit-exactly BEFORE the forward, every rank learns the verdict with the step's
+    decision vector and the stage changes hands.  The attacked step itself therefore computes exactly what the clean run
+    computes; afterwards the curves differ only by the flagged rank's dropped update of that step."""
+    clean = run_distributed(_pp_param_worker, 2, False)
+    hit = run_distributed(_pp_param_worker, 2, True)
+    assert clean[0]["attacks"] == [] and clean[0]["owner"] == [0, 1]
+    for r in hit:
+        assert r["attacks"] == [(1, 9, "model_poisoning")] and r["owner"] == [0, 0]
+        assert r["losses"][:9] == pytest.approx(clean[0]["losses"][:9], rel=1e-5)        # step 9 ran on the restored weights
+        assert r["losses"][9:] == pytest.approx(clean[0]["losses"][9:], rel=3e-2)

@@ -93,6 +93,7 @@ class PipelineStrategy:
         # message layouts both ends already know: key = (direction, stage boundary, micro-batch rows).  The first message
         # of a key travels with a shape/dtype header (read on the host: one synchronisation); afterwards only the payload
         # is sent and the receive needs no host round trip.  Cleared on every rank when the stage map changes.
+        self._drift_flag = 0.0
         self._known_rx: Dict[Tuple[str, int, int], Tuple[Tuple[int, ...], torch.dtype]] = {}
         self._known_tx: set = set()
 
@@ -131,6 +132,7 @@ class PipelineStrategy:
 
     def _adopt(self, sid: int) -> None:
         st = self.stages[sid].to(self.device)
+        self.t.parameter_monitor.reset(sid)              # a snapshot from an earlier tenure of this stage is stale
         params = [p for p in st.parameters() if p.requires_grad]
         if params and sid not in self.t.optimizers:
             self.t.optimizers[sid] = self.t._make_optimizer(params)
@@ -218,6 +220,18 @@ class PipelineStrategy:
         step = t.global_step
         xs = batch["input"].chunk(self.dp)[self.replica].chunk(M)
         ys = batch["target"].chunk(self.dp)[self.replica].chunk(M)
+        # parameter monitor, exact half: nothing may have touched a hosted stage since its last optimizer step.  A stage that
+        # fails is rolled back to the snapshot before this step's forward; the verdict travels with the decision vector.
+        tampered = self._drift_flag
+        self._drift_flag = 0.0
+        if c.parameter_monitoring_enabled:
+            for sid in self._my_stages():
+                params = list(self.stages[sid].parameters())
+                if t.attacker is not None:
+                    t.attacker.poison_parameters(self.rank, params, step)
+                if not t.parameter_monitor.unchanged(sid, params):
+                    t.parameter_monitor.restore(sid, params)
+                    tampered = 1.0
         acts: Dict[Tuple[int, int], Tuple[Optional[torch.Tensor], torch.Tensor]] = {}
         pending_sends: List = []
         stage_stats = torch.zeros(S, NUM_STATS, dtype=torch.float64)
@@ -297,7 +311,7 @@ class PipelineStrategy:
         loss_local = float(sum(l.detach() for l in losses).item()) if losses else 0.0
 
         # ---- replicated decisions ---------------------------------------------------
-        vec = torch.cat([stage_stats.reshape(-1), have_stats, torch.tensor([my_norm, loss_local,
+        vec = torch.cat([stage_stats.reshape(-1), have_stats, torch.tensor([tampered, my_norm, loss_local,
                          1.0 if losses else 0.0], dtype=torch.float64)])
         tc = time.perf_counter()
         table = comm.all_gather_vector(vec).numpy()
@@ -306,7 +320,7 @@ class PipelineStrategy:
         hv = table[:, S * NUM_STATS:S * NUM_STATS + S]
         norms = table[:, -3]
         loss = float(table[table[:, -1] > 0, -2].sum()) / self.dp  # mean over replicas
-        tainted = self._judge_step(ss, hv, norms, step)
+        tainted = self._judge_step(ss, hv, norms, step, tampered=table[:, -4])
 
         # ---- optimizer --------------------------------------------------------------
         for sid in list(t.optimizers):
@@ -325,6 +339,14 @@ class PipelineStrategy:
                 nn.utils.clip_grad_norm_(self.stages[sid].parameters(), c.clip_norm)
             opt.step()
             opt.zero_grad(set_to_none=True)
+        if c.parameter_monitoring_enabled:
+            # drift half: the size of this update against the stage's own history; refreshes the snapshot the next step's
+            # exact check compares with.  An abnormal update is rolled back and reported with the next decision vector.
+            for sid in self._my_stages():
+                params = list(self.stages[sid].parameters())
+                if t.parameter_monitor.detect_parameter_poisoning(sid, params, step):
+                    t.parameter_monitor.restore(sid, params)
+                    self._drift_flag = 1.0
         self._comm_s += comm_s
         self._step_s += time.perf_counter() - t0
         t.metrics_collector.collect_batch_metrics({
@@ -333,7 +355,8 @@ class PipelineStrategy:
             "step_time": time.perf_counter() - t0, "samples": batch["input"].shape[0]})
         return loss
 
-    def _judge_step(self, ss: np.ndarray, hv: np.ndarray, norms: np.ndarray, step: int) -> bool:
+    def _judge_step(self, ss: np.ndarray, hv: np.ndarray, norms: np.ndarray, step: int,
+                    tampered: Optional[np.ndarray] = None) -> bool:
         """The replicated decisions of one step, from the gathered table (identical on every rank): ``ss[src, s]`` = the 12
         statistics rank ``src`` measured on the output of stage ``s`` of its replica, ``hv`` says which entries exist,
         ``norms[node]`` = that rank's gradient norm.  Returns True when a stage output was flagged (the step is tainted).
@@ -357,6 +380,17 @@ class PipelineStrategy:
         offenders: List[int] = []
         tainted_replicas: set = set()
         unjudged: set = set()
+        if tampered is not None:
+            # the parameter monitor of a rank found (and rolled back) parameters that changed outside the optimizer, or an
+            # update far off the shard's drift history: MODEL_POISONING for that node; the step itself ran on clean weights
+            for node in np.nonzero(np.asarray(tampered) > 0)[0]:
+                node = int(node)
+                t.attack_history.append({"node_id": node, "timestamp": time.time(), "step": step, "attack_type": "model_poisoning",
+                                         "parameter_stats": {"restored_to_last_verified": True}})
+                t.metrics_collector.record_event("attack", node_id=node, type="model_poisoning", step=step)
+                t.trust_manager.mark_compromised(node, "model_poisoning")
+                t.training_state = type(t.training_state)("under_attack")
+                offenders.append(node)
         if c.attack_detection_enabled:
             for node in sorted(out_stats, key=lambda n: (n // self.pp, last_stage[n])):
                 if node // self.pp in tainted_replicas:
@@ -364,8 +398,9 @@ class PipelineStrategy:
                     continue
                 res = t.attack_detector.observe_stats(out_stats[node], node, step)
                 if res.is_attack:
-                    t.handle_detected_attack(node, None, result=res, reassign=False)
-                    offenders.append(node)
+                    if node not in offenders:
+                        t.handle_detected_attack(node, None, result=res, reassign=False)
+                        offenders.append(node)
                     tainted_replicas.add(node // self.pp)
         if c.gradient_verification_enabled:
             for node in range(self.world):
