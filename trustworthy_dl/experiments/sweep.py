@@ -44,8 +44,11 @@ def attack_sweep(base: ExperimentConfig, attack_types: Sequence[str], intensitie
         for mode in (gradient_modes if kind == "gradient_poisoning" else (None,)):
             for x in intensities:
                 tag = f"{base.experiment_name}_{kind}{'_' + mode if mode else ''}_{x:g}"
+                extra = {}
+                if kind == "model_poisoning":           # injected (and caught) by the parameter monitor's hooks
+                    extra["training_overrides"] = {**base.training_overrides, "parameter_monitoring_enabled": True}
                 r = one(tag, attack_enabled=True, attack_types=[kind], attack_intensity=float(x),
-                        gradient_mode=mode or base.gradient_mode)
+                        gradient_mode=mode or base.gradient_mode, **extra)
                 rows.append({"attack_type": kind, "gradient_mode": mode, "intensity": float(x), **r})
     out = Path(base.output_dir)
     out.mkdir(parents=True, exist_ok=True)
@@ -75,7 +78,7 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
     p.add_argument("--batch-size", type=int, default=16)
     p.add_argument("--lr", type=float, default=1e-3)
     p.add_argument("--targets", type=int, nargs="+", default=[1])
-    p.add_argument("--types", nargs="+", default=["gradient_poisoning", "output_poisoning"])
+    p.add_argument("--types", nargs="+", default=["gradient_poisoning", "output_poisoning", "model_poisoning"])
     p.add_argument("--modes", nargs="+", default=["scale", "sign_flip"])
     p.add_argument("--intensities", type=float, nargs="+", default=[0.05, 0.1, 0.25, 0.5, 1.0])
     p.add_argument("--output-dir", default="results/sweep")
