@@ -242,7 +242,6 @@ def _worker(rank, world, dp, virtual, micro, batch, steps, moves, attack_step=No
     (2, 1, 2, 4, 8, [(3, 1)]),             # interleaved stages {0,2} / {1,3}; then rank 0 hosts everything (local hand-offs only)
     (3, 1, 2, 6, 12, [(2, 2)]),            # six interleaved stages on three ranks, the rank with the head gives its stages up
     (4, 2, 2, 4, 16, [(2, 3), (4, 0)]),    # interleaved PP x DP, one move in each replica
-    (4, 1, 1, 4, 8, [(2, 2)]),             # four stages; stage 2 lands on a rank that hosts a non-adjacent stage
     (8, 2, 1, 4, 16, [(3, 2)]),            # BASELINE config 5 layout (PP x4 x DP x2) with a mid-run move
 ])
 def test_fused_pipeline_transport_matches_single_process(world, dp, virtual, micro, batch, moves):
@@ -261,8 +260,6 @@ def test_fused_pipeline_transport_matches_single_process(world, dp, virtual, mic
     assert hosted == sorted(list(range(S)) * dp)
     assert sum(r["wsum"] for r in res) == pytest.approx(dp * ref_wsum, rel=1e-5)
     assert res[0]["flows"][-1] >= res[0]["flows"][0]
-    if moves and world == 4 and dp == 1:
-        assert res[0]["flows"][-1] > res[0]["flows"][0]            # the move created communicators for its new flows
 
 
 def test_fused_pipeline_poisoned_stage_is_flagged_moved_and_its_update_dropped():
