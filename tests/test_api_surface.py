@@ -74,3 +74,14 @@ def test_model_follows_the_named_dataset():
     t3 = DistributedTrainer(TrainingConfig(model_name="vgg16", dataset_name="cifar10", num_nodes=2, device="cpu",
                                            model_kwargs={"num_classes": 7}))
     assert t3._dataset_model_kwargs() == {"num_classes": 7, "input_size": 32}            # explicit kwargs win
+
+
+def test_user_supplied_sequential_model_is_partitioned_by_its_children():
+    import torch.nn as nn
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Flatten(), nn.Linear(3 * 32 * 32, 64), nn.ReLU(), nn.Linear(64, 64), nn.ReLU(), nn.Linear(64, 10))
+    t = DistributedTrainer(TrainingConfig(model_name="custom", dataset_name="cifar10", batch_size=8, num_nodes=3, device="cpu",
+                                          checkpoint_interval=0, learning_rate=1e-2), model=m)
+    losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=8)]
+    assert t.stage_map.owner == [0, 1, 2] and sum(len(p) for p in t.model_partitions.values()) == 6
+    assert losses[-1] < losses[0]

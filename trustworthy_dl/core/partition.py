@@ -46,9 +46,12 @@ def balanced_partition(costs: Sequence[float], num_stages: int) -> List[int]:
 
 def build_stages(model: nn.Module, num_stages: int, cost_fn: Callable[[nn.Module], float] = unit_cost
                  ) -> List[nn.Sequential]:
-    if not hasattr(model, "stage_units"):
-        raise TypeError(f"{type(model).__name__} does not expose stage_units(); cannot partition")
-    units = list(model.stage_units())
+    if hasattr(model, "stage_units"):
+        units = list(model.stage_units())
+    elif isinstance(model, nn.Sequential):
+        units = list(model.children())            # a user's own sequential model: its children are the units
+    else:
+        raise TypeError(f"{type(model).__name__} does not expose stage_units() and is not an nn.Sequential; cannot partition")
     bounds = balanced_partition([cost_fn(u) for u in units], num_stages)
     return [nn.Sequential(*units[a:b]) for a, b in zip(bounds[:-1], bounds[1:])]
 
