@@ -50,7 +50,7 @@ def training_config_from_dict(d: Dict[str, Any], **overrides) -> TrainingConfig:
            "dtype": tr, "clip_norm": tr, "micro_batches": ds, "tp_size": ds, "pp_size": ds, "dp_size": ds,
            "max_reassignment_attempts": sec, "device": ds, "lr_schedule": tr, "checkpoint_dir": tr, "seed": tr,
            "engine": tr, "migration_model": ds, "zero": ds,
-           "detector_require_evidence": sec, "heartbeat_interval": ds, "pp_virtual": ds, "probation": sec}
+           "detector_require_evidence": sec, "heartbeat_interval": ds, "pp_virtual": ds, "probation": sec, "detector_min_history": sec}
     for name, section in opt.items():
         if name in section:
             kw[name] = section[name]

@@ -112,6 +112,7 @@ class TrainingConfig:
     checkpoint_dir: str = "checkpoints"
     migration_model: str = "reference"         # reference (1 GiB/s + 2 s) | nvlink
     detector_require_evidence: bool = True     # an anomaly verdict needs >= 1 statistic beyond z_evidence (False = reference rule)
+    detector_min_history: int = 10             # samples a node's history needs before its outputs are judged (reference: 10)
     heartbeat_interval: int = 10               # steps between liveness gathers across ranks (0 = off)
     initial_trust: float = 1.0
     steps_per_epoch: Optional[int] = None
@@ -162,7 +163,8 @@ class DistributedTrainer:
         self.heartbeat = HeartbeatMonitor(config.num_nodes, max_step_lag=2 * max(1, config.heartbeat_interval),
                                           on_offline=self.trust_manager.mark_offline)
         self.gradient_verifier = GradientVerifier(clip_norm=config.clip_norm)
-        self.attack_detector = AttackDetector(require_evidence=config.detector_require_evidence)
+        self.attack_detector = AttackDetector(require_evidence=config.detector_require_evidence,
+                                              min_history=config.detector_min_history)
         self.parameter_monitor = ParameterMonitor()
         self.metrics_collector = MetricsCollector()
         self.attacker = attacker
