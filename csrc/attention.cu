@@ -64,34 +64,9 @@ struct AttnParams {
 // byte offset of the 16-byte piece `q8` (0..7) of row r inside a [rows x 64] bf16 tile with 128B swizzle
 __device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t q8) { return r * 128u + ((q8 ^ (r & 7u)) << 4); }
 
-// write 32 fp32 values (columns c0..c0+31 of row r, already final) as bf16 into a [128 x 128] operand
-// stored as two swizzled [128 x 64] sub-tiles
-__device__ __forceinline__ void store_p_chunk(uint8_t* tile, int r, int c0, const float (&v)[32]) {
-    uint8_t* sub = tile + (c0 >> 6) * TILE_BYTES;
-    const int q0 = (c0 & 63) >> 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint4 u;
-        u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-        u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-        *reinterpret_cast<uint4*>(sub + swz(r, q0 + q)) = u;
-    }
-}
-
 __device__ __forceinline__ void tma_store_2d_tile(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                  :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
-}
-
-// ---- descriptor helpers for [128 x 64] swizzled tiles ------------------------------------------
-// tile rows are the M/N index, 64 contiguous elements are K (K-major); k16 = which 16-wide K slice
-__device__ __forceinline__ uint64_t desc_kmajor(const uint8_t* tile, int k16) {
-    return umma_smem_desc(smem_u32(tile) + k16 * 32, 16, 1024);
-}
-// tile rows are the K index, 64 contiguous elements are M/N (MN-major); `lbo` = distance between
-// consecutive 64-wide M/N chunks (only used when the operand is wider than 64)
-__device__ __forceinline__ uint64_t desc_mnmajor(const uint8_t* tile, int k16, uint32_t lbo) {
-    return umma_smem_desc(smem_u32(tile) + k16 * 2048, lbo, 1024);
 }
 
 // =================================================================================================
@@ -317,17 +292,10 @@ struct BwdCursor {
 // width chosen by the register array (32 / 16 columns in, 16 / 8 packed columns out)
 __device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32(taddr, r); }
 __device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x16(taddr, r); }
-__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[32]) { tmem_st_32x32(taddr, r); }
-__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[16]) { tmem_st_32x16(taddr, r); }
-__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[8]) { tmem_st_32x8(taddr, r); }
-
-__device__ __forceinline__ void named_bar_math(int id) {          // barrier among the math warps only
-    asm volatile("bar.sync %0, %1;" :: "r"(id), "n"(BWD_WS_MATH) : "memory");
-}
 
 // =================================================================================================
-// backward, phase-specialised (default): the persistent warp-specialised kernel above with the math split by PHASE
-// instead of by column: warps 0-7 only turn S into P (the MUFU-bound stage), warps 8-15 turn (P, dP) into dS and own
+// backward: persistent, warp-specialised (TMA warp, MMA-issue warp, 16 math warps), the math split by PHASE rather than
+// by column: warps 0-7 only turn S into P (the MUFU-bound stage), warps 8-15 turn (P, dP) into dS and own
 // the tile epilogue and the delta computation.  The exp of block j+1 therefore runs under the dS arithmetic, the dK/dQ
 // MMAs and the S MMA of block j instead of taking turns with them (the single dP buffer no longer serialises anything:
 // only the dS group touches dP).  dS is formed from the bf16 P that the tensor core consumes.
@@ -337,7 +305,6 @@ __global__ void __launch_bounds__(BWD_WS_THREADS, 1)
 attn_bwd_ps_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
                    const __grid_constant__ CUtensorMap tmap_dqkv, const __grid_constant__ CUtensorMap tmap_o, const AttnParams p) {
     constexpr int NSTR = BWD_WS_NSTR, NFIX = BWD_WS_NFIX;
-    constexpr int CW = 128 / BWD_WS_NCG;           // S / dP columns per math thread
     TRACE_DECL;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sFix = smem;                                   // [NFIX][2] : MODE0: K,V   MODE1: Q,dO

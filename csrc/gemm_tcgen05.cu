@@ -660,7 +660,6 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ TmapArray tmaps_a, const _
                             else mbar_arrive_remote(&tmem_empty[acc], 0);
                         }
                     }
-                    const int col0 = n_idx + c * 32;
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[c & 1][j]);
