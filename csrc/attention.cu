@@ -289,9 +289,6 @@ struct BwdCursor {
     int ob, h, b; // decoded tile: outer block, head, batch (integer divisions only when the tile changes)
 };
 
-// width chosen by the register array (32 / 16 columns in, 16 / 8 packed columns out)
-__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32(taddr, r); }
-__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x16(taddr, r); }
 
 // =================================================================================================
 // backward: persistent, warp-specialised (TMA warp, MMA-issue warp, 16 math warps), the math split by PHASE rather than
