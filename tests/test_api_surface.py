@@ -85,3 +85,12 @@ def test_user_supplied_sequential_model_is_partitioned_by_its_children():
     losses = [t.train_step(b) for b in get_dataloader("cifar10", "train", 8, num_batches=8)]
     assert t.stage_map.owner == [0, 1, 2] and sum(len(p) for p in t.model_partitions.values()) == 6
     assert losses[-1] < losses[0]
+
+
+def test_metric_summary_ignores_the_non_finite_loss_of_a_tainted_step():
+    from trustworthy_dl.utils.metrics import MetricsCollector
+    m = MetricsCollector()
+    for i, l in enumerate([2.0, float("nan"), 1.0]):
+        m.collect_batch_metrics({"loss": l, "step": i + 1, "epoch": 0, "trust_scores": {0: 1.0}, "step_time": 0.1, "samples": 4})
+    s = m.get_summary()
+    assert s["mean_loss"] == 1.5 and s["final_loss"] == 1.0 and s["non_finite_losses"] == 1

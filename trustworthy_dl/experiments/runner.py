@@ -222,7 +222,7 @@ class ExperimentRunner:
         tmx = self.results_data["training_metrics"]
         if not tmx:
             return {}
-        losses = [m["loss"] for m in tmx]
+        losses = [m["loss"] for m in tmx if np.isfinite(m["loss"])] or [float("nan")]
         summary = {"total_batches": len(tmx), "average_loss": float(np.mean(losses)), "final_loss": float(losses[-1]),
                    "loss_reduction": float((losses[0] - losses[-1]) / losses[0]) if len(losses) > 1 and losses[0] else 0.0,
                    "convergence_achieved": bool(losses[-1] < 0.5)}

@@ -51,9 +51,11 @@ class MetricsCollector:
         out: Dict[str, Any] = {"num_batches": len(self.records), "wall_time": time.time() - self._t0}
         if losses:
             arr = np.asarray(losses, dtype=np.float64)
-            out.update({"mean_loss": float(arr.mean()), "final_loss": float(arr[-1]),
-                        "min_loss": float(arr.min()),
-                        "perplexity": float(math.exp(min(20.0, arr[-min(10, arr.size):].mean())))})
+            fin = arr[np.isfinite(arr)]                 # a tainted step can report a non-finite loss (its update is dropped)
+            out["non_finite_losses"] = int(arr.size - fin.size)
+            if fin.size:
+                out.update({"mean_loss": float(fin.mean()), "final_loss": float(fin[-1]), "min_loss": float(fin.min()),
+                            "perplexity": float(math.exp(min(20.0, fin[-min(10, fin.size):].mean())))})
         accs = [r["accuracy"] for r in self.records if "accuracy" in r]
         if accs:
             out["accuracy"] = float(np.mean(accs[-10:]))
