@@ -82,13 +82,7 @@ class DataParallelStrategy:
                 logger.info("engine: auto -> eager path (%s)", "; ".join(why))
                 use_fused = False
         if use_fused:
-            from ..engine.gpt2_engine import GPT2Engine
-            self.engine = GPT2Engine.from_module(model, batch_size=max(1, c.batch_size // self.world),
-                                                 seq_len=c.seq_len or model.config.n_positions,
-                                                 lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
-                                                 security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
-                                                 zero=int(getattr(c, "zero", 0) or 0),
-                                                 trust_threshold=c.trust_threshold)
+            self.engine = self._make_engine(model)
             self.reducer = self.engine.reducer
             t.model_partitions[0] = model
         else:
@@ -112,6 +106,18 @@ class DataParallelStrategy:
         # data shards play the role of stages: shard i starts on rank i
         t.stage_map = StageMap(self.world, self.world)
         t.stage_costs = [1.0] * self.world
+
+    def _make_engine(self, model):
+        """The fused replica engine (one place, so that tests/test_fused_wrappers_cpu.py can run the host side of
+        ``_engine_step`` over gloo with a stand-in)."""
+        from ..engine.gpt2_engine import GPT2Engine
+        c = self.t.config
+        return GPT2Engine.from_module(model, batch_size=max(1, c.batch_size // self.world),
+                                      seq_len=c.seq_len or model.config.n_positions,
+                                      lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
+                                      security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
+                                      zero=int(getattr(c, "zero", 0) or 0),
+                                      trust_threshold=c.trust_threshold)
 
     # ------------------------------------------------------------------ step
     def _local_batch(self, batch: Dict[str, torch.Tensor]) -> Optional[Dict[str, torch.Tensor]]:

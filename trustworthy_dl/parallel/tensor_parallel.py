@@ -274,11 +274,7 @@ class TensorParallelStrategy:
         if not why:
             # the whole tensor-parallel step on the repo's kernels (engine/gpt2_tp_engine.py): K7 / K8 for every fused
             # collective, tcgen05 wgrads, local-head attention, LayerNorm on the token shard, one CUDA graph
-            from ..engine.gpt2_tp_engine import GPT2TPEngine
-            self.engine = GPT2TPEngine.from_module(base, batch_size=c.batch_size, seq_len=c.seq_len or base.config.n_positions,
-                                                   lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
-                                                   security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
-                                                   trust_threshold=c.trust_threshold)
+            self.engine = self._make_engine(base)
             self.model = base
             t.model_partitions[0] = base
             t.stage_map = StageMap(self.world, self.world)
@@ -304,6 +300,16 @@ class TensorParallelStrategy:
         t.schedulers[0] = t._make_scheduler(t.optimizers[0])
         t.stage_map = StageMap(self.world, self.world)
         t.stage_costs = [1.0] * self.world
+
+    def _make_engine(self, base):
+        """The tensor-parallel engine (one place, so that tests/test_fused_wrappers_cpu.py can run the host side of
+        ``_engine_step`` over gloo with a stand-in)."""
+        from ..engine.gpt2_tp_engine import GPT2TPEngine
+        c = self.t.config
+        return GPT2TPEngine.from_module(base, batch_size=c.batch_size, seq_len=c.seq_len or base.config.n_positions,
+                                        lr=c.learning_rate, weight_decay=c.weight_decay, device=self.device,
+                                        security=bool(c.attack_detection_enabled or c.gradient_verification_enabled),
+                                        trust_threshold=c.trust_threshold)
 
     def _fused_blockers(self, base) -> List[str]:
         c, cfg = self.t.config, base.config
