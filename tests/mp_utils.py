@@ -51,14 +51,22 @@ def run_distributed(fn, world: int, *args, timeout: float = 240.0):
     import time
     deadline = time.time() + timeout
     while any(p.is_alive() for p in procs) and time.time() < deadline:
-        if any(v[0] == "err" for v in dict(results).values()):
+        seen = dict(results)
+        if any(v[0] == "err" for v in seen.values()):
             break                                  # a rank failed: its peers would wait for it in a collective until the deadline
+        if any((not p.is_alive()) and i not in seen for i, p in enumerate(procs)):
+            time.sleep(0.5)                        # (the result may still be in flight)
+            if any((not p.is_alive()) and i not in dict(results) for i, p in enumerate(procs)):
+                break                              # a rank died without reporting: same thing
         time.sleep(0.1)
     alive = [i for i, p in enumerate(procs) if p.is_alive()]
     if alive:
         if any(v[0] == "err" for v in dict(results).values()):
             time.sleep(1.0)                        # let the other ranks report their own exception, if any
         failed = {r: v[1] for r, v in dict(results).items() if v[0] == "err"}
+        for i, p in enumerate(procs):
+            if not p.is_alive() and i not in dict(results) and i not in failed:
+                failed[i] = f"process exited with code {p.exitcode} without reporting a result"
         for p in procs:
             if p.is_alive():
                 p.kill()

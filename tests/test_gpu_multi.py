@@ -43,14 +43,22 @@ def _run(fn, world):
     import time
     deadline = time.time() + 240
     while any(p.is_alive() for p in procs) and time.time() < deadline:
-        if any(v[0] == "err" for v in dict(ret).values()):
+        seen = dict(ret)
+        if any(v[0] == "err" for v in seen.values()):
             break                                  # a rank failed: its peers would wait for it in a collective until the deadline
+        if any((not p.is_alive()) and i not in seen for i, p in enumerate(procs)):
+            time.sleep(0.5)                        # (the result may still be in flight)
+            if any((not p.is_alive()) and i not in dict(ret) for i, p in enumerate(procs)):
+                break                              # a rank died without reporting (device fault, abort): same thing
         time.sleep(0.2)
     failed = {r: v[1] for r, v in dict(ret).items() if v[0] == "err"}
     hung = [i for i, p in enumerate(procs) if p.is_alive()]
     if hung:
         time.sleep(2.0 if failed else 0.0)         # let the other ranks report their own exception, if any
         failed = {r: v[1] for r, v in dict(ret).items() if v[0] == "err"}
+        for i, p in enumerate(procs):
+            if not p.is_alive() and i not in dict(ret) and i not in failed:
+                failed[i] = f"process exited with code {p.exitcode} without reporting a result"
         for p in procs:
             if p.is_alive():
                 p.kill()
